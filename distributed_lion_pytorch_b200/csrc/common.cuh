@@ -1,0 +1,196 @@
+// common.cuh — shared device helpers for libdlion (sm_100a only).
+#pragma once
+#include <cuda_bf16.h>
+#include <cuda_fp16.h>
+#include <cuda_runtime.h>
+#include <stdint.h>
+#include <stdio.h>
+
+#include "../../include/dlion.h"
+
+namespace dlion {
+
+void set_error(const char* fmt, ...);
+int check_cuda(cudaError_t e, const char* what);
+
+#define DLION_CHECK_ARG(cond, ...)      \
+  do {                                  \
+    if (!(cond)) {                      \
+      ::dlion::set_error(__VA_ARGS__);  \
+      return DLION_E_BADARG;            \
+    }                                   \
+  } while (0)
+
+#define DLION_LAUNCH_CHECK(what) ::dlion::check_cuda(cudaGetLastError(), what)
+
+#define DISPATCH_DTYPE(dtype, ...)                                   \
+  switch (dtype) {                                                   \
+    case DLION_F32: { using T = float; __VA_ARGS__; } break;         \
+    case DLION_BF16: { using T = __nv_bfloat16; __VA_ARGS__; } break;\
+    case DLION_F16: { using T = __half; __VA_ARGS__; } break;        \
+    default: ::dlion::set_error("unsupported dtype %d", dtype); return DLION_E_UNSUPPORTED; \
+  }
+
+
+constexpr int kNumSMs = 148;  // B200
+
+static inline bool aligned16(const void* p) { return (reinterpret_cast<uintptr_t>(p) & 15u) == 0; }
+
+// ------------------------------------------------------------------ dtype traits
+// Every op rounds through the storage type exactly where ATen's elementwise kernels do, so
+// the fused kernels reproduce the reference's bf16 arithmetic bit for bit.
+template <typename T>
+struct DT;
+template <>
+struct DT<float> {
+  static constexpr int id = DLION_F32;
+  __device__ __forceinline__ static float rnd(float x) { return x; }
+  __device__ __forceinline__ static float to_f(float x) { return x; }
+  __device__ __forceinline__ static float from_f(float x) { return x; }
+};
+template <>
+struct DT<__nv_bfloat16> {
+  static constexpr int id = DLION_BF16;
+  __device__ __forceinline__ static float rnd(float x) { return __bfloat162float(__float2bfloat16_rn(x)); }
+  __device__ __forceinline__ static float to_f(__nv_bfloat16 x) { return __bfloat162float(x); }
+  __device__ __forceinline__ static __nv_bfloat16 from_f(float x) { return __float2bfloat16_rn(x); }
+};
+template <>
+struct DT<__half> {
+  static constexpr int id = DLION_F16;
+  __device__ __forceinline__ static float rnd(float x) { return __half2float(__float2half_rn(x)); }
+  __device__ __forceinline__ static float to_f(__half x) { return __half2float(x); }
+  __device__ __forceinline__ static __half from_f(float x) { return __float2half_rn(x); }
+};
+
+// 8 consecutive elements <-> float[8].  Pointers must be 16-byte aligned for 2-byte types and
+// 32-byte... no: fp32 uses two 16-byte accesses, so 16-byte alignment suffices everywhere.
+template <typename T>
+__device__ __forceinline__ void load8(const T* __restrict__ ptr, float (&v)[8]);
+template <typename T>
+__device__ __forceinline__ void store8(T* __restrict__ ptr, const float (&v)[8]);
+
+template <>
+__device__ __forceinline__ void load8<float>(const float* __restrict__ ptr, float (&v)[8]) {
+  const float4 a = reinterpret_cast<const float4*>(ptr)[0];
+  const float4 b = reinterpret_cast<const float4*>(ptr)[1];
+  v[0] = a.x; v[1] = a.y; v[2] = a.z; v[3] = a.w;
+  v[4] = b.x; v[5] = b.y; v[6] = b.z; v[7] = b.w;
+}
+template <>
+__device__ __forceinline__ void store8<float>(float* __restrict__ ptr, const float (&v)[8]) {
+  reinterpret_cast<float4*>(ptr)[0] = make_float4(v[0], v[1], v[2], v[3]);
+  reinterpret_cast<float4*>(ptr)[1] = make_float4(v[4], v[5], v[6], v[7]);
+}
+template <>
+__device__ __forceinline__ void load8<__nv_bfloat16>(const __nv_bfloat16* __restrict__ ptr, float (&v)[8]) {
+  const uint4 raw = *reinterpret_cast<const uint4*>(ptr);
+  const uint32_t w[4] = {raw.x, raw.y, raw.z, raw.w};
+#pragma unroll
+  for (int i = 0; i < 4; ++i) {  // bf16 -> fp32 is a 16-bit shift
+    v[2 * i] = __uint_as_float(w[i] << 16);
+    v[2 * i + 1] = __uint_as_float(w[i] & 0xffff0000u);
+  }
+}
+template <>
+__device__ __forceinline__ void store8<__nv_bfloat16>(__nv_bfloat16* __restrict__ ptr, const float (&v)[8]) {
+  uint32_t w[4];
+#pragma unroll
+  for (int i = 0; i < 4; ++i) {
+    const __nv_bfloat162 h = __floats2bfloat162_rn(v[2 * i], v[2 * i + 1]);
+    w[i] = *reinterpret_cast<const uint32_t*>(&h);
+  }
+  *reinterpret_cast<uint4*>(ptr) = make_uint4(w[0], w[1], w[2], w[3]);
+}
+template <>
+__device__ __forceinline__ void load8<__half>(const __half* __restrict__ ptr, float (&v)[8]) {
+  const uint4 raw = *reinterpret_cast<const uint4*>(ptr);
+  const uint32_t w[4] = {raw.x, raw.y, raw.z, raw.w};
+#pragma unroll
+  for (int i = 0; i < 4; ++i) {
+    const float2 f = __half22float2(*reinterpret_cast<const __half2*>(&w[i]));
+    v[2 * i] = f.x;
+    v[2 * i + 1] = f.y;
+  }
+}
+template <>
+__device__ __forceinline__ void store8<__half>(__half* __restrict__ ptr, const float (&v)[8]) {
+  uint32_t w[4];
+#pragma unroll
+  for (int i = 0; i < 4; ++i) {
+    const __half2 h = __floats2half2_rn(v[2 * i], v[2 * i + 1]);
+    w[i] = *reinterpret_cast<const uint32_t*>(&h);
+  }
+  *reinterpret_cast<uint4*>(ptr) = make_uint4(w[0], w[1], w[2], w[3]);
+}
+
+// ------------------------------------------------------------------ Lion math (one element)
+// blend: c = round(round(m*b1) + (1-b1)*g)   (reference: distributed_lion.py:54,68 —
+// exp_avg.clone().mul_(beta1).add(grad, alpha=1-beta1); ATen's add kernel is one fma in fp32)
+template <typename T>
+__device__ __forceinline__ float lion_blend(float m, float g, float beta1, float omb1) {
+  return DT<T>::rnd(fmaf(omb1, g, DT<T>::rnd(m * beta1)));
+}
+// momentum: m' = round(round(m*b2) + (1-b2)*g)   (reference: distributed_lion.py:59,96)
+template <typename T>
+__device__ __forceinline__ float lion_momentum(float m, float g, float beta2, float omb2) {
+  return DT<T>::rnd(fmaf(omb2, g, DT<T>::rnd(m * beta2)));
+}
+// parameter: p' = round(round(p*decay) - lr*u)    (reference: distributed_lion.py:51,55,64,92)
+template <typename T>
+__device__ __forceinline__ float lion_apply(float p, float u, float lr, float decay) {
+  return DT<T>::rnd(fmaf(-lr, u, DT<T>::rnd(p * decay)));
+}
+
+// ------------------------------------------------------------------ Philox4x32-10
+struct Philox {
+  __device__ __forceinline__ static uint4 gen(uint64_t seed, uint64_t ctr_lo, uint32_t ctr_hi0, uint32_t ctr_hi1) {
+    uint32_t k0 = (uint32_t)seed, k1 = (uint32_t)(seed >> 32);
+    uint32_t c0 = (uint32_t)ctr_lo, c1 = (uint32_t)(ctr_lo >> 32), c2 = ctr_hi0, c3 = ctr_hi1;
+#pragma unroll
+    for (int i = 0; i < 10; ++i) {
+      const uint32_t hi0 = __umulhi(0xD2511F53u, c0), lo0 = 0xD2511F53u * c0;
+      const uint32_t hi1 = __umulhi(0xCD9E8D57u, c2), lo1 = 0xCD9E8D57u * c2;
+      const uint32_t n0 = hi1 ^ c1 ^ k0, n1 = lo1, n2 = hi0 ^ c3 ^ k1, n3 = lo0;
+      c0 = n0; c1 = n1; c2 = n2; c3 = n3;
+      k0 += 0x9E3779B9u;
+      k1 += 0xBB67AE85u;
+    }
+    return make_uint4(c0, c1, c2, c3);
+  }
+  __device__ __forceinline__ static float u01(uint32_t x) { return (float)(x >> 8) * (1.0f / 16777216.0f); }
+};
+
+// the byte of 8 sign bits for 8 consecutive elements starting at global element index e0
+template <typename T>
+__device__ __forceinline__ uint32_t sign_byte(const float (&m)[8], const float (&g)[8], float beta1, float omb1,
+                                              float stoch_r, uint64_t seed, uint32_t step, uint32_t rank,
+                                              int64_t e0) {
+  uint32_t byte = 0;
+  if (stoch_r > 0.f) {
+    const uint4 r0 = Philox::gen(seed, (uint64_t)e0, step, rank);
+    const uint4 r1 = Philox::gen(seed, (uint64_t)e0 + 4, step, rank);
+    const uint32_t rr[8] = {r0.x, r0.y, r0.z, r0.w, r1.x, r1.y, r1.z, r1.w};
+    const float inv = 1.0f / (2.0f * stoch_r);
+#pragma unroll
+    for (int i = 0; i < 8; ++i) {
+      const float c = lion_blend<T>(m[i], g[i], beta1, omb1);
+      const float prob = (c + stoch_r) * inv;
+      byte |= (Philox::u01(rr[i]) < prob ? 1u : 0u) << i;
+    }
+  } else {
+#pragma unroll
+    for (int i = 0; i < 8; ++i) byte |= (lion_blend<T>(m[i], g[i], beta1, omb1) > 0.f ? 1u : 0u) << i;
+  }
+  return byte;
+}
+
+// direction u for one element given the +1 count among L live workers
+__device__ __forceinline__ float vote_dir(int cnt, int L, float invL_unused, int vote) {
+  const int twice = 2 * cnt;
+  if (vote == DLION_VOTE_AVERAGE) return __fdiv_rn((float)(twice - L), (float)L);
+  if (vote == DLION_VOTE_MAJORITY_ZERO && twice == L) return 0.f;
+  return twice > L ? 1.f : -1.f;
+}
+
+}  // namespace dlion

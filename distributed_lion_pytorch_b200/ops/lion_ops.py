@@ -1,0 +1,68 @@
+"""Optimizer kernels: N6 local Lion, sign-pack, vote-update and the fused N1 step.
+reference: distributed_lion.py:47-96 (update_fn / update_fn_distributed)."""
+from __future__ import annotations
+
+from typing import Optional
+
+import torch
+
+from . import _cabi
+
+
+def _scalars(lr: float, wd: float, beta1: float, beta2: float):
+    # computed in double exactly like the reference's Python expressions, rounded to fp32 once
+    return float(lr), float(1 - lr * wd), float(beta1), float(1 - beta1), float(beta2), float(1 - beta2)
+
+
+def _check_triplet(p, g, m):
+    assert p.is_cuda and p.is_contiguous() and g.is_contiguous() and m.is_contiguous()
+    assert p.dtype == g.dtype == m.dtype and p.numel() == g.numel() == m.numel()
+
+
+def local_step(p: torch.Tensor, g: torch.Tensor, m: torch.Tensor, lr: float, wd: float, beta1: float,
+               beta2: float) -> None:
+    _check_triplet(p, g, m)
+    lr_, decay, b1, omb1, b2, omb2 = _scalars(lr, wd, beta1, beta2)
+    with torch.cuda.device(p.device):
+        _cabi.check(_cabi.lib().dlion_lion_local(p.data_ptr(), g.data_ptr(), m.data_ptr(), p.numel(),
+                                                 _cabi.dtype_code(p.dtype), lr_, decay, b1, omb1, b2, omb2,
+                                                 _cabi.stream_ptr(p.device)), "lion_local")
+
+
+def stoch_radius(beta1: float, max_grad_norm: Optional[float]) -> float:
+    """r = (1 + 1/beta1) * max_grad_norm (reference: distributed_lion.py:106); 0 disables."""
+    if max_grad_norm is None:
+        return 0.0
+    return float((1.0 + 1.0 / beta1) * max_grad_norm)
+
+
+def sign_pack(m: torch.Tensor, g: torch.Tensor, beta1: float, out: torch.Tensor, *,
+              max_grad_norm: Optional[float] = None, seed: int = 0, step: int = 0, rank: int = 0) -> torch.Tensor:
+    """out: uint8[>= ceil(n/32)*4] (or int32 words); bit e%8 of byte e//8 = sign bit of element e."""
+    assert m.is_cuda and m.is_contiguous() and g.is_contiguous() and out.is_contiguous()
+    n = m.numel()
+    assert out.numel() * out.element_size() >= (n + 31) // 32 * 4, "wire buffer too small"
+    with torch.cuda.device(m.device):
+        _cabi.check(_cabi.lib().dlion_sign_pack(m.data_ptr(), g.data_ptr(), out.data_ptr(), n,
+                                                _cabi.dtype_code(m.dtype), float(beta1), float(1 - beta1),
+                                                stoch_radius(beta1, max_grad_norm), int(seed) & (2**64 - 1),
+                                                int(step) & 0xffffffff, int(rank), _cabi.stream_ptr(m.device)),
+                    "sign_pack")
+    return out
+
+
+def vote_update(p: torch.Tensor, g: torch.Tensor, m: torch.Tensor, gathered: torch.Tensor, world: int,
+                live_mask: Optional[int], lr: float, wd: float, beta2: float, vote: str = "majority",
+                tie: str = "neg") -> None:
+    """gathered: [world, row_bytes] uint8 (row_bytes % 4 == 0), row r = rank r's packed signs."""
+    _check_triplet(p, g, m)
+    assert gathered.is_contiguous() and gathered.dim() == 2 and gathered.shape[0] == world
+    row_bytes = gathered.shape[1] * gathered.element_size()
+    assert row_bytes % 4 == 0
+    mask = (1 << world) - 1 if live_mask is None else int(live_mask) & ((1 << world) - 1)
+    lr_, decay, _, _, b2, omb2 = _scalars(lr, wd, 0.0, beta2)
+    with torch.cuda.device(p.device):
+        _cabi.check(_cabi.lib().dlion_vote_update(p.data_ptr(), g.data_ptr(), m.data_ptr(), gathered.data_ptr(),
+                                                  row_bytes // 4, world, mask, p.numel(), _cabi.dtype_code(p.dtype),
+                                                  lr_, decay, b2, omb2, _cabi.VOTE_CODES[(vote, tie)],
+                                                  _cabi.stream_ptr(p.device)), "vote_update")

@@ -1,0 +1,140 @@
+"""Step back-ends for :class:`Lion` — where the sign exchange happens.
+
+reference: distributed_lion.py:61-96 is the only strategy upstream (encode → list-API
+``all_gather`` of an int64 tensor per parameter → decode → ``torch.mode``).  Here the
+strategy is pluggable per bucket; see ``optim/lion.py`` for the user-facing description.
+"""
+from __future__ import annotations
+
+import os
+from typing import List, Optional
+
+import torch
+import torch.distributed as dist
+
+from . import semantics as sem
+from .bucket import Bucket
+
+
+class _Backend:
+    name = "base"
+
+    def __init__(self, opt):
+        self.world_size = opt.world_size
+        self.opt = opt
+
+    def on_rebucket(self, opt) -> None:
+        pass
+
+    def _use_kernels(self, b: Bucket) -> bool:
+        return self.opt._kernels_ok(b.device)
+
+    def step(self, b: Bucket, lr: float, wd: float, beta1: float, beta2: float, missing: List[int]) -> None:
+        raise NotImplementedError
+
+
+class LocalBackend(_Backend):
+    """Single-worker Lion (reference: distributed_lion.py:47-59)."""
+    name = "local"
+
+    def step(self, b, lr, wd, beta1, beta2, missing):
+        if missing:
+            # reference semantics: a parameter without a gradient is left untouched this step
+            skip = set(missing)
+            spans = [(pv, gv, mv) for i, (pv, gv, mv) in enumerate(zip(b.p_views, b.g_views, b.m_views))
+                     if i not in skip]
+        else:
+            spans = [(b.flat_p, b.flat_g, b.flat_m)]
+        if self._use_kernels(b):
+            from ..ops import lion_ops
+            for p, g, m in spans:
+                lion_ops.local_step(p, g, m, lr, wd, beta1, beta2)
+        else:
+            for p, g, m in spans:
+                sem.local_lion_step_(p, g, m, lr, wd, beta1, beta2)
+
+
+class AllGatherBackend(_Backend):
+    """``nccl_1bit``: split pack / all-gather / vote+update.  The true 1-bit payload goes
+    through ``torch.distributed`` (NCCL on GPUs, gloo on CPU) — the baseline the fused
+    kernel is measured against, and the fallback for multi-node jobs."""
+    name = "nccl_1bit"
+
+    def _wire(self, b: Bucket):
+        W = self.world_size
+        mine = b.scratch.get("wire_out")
+        if mine is None or mine.numel() != b.wire_bytes:
+            mine = torch.zeros(b.wire_bytes, dtype=torch.uint8, device=b.device)
+            b.scratch["wire_out"] = mine
+            b.scratch["wire_in"] = torch.zeros(W, b.wire_bytes, dtype=torch.uint8, device=b.device)
+        return mine, b.scratch["wire_in"]
+
+    def _all_gather(self, out: torch.Tensor, inp: torch.Tensor) -> None:
+        pg = self.opt.process_group
+        try:
+            dist.all_gather_into_tensor(out.view(-1), inp, group=pg)
+        except (RuntimeError, NotImplementedError):
+            chunks = list(out.unbind(0))
+            dist.all_gather(chunks, inp, group=pg)
+
+    def step(self, b, lr, wd, beta1, beta2, missing):
+        opt = self.opt
+        W = self.world_size
+        mine, gathered = self._wire(b)
+        kern = self._use_kernels(b)
+        if kern:
+            from ..ops import lion_ops
+            lion_ops.sign_pack(b.flat_m, b.flat_g, beta1, mine, max_grad_norm=opt.max_grad_norm,
+                               seed=opt.seed, step=opt._steps_done, rank=opt.rank)
+        else:
+            gen = opt.cpu_generator() if opt.max_grad_norm is not None else None
+            bits = sem.local_bits(b.flat_m, b.flat_g, beta1, max_grad_norm=opt.max_grad_norm, generator=gen)
+            mine.copy_(sem.pack_bits(bits))
+        self._all_gather(gathered, mine)
+        L = opt.live_count()
+        if kern:
+            lion_ops.vote_update(b.flat_p, b.flat_g, b.flat_m, gathered, W, opt.live_mask, lr, wd, beta2,
+                                 opt.vote, opt.tie)
+        else:
+            cnt = sem.count_votes(gathered, b.numel, opt.live_mask)
+            sem.apply_vote_(b.flat_p, b.flat_g, b.flat_m, cnt, L, lr, wd, beta2, opt.vote, opt.tie)
+
+
+class FusedBackend(_Backend):
+    """One persistent sm_100a kernel per bucket chunk; the sign words travel as peer stores
+    over NVLink into symmetric arenas (``parallel.symm``); no NCCL call on the hot path."""
+    name = "fused"
+
+    def __init__(self, opt):
+        super().__init__(opt)
+        from ..parallel import symm
+        self._symm = symm
+        self._ctx = None
+
+    def on_rebucket(self, opt) -> None:
+        self._ctx = None
+
+    def step(self, b, lr, wd, beta1, beta2, missing):
+        opt = self.opt
+        if b.device.type != "cuda":
+            raise RuntimeError("comm='fused' needs CUDA tensors; use comm='nccl_1bit' on CPU")
+        if self._ctx is None:
+            self._ctx = self._symm.FusedExchange(opt.process_group, b.device)
+        self._ctx.step(b, lr, wd, beta1, beta2, vote=opt.vote, tie=opt.tie, live_mask=opt.live_mask,
+                       max_grad_norm=opt.max_grad_norm, seed=opt.seed, step_index=opt._steps_done)
+
+
+def pick_auto(opt) -> _Backend:
+    """CUDA + every rank on one NVLink domain + peer-mapped memory available → fused; else nccl_1bit."""
+    dev = None
+    for g in opt.param_groups:
+        for p in g["params"]:
+            dev = p.device
+            break
+        if dev is not None:
+            break
+    if dev is not None and dev.type == "cuda" and opt._kernels_ok(dev):
+        from ..parallel import symm
+        if symm.fused_supported(opt.process_group):
+            return FusedBackend(opt)
+    return AllGatherBackend(opt)

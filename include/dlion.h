@@ -1,0 +1,183 @@
+/*
+ * dlion.h — C ABI of libdlion.so, the sm_100a kernel library of distributed_lion_pytorch_b200.
+ *
+ * Conventions
+ *   - every entry point returns 0 on success, a cudaError_t (> 0) when the CUDA runtime
+ *     reported a failure, or a negative DLION_E_* code for argument errors;
+ *     dlion_last_error() returns a human-readable description of the last failure on the
+ *     calling thread;
+ *   - `stream` is a cudaStream_t passed as void* (0 = legacy default stream);
+ *   - tensors are raw device pointers, 16-byte aligned unless stated otherwise; `dtype` is a
+ *     dlion_dtype; element counts are int64_t;
+ *   - nothing in this library allocates device memory unless the comment says so: callers
+ *     (PyTorch's caching allocator, in this repository) own every buffer.
+ *
+ * "reference:" comments cite kyleliang919/distributed-lion-pytorch (file:line) — the Python
+ * op sequence each kernel replaces.
+ */
+#ifndef DLION_H_
+#define DLION_H_
+
+#include <stdint.h>
+
+#ifdef __cplusplus
+extern "C" {
+#endif
+
+#define DLION_VERSION 100
+
+typedef enum { DLION_F32 = 0, DLION_BF16 = 1, DLION_F16 = 2 } dlion_dtype;
+
+/* vote rule applied to cnt (# of live +1 ballots) out of L live workers */
+typedef enum {
+  DLION_VOTE_MAJORITY_NEG = 0,  /* +1 iff 2cnt > L else -1      (reference: distributed_lion.py:33-43,91) */
+  DLION_VOTE_MAJORITY_ZERO = 1, /* as above, 0 on 2cnt == L     (paper: sign(sum delta_i))               */
+  DLION_VOTE_AVERAGE = 2        /* (2cnt - L) / L               (paper: Averaging)                       */
+} dlion_vote;
+
+#define DLION_E_BADARG (-1)
+#define DLION_E_UNSUPPORTED (-2)
+#define DLION_E_TOOBIG (-3)
+#define DLION_E_TIMEOUT (-4)
+
+#define DLION_MAX_RANKS 16
+
+const char* dlion_last_error(void);
+int dlion_version(void);
+/* number of SMs / max co-resident CTAs of the fused kernel on the current device */
+int dlion_device_sm_count(int* out);
+
+/* ---------------------------------------------------------------- optimizer kernels */
+
+/* N6 — single-worker Lion, one pass: p*=decay; p-=lr*sign(b1*m+(1-b1)*g); m=b2*m+(1-b2)*g.
+ * `decay` = 1 - lr*wd, `omb1` = 1-beta1, `omb2` = 1-beta2 are computed by the caller in double
+ * and rounded once, like ATen does with Python scalars.
+ * reference: distributed_lion.py:47-59 (update_fn: 7 ATen kernels, 2 temporaries). */
+int dlion_lion_local(void* p, const void* g, void* m, int64_t n, int dtype, float lr, float decay,
+                     float beta1, float omb1, float beta2, float omb2, void* stream);
+
+/* Sign + pack: words[e/32] bit e%32 = (b1*m + (1-b1)*g)[e] > 0; tail bits of the last word are 0.
+ * stoch_r > 0 selects stochastic binarisation, bit ~ Bernoulli((c + r) / 2r) with a Philox
+ * stream keyed by (seed, step, rank, element).
+ * reference: distributed_lion.py:68-77 (and :106-117 for the stochastic variant). */
+int dlion_sign_pack(const void* m, const void* g, uint32_t* words, int64_t n, int dtype, float beta1,
+                    float omb1, float stoch_r, uint64_t seed, uint32_t step, uint32_t rank, void* stream);
+
+/* Vote + update from gathered words (`gathered` = world rows of `row_words` uint32 each).
+ * live_mask bit r = rank r's ballot counts.
+ * reference: distributed_lion.py:64,84-96 (unpack ×W, torch.mode, add_, momentum EMA). */
+int dlion_vote_update(void* p, const void* g, void* m, const uint32_t* gathered, int64_t row_words,
+                      int world, uint32_t live_mask, int64_t n, int dtype, float lr, float decay,
+                      float beta2, float omb2, int vote, void* stream);
+
+/* N1 — the fused sign-pack-exchange-vote-update kernel (one persistent cooperative launch).
+ *
+ * Every rank launches the same grid over the same n (multiple of the tile).  For tile t the
+ * CTA that owns it TMA-loads g/m/p into shared memory, packs the signs, stores the words into
+ * arena slot [parity][my rank] of every peer (`arena[r]` is rank r's arena as mapped into THIS
+ * process; arena[rank] is the local one), releases a per-(source rank, CTA) progress flag on
+ * each peer, and `lookahead` tiles later acquires the peers' flags, popcounts the live ballots
+ * and writes p and m.  No other kernel and no NCCL call takes part.
+ *
+ *   arena layout (uint32): [2 parities][world][arena_words]      arena_words >= n/32
+ *   flags layout (uint64): [world][DLION_FUSED_MAX_CTAS]         monotone, never reset
+ *   epoch: strictly increasing launch counter shared by all ranks (parity = epoch & 1)
+ *
+ * emulate_ranks > 0: single-GPU protocol emulation — the grid is split into `emulate_ranks`
+ * groups of CTAs, group v acting as rank v on p/g/m + v*emu_stride elements, all arenas /
+ * flags living on this device (arena[v], flags[v]).  Used by the one-GPU tests.
+ *
+ * status (device int32[4], may be NULL): [0]=0 ok / 1 flag-wait timeout, [1]=CTA, [2]=src rank.
+ * reference: distributed_lion.py:61-96 + the NCCL all_gather it calls at :81. */
+typedef struct {
+  void* p;
+  const void* g;
+  void* m;
+  int64_t n;
+  int dtype;
+  int world;
+  int rank;
+  uint32_t live_mask;  /* ballots that count */
+  uint32_t wait_mask;  /* ranks whose flags are awaited (normally all) */
+  float lr, decay, beta1, omb1, beta2, omb2;
+  int vote;
+  float stoch_r;
+  uint64_t seed;
+  uint32_t step;
+  uint64_t epoch;
+  uint32_t* arena[DLION_MAX_RANKS];
+  uint64_t* flags[DLION_MAX_RANKS];
+  int64_t arena_words;
+  int grid;            /* CTAs per (virtual) rank; identical on every rank */
+  int emulate_ranks;
+  int64_t emu_stride;
+  int32_t* status;
+  int64_t spin_limit;  /* flag polls before giving up (0 = default) */
+} dlion_fused_args;
+
+#define DLION_FUSED_MAX_CTAS 1024
+int dlion_fused_step(const dlion_fused_args* args, void* stream);
+/* tile size (elements) for a dtype, and the largest grid the device can co-schedule */
+int dlion_fused_tile(int dtype);
+int dlion_fused_max_grid(int dtype, int* out);
+
+/* ---------------------------------------------------------------- bucket kernels (N2) */
+
+/* Copy/cast up to `count` tensors into their slots of a flat bucket with one launch per 96
+ * tensors.  srcs/dsts/numels are HOST arrays.  reference: the implicit per-tensor loop of
+ * distributed_lion.py:179-198 and flatten_and_pad :14-24. */
+int dlion_multi_gather(const void* const* srcs, void* const* dsts, const int64_t* numels, int count,
+                       int src_dtype, int dst_dtype, void* stream);
+
+/* Sum of squares of x into out[0] (fp32).  `scratch` is caller-provided device memory of at
+ * least dlion_sumsq_scratch_bytes() bytes whose first 8 bytes are zero before the first use;
+ * the kernel leaves them zero again, so one zero-initialised buffer serves every later call
+ * on the same stream.  Used for local gradient-norm clipping (HF Trainer's max_grad_norm,
+ * which the reference inherits: SURVEY §3.1). */
+int64_t dlion_sumsq_scratch_bytes(void);
+int dlion_sumsq(const void* x, int64_t n, int dtype, void* scratch, float* out, void* stream);
+/* x *= min(1, max_norm / (sqrt(*sumsq) + 1e-6)) — torch.nn.utils.clip_grad_norm_'s coefficient */
+int dlion_clip_scale(void* x, int64_t n, int dtype, const float* sumsq, float max_norm, void* stream);
+
+/* ---------------------------------------------------------------- model kernels */
+
+/* N3 — y = LayerNorm(x + residual) (residual may be NULL); also writes the pre-norm sum to
+ * `sum_out` (may alias nothing or be NULL when residual is NULL) and saves mean/rstd (fp32,
+ * one per row).  RMSNorm when `bias == NULL && rms != 0`.
+ * reference: HF GPT2Block / LlamaDecoderLayer reached via async_trainer.py:24. */
+int dlion_norm_fwd(const void* x, const void* residual, const void* weight, const void* bias, void* y,
+                   void* sum_out, float* mean, float* rstd, int64_t rows, int cols, float eps, int rms,
+                   int dtype, void* stream);
+/* backward: dx (and d residual, identical) = norm-backward(dy) + dsum_in (may be NULL);
+ * dweight/dbias partials are accumulated in fp32 `dw_partial`/`db_partial` of shape
+ * [dlion_norm_bwd_partial_rows(), cols]; reduce with dlion_norm_bwd_finalize. */
+int dlion_norm_bwd_partial_rows(void);
+int dlion_norm_bwd(const void* dy, const void* dsum_in, const void* xsum, const void* weight,
+                   const float* mean, const float* rstd, void* dx, float* dw_partial, float* db_partial,
+                   int64_t rows, int cols, int rms, int dtype, void* stream);
+int dlion_norm_bwd_finalize(const float* dw_partial, const float* db_partial, void* dweight, void* dbias,
+                            int cols, int dtype, void* stream);
+
+/* N4 — rotary embedding applied in place to q [tokens, q_heads, head_dim] and k
+ * [tokens, k_heads, head_dim] (HF "rotate_half" pairing: i <-> i + head_dim/2); cos/sin are
+ * fp32 [seq, head_dim/2]; pos = token index % seq_len.  inverse != 0 applies the transpose
+ * rotation (the backward).  reference: HF LlamaAttention via sft_llama2.py:147. */
+int dlion_rope(void* q, void* k, const float* cos, const float* sin, int64_t tokens, int seq_len,
+               int q_heads, int k_heads, int head_dim, int64_t q_token_stride, int64_t k_token_stride,
+               int inverse, int dtype, void* stream);
+
+/* N5 — cross-entropy over one chunk of logits rows, in place: on return logits holds
+ * d loss / d logits * grad_scale (softmax - onehot, zero rows where label == ignore_index),
+ * loss[row] = -log softmax[label] (0 if ignored), logp optional same thing negated.
+ * reference: HF ForCausalLM loss in compute_loss (async_trainer.py:24); DPO log-probs in TRL. */
+int dlion_ce_fwd_bwd(void* logits, const int64_t* labels, float* loss, int64_t rows, int vocab,
+                     int64_t row_stride, int64_t ignore_index, float grad_scale, int write_grad, int dtype,
+                     void* stream);
+/* per-row backward scale variant used by DPO: logits <- (softmax - onehot) * row_scale[row] */
+int dlion_ce_bwd_rowscale(void* logits, const int64_t* labels, const float* row_scale, int64_t rows,
+                          int vocab, int64_t row_stride, int64_t ignore_index, int dtype, void* stream);
+
+#ifdef __cplusplus
+}
+#endif
+#endif /* DLION_H_ */

@@ -1,0 +1,159 @@
+"""API tier (single process, CPU): state_dict schema, param groups, closure, grad=None,
+external LambdaLR — against the reference optimizer loaded by path."""
+import copy
+
+import pytest
+import torch
+
+from distributed_lion import Lion
+
+
+def _model(seed=0, dtype=torch.float32):
+    torch.manual_seed(seed)
+    m = torch.nn.Sequential(torch.nn.Linear(13, 7), torch.nn.Tanh(), torch.nn.Linear(7, 3))
+    return m.to(dtype)
+
+
+def _same(a, b, dtype):
+    """fp32: bit-exact.  bf16 on CPU: ATen's vectorised loop rounds `alpha` to bf16 and its
+    scalar-tail loop does not (probed: 28 % of elements differ by one ulp between the two),
+    and flat buckets move elements between the two loops — so bf16-on-CPU is compared to one
+    bf16 ulp.  (On CUDA both go through one fp32 functor; the GPU tests compare exactly.)"""
+    if dtype == torch.float32:
+        return torch.equal(a, b)
+    return torch.allclose(a.float(), b.float(), rtol=2 ** -6, atol=3e-5)
+
+
+def _run(opt, model, steps=4, sched=None, seed=1):
+    torch.manual_seed(seed)
+    for _ in range(steps):
+        x = torch.randn(5, 13).to(next(model.parameters()).dtype)
+        loss = model(x).float().pow(2).mean()
+        opt.zero_grad()
+        loss.backward()
+        opt.step()
+        if sched is not None:
+            sched.step()
+
+
+@pytest.mark.parametrize("dtype", [torch.float32, torch.bfloat16])
+def test_local_matches_reference_bitexact(ref_mod, dtype):
+    m_ref, m_new = _model(0, dtype), _model(0, dtype)
+    o_ref = ref_mod.Lion(m_ref.parameters(), lr=1e-3, weight_decay=0.1)
+    o_new = Lion(m_new.parameters(), lr=1e-3, weight_decay=0.1)
+    s_ref = torch.optim.lr_scheduler.LambdaLR(o_ref, lambda s: 1.0 / (1 + s))
+    s_new = torch.optim.lr_scheduler.LambdaLR(o_new, lambda s: 1.0 / (1 + s))
+    _run(o_ref, m_ref, sched=s_ref)
+    _run(o_new, m_new, sched=s_new)
+    for a, b in zip(m_ref.parameters(), m_new.parameters()):
+        assert _same(a, b, dtype)
+    sd_ref, sd_new = o_ref.state_dict(), o_new.state_dict()
+    assert sd_ref["param_groups"][0].keys() == sd_new["param_groups"][0].keys()
+    assert sd_ref["state"].keys() == sd_new["state"].keys()
+    for k in sd_ref["state"]:
+        assert list(sd_new["state"][k].keys()) == ["exp_avg"]
+        assert _same(sd_ref["state"][k]["exp_avg"], sd_new["state"][k]["exp_avg"], dtype)
+        assert sd_new["state"][k]["exp_avg"].dtype == dtype
+
+
+def test_state_dict_roundtrip_with_reference(ref_mod):
+    m_ref, m_new = _model(2), _model(2)
+    o_ref = ref_mod.Lion(m_ref.parameters(), lr=1e-3, weight_decay=0.05)
+    _run(o_ref, m_ref, steps=2)
+    # a reference-produced optimizer.pt loads into ours ...
+    m_new.load_state_dict(m_ref.state_dict())
+    o_new = Lion(m_new.parameters(), lr=1e-3, weight_decay=0.05)
+    o_new.load_state_dict(copy.deepcopy(o_ref.state_dict()))
+    _run(o_ref, m_ref, steps=3, seed=7)
+    _run(o_new, m_new, steps=3, seed=7)
+    for a, b in zip(m_ref.parameters(), m_new.parameters()):
+        assert torch.equal(a, b)
+    # ... and ours loads into the reference
+    o_ref2 = ref_mod.Lion(m_ref.parameters(), lr=1e-3, weight_decay=0.05)
+    o_ref2.load_state_dict(o_new.state_dict())
+    # state_dict tensors are independent copies, not bucket views
+    sd = o_new.state_dict()
+    t = sd["state"][0]["exp_avg"]
+    assert t.untyped_storage().nbytes() == t.numel() * t.element_size()
+
+
+def test_load_after_steps_folds_into_bucket():
+    m1, m2 = _model(3), _model(3)
+    o1, o2 = Lion(m1.parameters(), lr=1e-3), Lion(m2.parameters(), lr=1e-3)
+    _run(o1, m1, steps=3)
+    _run(o2, m2, steps=1, seed=99)          # o2 already has buckets
+    m2.load_state_dict(m1.state_dict())
+    o2.load_state_dict(o1.state_dict())
+    _run(o1, m1, steps=2, seed=5)
+    _run(o2, m2, steps=2, seed=5)
+    for a, b in zip(m1.parameters(), m2.parameters()):
+        assert torch.equal(a, b)
+
+
+def test_param_groups_and_closure(ref_mod):
+    m_ref, m_new = _model(4), _model(4)
+
+    def groups(m):
+        return [{"params": [p for n, p in m.named_parameters() if n.endswith("weight")], "weight_decay": 0.1},
+                {"params": [p for n, p in m.named_parameters() if n.endswith("bias")], "weight_decay": 0.0,
+                 "lr": 5e-4, "betas": (0.95, 0.98)}]
+    o_ref = ref_mod.Lion(groups(m_ref), lr=1e-3)
+    o_new = Lion(groups(m_new), lr=1e-3)
+    x = torch.randn(4, 13)
+    for o, m in ((o_ref, m_ref), (o_new, m_new)):
+        def closure():
+            o.zero_grad()
+            l = m(x).pow(2).sum()
+            l.backward()
+            return l
+        out = o.step(closure)
+        assert out is not None and out.requires_grad is True or out is not None
+    for a, b in zip(m_ref.parameters(), m_new.parameters()):
+        assert torch.equal(a, b)
+    assert len(o_new.buckets) == 2
+
+
+def test_grad_none_params_are_skipped_locally(ref_mod):
+    m_ref, m_new = _model(5), _model(5)
+    o_ref = ref_mod.Lion(m_ref.parameters(), lr=1e-2, weight_decay=0.1)
+    o_new = Lion(m_new.parameters(), lr=1e-2, weight_decay=0.1)
+    for m, o in ((m_ref, o_ref), (m_new, o_new)):
+        torch.manual_seed(0)
+        for step in range(4):
+            o.zero_grad(set_to_none=True) if o is o_ref else o.zero_grad()
+            x = torch.randn(3, 13)
+            h = m[0](x)
+            loss = h.pow(2).mean() if step % 2 == 0 else m[2](torch.tanh(h)).pow(2).mean()
+            loss.backward()
+            if o is o_new and step % 2 == 0:
+                for p in m[2].parameters():
+                    p.grad = None       # emulate set_to_none semantics for unused params
+            o.step()
+    for a, b in zip(m_ref.parameters(), m_new.parameters()):
+        assert torch.equal(a, b)
+    assert len(o_ref.state_dict()["state"]) == len(o_new.state_dict()["state"])
+
+
+def test_params_alias_flat_bucket_and_flat_grads():
+    m = _model(6)
+    o = Lion(m.parameters(), lr=1e-3)
+    _run(o, m, steps=2)
+    b = o.buckets[0]
+    for p, pv, gv in zip(b.params, b.p_views, b.g_views):
+        assert p.data_ptr() == pv.data_ptr()
+        assert p.grad is not None and p.grad.data_ptr() == gv.data_ptr()
+    assert b.numel % 8192 == 0 and all(off % 128 == 0 for off in b.offsets)
+
+
+def test_constructor_validation():
+    p = [torch.nn.Parameter(torch.zeros(3))]
+    with pytest.raises(ValueError):
+        Lion(p, lr=0.0)
+    with pytest.raises(ValueError):
+        Lion(p, betas=(1.1, 0.9))
+    with pytest.raises(ValueError):
+        Lion(p, vote="median")
+    o = Lion(p)
+    assert o.defaults == {"lr": 1e-4, "betas": (0.9, 0.99), "weight_decay": 0.0} or \
+        {k: o.defaults[k] for k in ("lr", "betas", "weight_decay")} == {"lr": 1e-4, "betas": (0.9, 0.99), "weight_decay": 0.0}
+    assert o.backend_name == "local"
