@@ -1,0 +1,148 @@
+// cross_entropy.cu — N5: cross-entropy over a chunk of logits rows, forward + backward in place.
+//
+// The Python side (ops/cross_entropy.py) tiles the token dimension, so only one
+// [chunk, vocab] logits block exists at a time and the full [tokens, vocab] logits (and their
+// fp32 upcast) are never materialised.  For each row one CTA makes an online (max, sum-exp)
+// pass, then a second pass that overwrites the logits with (softmax - onehot) * scale — the
+// second pass re-reads the row from L2 (a row is <= 100 KB, 148 CTAs' rows fit in the 126 MB
+// L2 many times over).  Rows are 16-byte aligned because the caller pads the vocab stride.
+// reference: the HF ForCausalLM loss (shift, fp32 upcast of the full logits,
+// F.cross_entropy) inside compute_loss (async_trainer.py:24); TRL's log-prob gather for DPO.
+#include <math_constants.h>
+
+#include "common.cuh"
+
+namespace dlion {
+
+constexpr int kCEThreads = 512;
+
+struct MaxSum {
+  float m, s;
+};
+__device__ __forceinline__ MaxSum combine(MaxSum a, MaxSum b) {
+  const float m = fmaxf(a.m, b.m);
+  if (m == -CUDART_INF_F) return {m, 0.f};
+  return {m, a.s * __expf(a.m - m) + b.s * __expf(b.m - m)};
+}
+__device__ __forceinline__ MaxSum block_maxsum(MaxSum v, MaxSum* smem) {
+#pragma unroll
+  for (int o = 16; o > 0; o >>= 1) {
+    MaxSum other{__shfl_xor_sync(0xffffffffu, v.m, o), __shfl_xor_sync(0xffffffffu, v.s, o)};
+    v = combine(v, other);
+  }
+  const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
+  if (lane == 0) smem[warp] = v;
+  __syncthreads();
+  v = lane < (kCEThreads >> 5) ? smem[lane] : MaxSum{-CUDART_INF_F, 0.f};
+#pragma unroll
+  for (int o = 16; o > 0; o >>= 1) {
+    MaxSum other{__shfl_xor_sync(0xffffffffu, v.m, o), __shfl_xor_sync(0xffffffffu, v.s, o)};
+    v = combine(v, other);
+  }
+  return v;   // identical in every thread
+}
+
+// MODE 0: loss only.  MODE 1: loss + grad with a uniform scale.  MODE 2: grad with per-row scale.
+template <typename T, int MODE>
+__global__ void __launch_bounds__(kCEThreads) ce_kernel(T* __restrict__ logits, const int64_t* __restrict__ labels,
+                                                        float* __restrict__ loss, const float* __restrict__ row_scale,
+                                                        int64_t rows, int vocab, int64_t row_stride,
+                                                        int64_t ignore_index, float grad_scale) {
+  __shared__ MaxSum red[32];
+  const int nvec = vocab >> 3;
+  const int tail0 = nvec << 3;
+  const int padded = (int)row_stride;   // columns [vocab, row_stride) are padding: zero their grad
+  for (int64_t row = blockIdx.x; row < rows; row += gridDim.x) {
+    T* x = logits + row * row_stride;
+    const int64_t label = labels[row];
+    const bool ignored = label == ignore_index || label < 0 || label >= vocab;
+    float scale = grad_scale;
+    if (MODE == 2) scale = row_scale[row];
+    if (ignored) {
+      if (MODE != 2 && threadIdx.x == 0 && loss != nullptr) loss[row] = 0.f;
+      if (MODE != 0)
+        for (int j = threadIdx.x; j < (padded >> 3); j += kCEThreads)
+          *reinterpret_cast<uint4*>(x + j * 8) = make_uint4(0, 0, 0, 0);
+      continue;   // block-uniform branch
+    }
+    MaxSum acc{-CUDART_INF_F, 0.f};
+    for (int j = threadIdx.x; j < nvec; j += kCEThreads) {
+      float f[8];
+      load8<T>(x + j * 8, f);
+      float mx = f[0];
+#pragma unroll
+      for (int i = 1; i < 8; ++i) mx = fmaxf(mx, f[i]);
+      const float m = fmaxf(acc.m, mx);
+      float s = acc.s * __expf(acc.m - m);
+#pragma unroll
+      for (int i = 0; i < 8; ++i) s += __expf(f[i] - m);
+      acc = {m, s};
+    }
+    if (threadIdx.x < vocab - tail0) {
+      const float f = DT<T>::to_f(x[tail0 + threadIdx.x]);
+      acc = combine(acc, MaxSum{f, 1.f});
+    }
+    __syncthreads();   // red[] reuse across rows
+    const MaxSum tot = block_maxsum(acc, red);
+    const float lse = tot.m + logf(tot.s);
+    if (MODE != 2 && threadIdx.x == 0 && loss != nullptr) loss[row] = lse - DT<T>::to_f(x[label]);
+    if (MODE == 0) continue;
+    __syncthreads();   // everyone (incl. thread 0's x[label] read) is done with the raw logits
+    const float inv = 1.0f / tot.s;
+    for (int j = threadIdx.x; j < (padded >> 3); j += kCEThreads) {
+      float f[8];
+      load8<T>(x + j * 8, f);
+#pragma unroll
+      for (int i = 0; i < 8; ++i) {
+        const int col = j * 8 + i;
+        float p = col < vocab ? __expf(f[i] - tot.m) * inv : 0.f;
+        if (col == (int)label) p -= 1.f;
+        f[i] = p * scale;
+      }
+      store8<T>(x + j * 8, f);
+    }
+  }
+}
+
+template <int MODE>
+static int launch(void* logits, const int64_t* labels, float* loss, const float* row_scale, int64_t rows, int vocab,
+                  int64_t row_stride, int64_t ignore_index, float grad_scale, int dtype, cudaStream_t s) {
+  const int64_t cap = (int64_t)kNumSMs * 4;
+  const int grid = (int)(rows < cap ? rows : cap);
+  DISPATCH_DTYPE(dtype, ce_kernel<T, MODE><<<grid, kCEThreads, 0, s>>>((T*)logits, labels, loss, row_scale, rows, vocab,
+                                                                        row_stride, ignore_index, grad_scale));
+  return DLION_LAUNCH_CHECK("dlion_ce");
+}
+
+static int check_ce(const void* logits, const int64_t* labels, int64_t rows, int vocab, int64_t row_stride) {
+  DLION_CHECK_ARG(rows >= 0 && vocab > 0 && row_stride >= vocab, "dlion_ce: bad shape");
+  DLION_CHECK_ARG(row_stride % 8 == 0 && aligned16(logits), "dlion_ce: rows must be 16-byte aligned (pad the vocab stride to a multiple of 8)");
+  DLION_CHECK_ARG(labels != nullptr, "dlion_ce: labels required");
+  return 0;
+}
+
+}  // namespace dlion
+
+using namespace dlion;
+
+extern "C" int dlion_ce_fwd_bwd(void* logits, const int64_t* labels, float* loss, int64_t rows, int vocab,
+                                int64_t row_stride, int64_t ignore_index, float grad_scale, int write_grad, int dtype,
+                                void* stream) {
+  int rc = check_ce(logits, labels, rows, vocab, row_stride);
+  if (rc) return rc;
+  DLION_CHECK_ARG(loss != nullptr, "dlion_ce_fwd_bwd: loss output required");
+  if (rows == 0) return 0;
+  cudaStream_t s = (cudaStream_t)stream;
+  return write_grad ? launch<1>(logits, labels, loss, nullptr, rows, vocab, row_stride, ignore_index, grad_scale, dtype, s)
+                    : launch<0>(logits, labels, loss, nullptr, rows, vocab, row_stride, ignore_index, grad_scale, dtype, s);
+}
+
+extern "C" int dlion_ce_bwd_rowscale(void* logits, const int64_t* labels, const float* row_scale, int64_t rows,
+                                     int vocab, int64_t row_stride, int64_t ignore_index, int dtype, void* stream) {
+  int rc = check_ce(logits, labels, rows, vocab, row_stride);
+  if (rc) return rc;
+  DLION_CHECK_ARG(row_scale != nullptr, "dlion_ce_bwd_rowscale: row_scale required");
+  if (rows == 0) return 0;
+  return launch<2>(logits, labels, nullptr, row_scale, rows, vocab, row_stride, ignore_index, 0.f, dtype,
+                   (cudaStream_t)stream);
+}

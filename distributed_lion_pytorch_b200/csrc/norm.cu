@@ -1,0 +1,333 @@
+// norm.cu — N3: fused residual-add + LayerNorm / RMSNorm, forward and backward.
+//
+// One CTA owns one row at a time and keeps it in registers (VPT 16-byte vectors per thread),
+// so the forward reads x (+ residual) once and writes y (+ the new residual stream) once, and
+// the backward reads dy, the saved residual stream and the incoming residual gradient once
+// and writes dx once.  dweight / dbias are accumulated per CTA in registers across the rows
+// it visits and written as fp32 partial rows; a second tiny kernel folds the partials.
+//
+// reference: the HF GPT2Block (ln_1 / ln_2 around residual adds) and LlamaDecoderLayer
+// (input_layernorm / post_attention_layernorm) that the reference reaches through
+// Trainer.compute_loss (async_trainer.py:24,52,80) as separate add + layer_norm ATen kernels.
+#include "common.cuh"
+
+namespace dlion {
+
+constexpr int kNormBwdParts = kNumSMs * 4;
+
+template <int BLOCK>
+__device__ __forceinline__ float block_allreduce_sum(float v, float* smem) {
+#pragma unroll
+  for (int o = 16; o > 0; o >>= 1) v += __shfl_xor_sync(0xffffffffu, v, o);
+  if constexpr (BLOCK > 32) {
+    const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
+    __syncthreads();   // protect smem reuse across consecutive reductions
+    if (lane == 0) smem[warp] = v;
+    __syncthreads();
+    v = lane < (BLOCK >> 5) ? smem[lane] : 0.f;
+#pragma unroll
+    for (int o = 16; o > 0; o >>= 1) v += __shfl_xor_sync(0xffffffffu, v, o);
+  }
+  return v;
+}
+
+// Thread t owns vectors t, t+BLOCK, ... (VPT of them); vector j covers columns [8j, 8j+8).
+template <typename T, int VPT, int BLOCK, bool RMS>
+__global__ void __launch_bounds__(BLOCK) norm_fwd_kernel(const T* __restrict__ x, const T* __restrict__ res,
+                                                         const T* __restrict__ w, const T* __restrict__ b,
+                                                         T* __restrict__ y, T* __restrict__ sum_out,
+                                                         float* __restrict__ mean_out, float* __restrict__ rstd_out,
+                                                         int64_t rows, int cols, float eps) {
+  __shared__ float red[32];
+  const int nvec = cols >> 3;
+  float wv[VPT][8], bv[VPT][8];
+#pragma unroll
+  for (int k = 0; k < VPT; ++k) {
+    const int j = threadIdx.x + k * BLOCK;
+    if (j < nvec) {
+      load8<T>(w + j * 8, wv[k]);
+      if (!RMS && b != nullptr) load8<T>(b + j * 8, bv[k]);
+      else {
+#pragma unroll
+        for (int i = 0; i < 8; ++i) bv[k][i] = 0.f;
+      }
+    }
+  }
+  const float inv_cols = 1.0f / (float)cols;
+  for (int64_t row = blockIdx.x; row < rows; row += gridDim.x) {
+    const T* xr = x + row * cols;
+    float s[VPT][8];
+    float acc = 0.f;
+#pragma unroll
+    for (int k = 0; k < VPT; ++k) {
+      const int j = threadIdx.x + k * BLOCK;
+      if (j < nvec) {
+        load8<T>(xr + j * 8, s[k]);
+        if (res != nullptr) {
+          float r[8];
+          load8<T>(res + row * cols + j * 8, r);
+#pragma unroll
+          for (int i = 0; i < 8; ++i) s[k][i] = DT<T>::rnd(s[k][i] + r[i]);   // the residual stream lives in T
+        }
+        if (sum_out != nullptr) store8<T>(sum_out + row * cols + j * 8, s[k]);
+#pragma unroll
+        for (int i = 0; i < 8; ++i) acc += RMS ? s[k][i] * s[k][i] : s[k][i];
+      }
+    }
+    float mean = 0.f, rstd;
+    if (RMS) {
+      const float ss = block_allreduce_sum<BLOCK>(acc, red);
+      rstd = rsqrtf(ss * inv_cols + eps);
+    } else {
+      mean = block_allreduce_sum<BLOCK>(acc, red) * inv_cols;
+      float var = 0.f;
+#pragma unroll
+      for (int k = 0; k < VPT; ++k) {
+        const int j = threadIdx.x + k * BLOCK;
+        if (j < nvec) {
+#pragma unroll
+          for (int i = 0; i < 8; ++i) {
+            const float d = s[k][i] - mean;
+            var = fmaf(d, d, var);
+          }
+        }
+      }
+      var = block_allreduce_sum<BLOCK>(var, red) * inv_cols;
+      rstd = rsqrtf(var + eps);
+    }
+    if (threadIdx.x == 0) {
+      if (mean_out != nullptr) mean_out[row] = mean;
+      rstd_out[row] = rstd;
+    }
+#pragma unroll
+    for (int k = 0; k < VPT; ++k) {
+      const int j = threadIdx.x + k * BLOCK;
+      if (j < nvec) {
+        float o[8];
+#pragma unroll
+        for (int i = 0; i < 8; ++i) {
+          if (RMS) o[i] = wv[k][i] * DT<T>::rnd(s[k][i] * rstd);          // HF: weight * h.to(input_dtype)
+          else o[i] = fmaf((s[k][i] - mean) * rstd, wv[k][i], bv[k][i]);
+        }
+        store8<T>(y + row * cols + j * 8, o);
+      }
+    }
+  }
+}
+
+template <typename T, int VPT, int BLOCK, bool RMS>
+__global__ void __launch_bounds__(BLOCK) norm_bwd_kernel(const T* __restrict__ dy, const T* __restrict__ dsum_in,
+                                                         const T* __restrict__ xs, const T* __restrict__ w,
+                                                         const float* __restrict__ mean_in,
+                                                         const float* __restrict__ rstd_in, T* __restrict__ dx,
+                                                         float* __restrict__ dw_part, float* __restrict__ db_part,
+                                                         int64_t rows, int cols) {
+  __shared__ float red[32];
+  const int nvec = cols >> 3;
+  float wv[VPT][8], dwv[VPT][8], dbv[VPT][8];
+#pragma unroll
+  for (int k = 0; k < VPT; ++k) {
+    const int j = threadIdx.x + k * BLOCK;
+    if (j < nvec) load8<T>(w + j * 8, wv[k]);
+#pragma unroll
+    for (int i = 0; i < 8; ++i) dwv[k][i] = 0.f, dbv[k][i] = 0.f;
+  }
+  const float inv_cols = 1.0f / (float)cols;
+  for (int64_t row = blockIdx.x; row < rows; row += gridDim.x) {
+    const float mean = RMS ? 0.f : mean_in[row];
+    const float rstd = rstd_in[row];
+    float g[VPT][8], xh[VPT][8];
+    float sg = 0.f, sgx = 0.f;
+#pragma unroll
+    for (int k = 0; k < VPT; ++k) {
+      const int j = threadIdx.x + k * BLOCK;
+      if (j < nvec) {
+        float d[8], s[8];
+        load8<T>(dy + row * cols + j * 8, d);
+        load8<T>(xs + row * cols + j * 8, s);
+#pragma unroll
+        for (int i = 0; i < 8; ++i) {
+          xh[k][i] = (s[i] - mean) * rstd;
+          g[k][i] = d[i] * wv[k][i];
+          dwv[k][i] = fmaf(d[i], RMS ? DT<T>::rnd(xh[k][i]) : xh[k][i], dwv[k][i]);
+          dbv[k][i] += d[i];
+          sg += g[k][i];
+          sgx = fmaf(g[k][i], xh[k][i], sgx);
+        }
+      }
+    }
+    const float mg = RMS ? 0.f : block_allreduce_sum<BLOCK>(sg, red) * inv_cols;
+    const float mgx = block_allreduce_sum<BLOCK>(sgx, red) * inv_cols;
+#pragma unroll
+    for (int k = 0; k < VPT; ++k) {
+      const int j = threadIdx.x + k * BLOCK;
+      if (j < nvec) {
+        float o[8];
+#pragma unroll
+        for (int i = 0; i < 8; ++i) o[i] = rstd * (g[k][i] - mg - xh[k][i] * mgx);
+        if (dsum_in != nullptr) {
+          float r[8];
+          load8<T>(dsum_in + row * cols + j * 8, r);
+#pragma unroll
+          for (int i = 0; i < 8; ++i) o[i] += r[i];
+        }
+        store8<T>(dx + row * cols + j * 8, o);
+      }
+    }
+  }
+#pragma unroll
+  for (int k = 0; k < VPT; ++k) {
+    const int j = threadIdx.x + k * BLOCK;
+    if (j < nvec) {
+      float* dwp = dw_part + (int64_t)blockIdx.x * cols + j * 8;
+      reinterpret_cast<float4*>(dwp)[0] = make_float4(dwv[k][0], dwv[k][1], dwv[k][2], dwv[k][3]);
+      reinterpret_cast<float4*>(dwp)[1] = make_float4(dwv[k][4], dwv[k][5], dwv[k][6], dwv[k][7]);
+      if (!RMS && db_part != nullptr) {
+        float* dbp = db_part + (int64_t)blockIdx.x * cols + j * 8;
+        reinterpret_cast<float4*>(dbp)[0] = make_float4(dbv[k][0], dbv[k][1], dbv[k][2], dbv[k][3]);
+        reinterpret_cast<float4*>(dbp)[1] = make_float4(dbv[k][4], dbv[k][5], dbv[k][6], dbv[k][7]);
+      }
+    }
+  }
+}
+
+// partials [parts, cols] -> dweight/dbias (T).  blockDim (32, 8): 32 columns x 8 row slices.
+template <typename T>
+__global__ void norm_bwd_finalize_kernel(const float* __restrict__ dw_part, const float* __restrict__ db_part,
+                                         T* __restrict__ dw, T* __restrict__ db, int parts, int cols) {
+  __shared__ float sw[8][33], sb[8][33];
+  const int c = blockIdx.x * 32 + threadIdx.x;
+  float aw = 0.f, ab = 0.f;
+  if (c < cols)
+    for (int r = threadIdx.y; r < parts; r += 8) {
+      aw += dw_part[(int64_t)r * cols + c];
+      if (db_part != nullptr) ab += db_part[(int64_t)r * cols + c];
+    }
+  sw[threadIdx.y][threadIdx.x] = aw;
+  sb[threadIdx.y][threadIdx.x] = ab;
+  __syncthreads();
+  if (threadIdx.y == 0 && c < cols) {
+#pragma unroll
+    for (int r = 1; r < 8; ++r) aw += sw[r][threadIdx.x], ab += sb[r][threadIdx.x];
+    dw[c] = DT<T>::from_f(aw);
+    if (db != nullptr && db_part != nullptr) db[c] = DT<T>::from_f(ab);
+  }
+}
+
+template <typename T, int VPT, int BLOCK>
+static int launch_fwd(const void* x, const void* res, const void* w, const void* b, void* y, void* sum_out,
+                      float* mean, float* rstd, int64_t rows, int cols, float eps, int rms, cudaStream_t s) {
+  const int64_t cap = (int64_t)kNumSMs * (2048 / BLOCK);
+  const int grid = (int)(rows < cap ? rows : cap);
+  if (rms)
+    norm_fwd_kernel<T, VPT, BLOCK, true><<<grid, BLOCK, 0, s>>>((const T*)x, (const T*)res, (const T*)w, nullptr,
+                                                                (T*)y, (T*)sum_out, mean, rstd, rows, cols, eps);
+  else
+    norm_fwd_kernel<T, VPT, BLOCK, false><<<grid, BLOCK, 0, s>>>((const T*)x, (const T*)res, (const T*)w,
+                                                                 (const T*)b, (T*)y, (T*)sum_out, mean, rstd, rows,
+                                                                 cols, eps);
+  return DLION_LAUNCH_CHECK("dlion_norm_fwd");
+}
+
+template <typename T, int VPT, int BLOCK>
+static int launch_bwd(const void* dy, const void* dsum_in, const void* xs, const void* w, const float* mean,
+                      const float* rstd, void* dx, float* dwp, float* dbp, int64_t rows, int cols, int rms,
+                      cudaStream_t s) {
+  const int grid = (int)(rows < kNormBwdParts ? rows : kNormBwdParts);
+  if (rms)
+    norm_bwd_kernel<T, VPT, BLOCK, true><<<grid, BLOCK, 0, s>>>((const T*)dy, (const T*)dsum_in, (const T*)xs,
+                                                                (const T*)w, mean, rstd, (T*)dx, dwp, dbp, rows, cols);
+  else
+    norm_bwd_kernel<T, VPT, BLOCK, false><<<grid, BLOCK, 0, s>>>((const T*)dy, (const T*)dsum_in, (const T*)xs,
+                                                                 (const T*)w, mean, rstd, (T*)dx, dwp, dbp, rows,
+                                                                 cols);
+  return DLION_LAUNCH_CHECK("dlion_norm_bwd");
+}
+
+// choose (VPT, BLOCK) so that BLOCK * VPT * 8 >= cols with few idle threads
+#define NORM_SHAPE_DISPATCH(FN, ...)                                              \
+  do {                                                                            \
+    const int nvec = cols >> 3;                                                   \
+    if (nvec <= 32) return FN<T, 1, 32>(__VA_ARGS__);                             \
+    if (nvec <= 64) return FN<T, 1, 64>(__VA_ARGS__);                             \
+    if (nvec <= 96) return FN<T, 1, 96>(__VA_ARGS__);                             \
+    if (nvec <= 128) return FN<T, 1, 128>(__VA_ARGS__);                           \
+    if (nvec <= 256) return FN<T, 1, 256>(__VA_ARGS__);                           \
+    if (nvec <= 512) return FN<T, 2, 256>(__VA_ARGS__);                           \
+    if (nvec <= 1024) return FN<T, 4, 256>(__VA_ARGS__);                          \
+    ::dlion::set_error("norm: cols %d > 8192 unsupported", cols);                 \
+    return DLION_E_UNSUPPORTED;                                                   \
+  } while (0)
+
+template <typename T>
+static int fwd_t(const void* x, const void* res, const void* w, const void* b, void* y, void* sum_out, float* mean,
+                 float* rstd, int64_t rows, int cols, float eps, int rms, cudaStream_t s) {
+  NORM_SHAPE_DISPATCH(launch_fwd, x, res, w, b, y, sum_out, mean, rstd, rows, cols, eps, rms, s);
+}
+template <typename T>
+static int bwd_t(const void* dy, const void* dsum_in, const void* xs, const void* w, const float* mean,
+                 const float* rstd, void* dx, float* dwp, float* dbp, int64_t rows, int cols, int rms,
+                 cudaStream_t s) {
+  NORM_SHAPE_DISPATCH(launch_bwd, dy, dsum_in, xs, w, mean, rstd, dx, dwp, dbp, rows, cols, rms, s);
+}
+
+}  // namespace dlion
+
+using namespace dlion;
+
+extern "C" int dlion_norm_fwd(const void* x, const void* residual, const void* weight, const void* bias, void* y,
+                              void* sum_out, float* mean, float* rstd, int64_t rows, int cols, float eps, int rms,
+                              int dtype, void* stream) {
+  DLION_CHECK_ARG(rows >= 0 && cols > 0 && (cols & 7) == 0, "dlion_norm_fwd: cols (%d) must be a positive multiple of 8",
+                  cols);
+  DLION_CHECK_ARG(aligned16(x) && aligned16(y) && aligned16(weight) && aligned16(residual) && aligned16(sum_out) &&
+                      aligned16(bias),
+                  "dlion_norm_fwd: pointers must be 16-byte aligned");
+  DLION_CHECK_ARG(rstd != nullptr && (rms || mean != nullptr), "dlion_norm_fwd: mean/rstd outputs required");
+  if (rows == 0) return 0;
+  cudaStream_t s = (cudaStream_t)stream;
+  switch (dtype) {
+    case DLION_F32: return fwd_t<float>(x, residual, weight, bias, y, sum_out, mean, rstd, rows, cols, eps, rms, s);
+    case DLION_BF16:
+      return fwd_t<__nv_bfloat16>(x, residual, weight, bias, y, sum_out, mean, rstd, rows, cols, eps, rms, s);
+    case DLION_F16: return fwd_t<__half>(x, residual, weight, bias, y, sum_out, mean, rstd, rows, cols, eps, rms, s);
+  }
+  set_error("dlion_norm_fwd: unsupported dtype %d", dtype);
+  return DLION_E_UNSUPPORTED;
+}
+
+extern "C" int dlion_norm_bwd_partial_rows(void) { return kNormBwdParts; }
+
+extern "C" int dlion_norm_bwd(const void* dy, const void* dsum_in, const void* xsum, const void* weight,
+                              const float* mean, const float* rstd, void* dx, float* dw_partial, float* db_partial,
+                              int64_t rows, int cols, int rms, int dtype, void* stream) {
+  DLION_CHECK_ARG(rows >= 0 && cols > 0 && (cols & 7) == 0, "dlion_norm_bwd: cols (%d) must be a positive multiple of 8",
+                  cols);
+  DLION_CHECK_ARG(aligned16(dy) && aligned16(dsum_in) && aligned16(xsum) && aligned16(weight) && aligned16(dx) &&
+                      aligned16(dw_partial) && aligned16(db_partial),
+                  "dlion_norm_bwd: pointers must be 16-byte aligned");
+  if (rows == 0) return 0;
+  cudaStream_t s = (cudaStream_t)stream;
+  switch (dtype) {
+    case DLION_F32:
+      return bwd_t<float>(dy, dsum_in, xsum, weight, mean, rstd, dx, dw_partial, db_partial, rows, cols, rms, s);
+    case DLION_BF16:
+      return bwd_t<__nv_bfloat16>(dy, dsum_in, xsum, weight, mean, rstd, dx, dw_partial, db_partial, rows, cols, rms,
+                                  s);
+    case DLION_F16:
+      return bwd_t<__half>(dy, dsum_in, xsum, weight, mean, rstd, dx, dw_partial, db_partial, rows, cols, rms, s);
+  }
+  set_error("dlion_norm_bwd: unsupported dtype %d", dtype);
+  return DLION_E_UNSUPPORTED;
+}
+
+extern "C" int dlion_norm_bwd_finalize(const float* dw_partial, const float* db_partial, void* dweight, void* dbias,
+                                       int parts, int cols, int dtype, void* stream) {
+  DLION_CHECK_ARG(parts > 0 && cols > 0 && dw_partial && dweight, "dlion_norm_bwd_finalize: bad arguments");
+  cudaStream_t s = (cudaStream_t)stream;
+  const dim3 block(32, 8);
+  const int grid = (cols + 31) / 32;
+  DISPATCH_DTYPE(dtype, norm_bwd_finalize_kernel<T><<<grid, block, 0, s>>>(dw_partial, db_partial, (T*)dweight,
+                                                                             (T*)dbias, parts, cols));
+  return DLION_LAUNCH_CHECK("dlion_norm_bwd_finalize");
+}

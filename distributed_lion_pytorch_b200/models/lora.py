@@ -1,0 +1,92 @@
+"""Native LoRA adapters (stands in for PEFT, which is not installed on the box).
+
+reference: ``LoraConfig(r=8, lora_alpha=16, lora_dropout=0.05, target_modules=["q_proj",
+"v_proj"])`` in sft_llama2.py:44-51 and dpo_llama2.py:192-207, and
+``AutoPeftModelForCausalLM.merge_and_unload`` in sft_llama2.py:195-196.  Unlike the reference
+ the optimizer must be built AFTER ``apply_lora`` so it sees the adapter params.
+"""
+from __future__ import annotations
+
+import math
+from dataclasses import dataclass, field
+from typing import Dict, Iterable, List
+
+import torch
+import torch.nn as nn
+import torch.nn.functional as F
+
+
+@dataclass
+class LoraConfig:
+    r: int = 8
+    lora_alpha: int = 16
+    lora_dropout: float = 0.05
+    target_modules: List[str] = field(default_factory=lambda: ["q_proj", "v_proj"])
+    bias: str = "none"
+    task_type: str = "CAUSAL_LM"
+
+
+class LoRALinear(nn.Module):
+    def __init__(self, base: nn.Linear, r: int, alpha: int, dropout: float):
+        super().__init__()
+        self.base = base
+        self.r, self.scaling = r, alpha / r
+        self.lora_A = nn.Parameter(torch.empty(r, base.in_features, dtype=base.weight.dtype, device=base.weight.device))
+        self.lora_B = nn.Parameter(torch.zeros(base.out_features, r, dtype=base.weight.dtype, device=base.weight.device))
+        nn.init.kaiming_uniform_(self.lora_A, a=math.sqrt(5))
+        self.dropout = dropout
+        base.weight.requires_grad_(False)
+        if base.bias is not None:
+            base.bias.requires_grad_(False)
+
+    def forward(self, x):
+        y = self.base(x)
+        xd = F.dropout(x, self.dropout, self.training) if self.dropout > 0 else x
+        return y + (xd @ self.lora_A.t()) @ self.lora_B.t() * self.scaling
+
+    @torch.no_grad()
+    def merged(self) -> nn.Linear:
+        self.base.weight.add_((self.lora_B.float() @ self.lora_A.float() * self.scaling).to(self.base.weight.dtype))
+        self.base.weight.requires_grad_(True)
+        return self.base
+
+
+def apply_lora(model: nn.Module, cfg: LoraConfig) -> nn.Module:
+    """Freeze the base model and wrap every ``nn.Linear`` whose name ends with a target."""
+    for p in model.parameters():
+        p.requires_grad_(False)
+    hits = 0
+    for parent in list(model.modules()):
+        for name, child in list(parent.named_children()):
+            if isinstance(child, nn.Linear) and any(name == t or name.endswith(t) for t in cfg.target_modules):
+                setattr(parent, name, LoRALinear(child, cfg.r, cfg.lora_alpha, cfg.lora_dropout))
+                hits += 1
+    if hits == 0:
+        raise ValueError(f"no module matched target_modules={cfg.target_modules}")
+    model.peft_config = cfg
+    return model
+
+
+def merge_and_unload(model: nn.Module) -> nn.Module:
+    for parent in list(model.modules()):
+        for name, child in list(parent.named_children()):
+            if isinstance(child, LoRALinear):
+                setattr(parent, name, child.merged())
+    for p in model.parameters():
+        p.requires_grad_(True)
+    if hasattr(model, "peft_config"):
+        del model.peft_config
+    return model
+
+
+def lora_state_dict(model: nn.Module) -> Dict[str, torch.Tensor]:
+    return {k: v.detach().cpu().clone() for k, v in model.state_dict().items() if "lora_" in k}
+
+
+def print_trainable_parameters(model: nn.Module) -> str:
+    """reference: sft_llama2.py:78-90 (defined upstream, never called)."""
+    trainable = sum(p.numel() for p in model.parameters() if p.requires_grad)
+    total = sum(p.numel() for p in model.parameters())
+    msg = f"trainable params: {trainable} || all params: {total} || trainable%: {100 * trainable / max(total, 1):.4f}"
+    print(msg)
+    return msg

@@ -1,0 +1,198 @@
+"""N5 — chunked linear + cross-entropy: the [tokens, vocab] logits are never materialised.
+
+``linear_cross_entropy(h, weight, labels)`` == ``F.cross_entropy(h @ weight.T, labels)`` (mean
+over non-ignored tokens).  The token dimension is tiled; per tile: one cuBLAS GEMM makes a
+bf16 logits block, the CE kernel (csrc/cross_entropy.cu) turns it into per-row losses and, in
+place, into d loss / d logits; two more GEMMs fold that block into dh and dW straight away
+(the gradient is produced during the forward, as the loss is always the last node).
+
+``linear_log_probs(h, weight, labels)`` returns per-token log-probabilities (for DPO); its
+backward recomputes each logits block and applies the per-row upstream gradient in the kernel.
+
+reference: HF ``ForCausalLM`` loss inside ``compute_loss`` (async_trainer.py:24) — full logits
++ fp32 upcast + log_softmax; TRL's ``get_batch_logps`` for DPO.
+"""
+from __future__ import annotations
+
+import contextlib
+import os
+from typing import Optional
+
+import torch
+import torch.nn.functional as F
+
+from . import _cabi, require_library
+
+IGNORE_INDEX = -100
+_DEFAULT_CHUNK = 4096
+
+
+def _pad_rows(weight: torch.Tensor, mult: int = 64) -> torch.Tensor:
+    """[V, H] -> [Vp, H] with zero rows so every logits row is 16-byte aligned and the GEMMs
+    see friendly leading dimensions; ``wp[:V]`` is a contiguous prefix view."""
+    V = weight.shape[0]
+    Vp = (V + mult - 1) // mult * mult
+    if Vp == V:
+        return weight
+    wp = weight.new_zeros(Vp, weight.shape[1])
+    wp[:V].copy_(weight)
+    return wp
+
+
+_EMULATE = os.environ.get("DLION_EMULATE_KERNELS") == "1"   # CPU stand-ins, to test the autograd plumbing
+
+
+def _kernel_ok(h: torch.Tensor) -> bool:
+    if not h.is_cuda:
+        return _EMULATE
+    return require_library() and h.dtype in (torch.float32, torch.bfloat16, torch.float16)
+
+
+def _ce_kernel(logits, labels, losses, V: int, ignore_index: int, write_grad: bool, row_scale=None) -> None:
+    """logits [c, Vp] (modified in place when write_grad / row_scale), losses fp32 [c] or None."""
+    if logits.is_cuda:
+        L = _cabi.lib()
+        dt = _cabi.dtype_code(logits.dtype)
+        st = _cabi.stream_ptr(logits.device)
+        rows, Vp = logits.shape
+        if row_scale is None:
+            _cabi.check(L.dlion_ce_fwd_bwd(logits.data_ptr(), labels.data_ptr(), losses.data_ptr(), rows, V, Vp,
+                                           ignore_index, 1.0, int(write_grad), dt, st), "ce_fwd_bwd")
+        else:
+            _cabi.check(L.dlion_ce_bwd_rowscale(logits.data_ptr(), labels.data_ptr(), row_scale.data_ptr(), rows, V,
+                                                Vp, ignore_index, dt, st), "ce_bwd_rowscale")
+        return
+    # torch stand-in with the kernel's exact contract
+    x = logits[:, :V].float()
+    valid = (labels != ignore_index) & (labels >= 0) & (labels < V)
+    safe = labels.clamp(0, V - 1)
+    lse = torch.logsumexp(x, dim=-1)
+    if losses is not None:
+        losses.copy_(torch.where(valid, lse - x.gather(1, safe[:, None]).squeeze(1), torch.zeros_like(lse)))
+    if write_grad or row_scale is not None:
+        g = torch.softmax(x, dim=-1)
+        g.scatter_add_(1, safe[:, None], -torch.ones_like(lse)[:, None])
+        scale = valid.float() if row_scale is None else valid.float() * row_scale
+        logits.zero_()
+        logits[:, :V].copy_(g * scale[:, None])
+
+
+def _device_guard(t: torch.Tensor):
+    return torch.cuda.device(t.device) if t.is_cuda else contextlib.nullcontext()
+
+
+class _LinearCE(torch.autograd.Function):
+    @staticmethod
+    def forward(ctx, h, weight, labels, ignore_index: int, chunk: int):
+        N, H = h.shape
+        V = weight.shape[0]
+        wp = _pad_rows(weight)
+        Vp = wp.shape[0]
+        losses = torch.empty(N, dtype=torch.float32, device=h.device)
+        n_valid = (labels != ignore_index).sum().clamp_(min=1).to(torch.float32)
+        need_grad = ctx.needs_input_grad[0] or ctx.needs_input_grad[1]
+        dh = torch.empty_like(h) if need_grad else None
+        dwp = torch.zeros_like(wp) if need_grad else None
+        with _device_guard(h):
+            for s in range(0, N, chunk):
+                e = min(N, s + chunk)
+                hc = h[s:e]
+                logits = hc @ wp.t()                                   # [c, Vp]
+                _ce_kernel(logits, labels[s:e], losses[s:e], V, ignore_index, need_grad)
+                if need_grad:
+                    torch.mm(logits, wp, out=dh[s:e])                  # d h   (unscaled)
+                    dwp.addmm_(logits.t(), hc)                         # d W   (unscaled)
+        loss = losses.sum() / n_valid
+        if need_grad:
+            ctx.save_for_backward(dh, dwp, n_valid)
+            ctx.V = V
+        return loss
+
+    @staticmethod
+    def backward(ctx, grad_out):
+        dh, dwp, n_valid = ctx.saved_tensors
+        scale = (grad_out.float() / n_valid)
+        dh.mul_(scale.to(dh.dtype))
+        dw = dwp[:ctx.V]
+        dw.mul_(scale.to(dw.dtype))
+        return dh, dw, None, None, None
+
+
+class _LinearLogProbs(torch.autograd.Function):
+    @staticmethod
+    def forward(ctx, h, weight, labels, ignore_index: int, chunk: int):
+        N, H = h.shape
+        V = weight.shape[0]
+        wp = _pad_rows(weight)
+        Vp = wp.shape[0]
+        losses = torch.empty(N, dtype=torch.float32, device=h.device)
+        with _device_guard(h):
+            for s in range(0, N, chunk):
+                e = min(N, s + chunk)
+                logits = h[s:e] @ wp.t()
+                _ce_kernel(logits, labels[s:e], losses[s:e], V, ignore_index, False)
+        ctx.save_for_backward(h, weight, labels)
+        ctx.ignore_index, ctx.chunk = ignore_index, chunk
+        return -losses
+
+    @staticmethod
+    def backward(ctx, grad_logp):
+        h, weight, labels = ctx.saved_tensors
+        N, H = h.shape
+        V = weight.shape[0]
+        wp = _pad_rows(weight)
+        Vp = wp.shape[0]
+        dh = torch.empty_like(h)
+        dwp = torch.zeros_like(wp)
+        # logp = -ce  =>  d logits = (softmax - onehot) * (-grad_logp)
+        row_scale = (-grad_logp).float().contiguous()
+        with _device_guard(h):
+            for s in range(0, N, ctx.chunk):
+                e = min(N, s + ctx.chunk)
+                hc = h[s:e]
+                logits = hc @ wp.t()
+                _ce_kernel(logits, labels[s:e], None, V, ctx.ignore_index, False, row_scale=row_scale[s:e])
+                torch.mm(logits, wp, out=dh[s:e])
+                dwp.addmm_(logits.t(), hc)
+        return dh, dwp[:V], None, None, None
+
+
+def linear_cross_entropy(h: torch.Tensor, weight: torch.Tensor, labels: torch.Tensor,
+                         ignore_index: int = IGNORE_INDEX, chunk: Optional[int] = None) -> torch.Tensor:
+    """h: [N, H], weight: [V, H], labels: [N] int64 → scalar mean CE over non-ignored rows."""
+    if _kernel_ok(h):
+        return _LinearCE.apply(h.contiguous(), weight, labels.contiguous(), ignore_index, chunk or _DEFAULT_CHUNK)
+    # CPU / fallback: still chunked so memory stays bounded
+    chunk = chunk or _DEFAULT_CHUNK
+    total = h.new_zeros((), dtype=torch.float32)
+    for s in range(0, h.shape[0], chunk):
+        logits = (h[s:s + chunk] @ weight.t()).float()
+        total = total + F.cross_entropy(logits, labels[s:s + chunk], ignore_index=ignore_index, reduction="sum")
+    return total / (labels != ignore_index).sum().clamp(min=1)
+
+
+def linear_log_probs(h: torch.Tensor, weight: torch.Tensor, labels: torch.Tensor,
+                     ignore_index: int = IGNORE_INDEX, chunk: Optional[int] = None) -> torch.Tensor:
+    """Per-token log p(label) as fp32 [N]; ignored positions give 0."""
+    if _kernel_ok(h):
+        return _LinearLogProbs.apply(h.contiguous(), weight, labels.contiguous(), ignore_index,
+                                     chunk or _DEFAULT_CHUNK)
+    chunk = chunk or _DEFAULT_CHUNK
+    outs = []
+    for s in range(0, h.shape[0], chunk):
+        logits = (h[s:s + chunk] @ weight.t()).float()
+        outs.append(-F.cross_entropy(logits, labels[s:s + chunk], ignore_index=ignore_index, reduction="none"))
+    return torch.cat(outs)
+
+
+def cross_entropy_rows(logits: torch.Tensor, labels: torch.Tensor, ignore_index: int = IGNORE_INDEX) -> torch.Tensor:
+    """Per-row CE of an existing [rows, vocab] logits tensor (not modified); test/eval helper."""
+    if logits.is_cuda and _kernel_ok(logits) and logits.stride(-1) == 1 and logits.stride(0) % 8 == 0 and logits.data_ptr() % 16 == 0:
+        out = torch.empty(logits.shape[0], dtype=torch.float32, device=logits.device)
+        with torch.cuda.device(logits.device):
+            _cabi.check(_cabi.lib().dlion_ce_fwd_bwd(logits.data_ptr(), labels.contiguous().data_ptr(), out.data_ptr(),
+                                                     logits.shape[0], logits.shape[1], logits.stride(0), ignore_index,
+                                                     1.0, 0, _cabi.dtype_code(logits.dtype),
+                                                     _cabi.stream_ptr(logits.device)), "ce_fwd")
+        return out
+    return F.cross_entropy(logits.float(), labels, ignore_index=ignore_index, reduction="none")

@@ -1,0 +1,91 @@
+"""N3 — fused residual-add + LayerNorm / RMSNorm (forward and backward kernels).
+
+``add_layer_norm(x, residual, weight, bias, eps)`` returns ``(y, new_residual)`` where
+``new_residual = x + residual`` (``x`` itself when ``residual is None``) and
+``y = LayerNorm(new_residual)``; ``add_rms_norm`` is the Llama flavour.  On CUDA both passes
+run in ``csrc/norm.cu``; on CPU the same math runs as plain PyTorch so the models work
+under gloo.  reference: HF GPT2Block / LlamaDecoderLayer via async_trainer.py:24.
+"""
+from __future__ import annotations
+
+from typing import Optional, Tuple
+
+import torch
+
+from . import _cabi, require_library
+
+
+def _use_kernel(x: torch.Tensor) -> bool:
+    return x.is_cuda and require_library() and x.shape[-1] % 8 == 0 and x.shape[-1] <= 8192 \
+        and x.dtype in (torch.float32, torch.bfloat16, torch.float16)
+
+
+class _FusedNorm(torch.autograd.Function):
+    @staticmethod
+    def forward(ctx, x, residual, weight, bias, eps: float, rms: bool):
+        cols = x.shape[-1]
+        xc = x.contiguous()
+        rc = residual.contiguous() if residual is not None else None
+        rows = xc.numel() // cols
+        y = torch.empty_like(xc)
+        summed = torch.empty_like(xc) if rc is not None else xc
+        mean = torch.empty(rows, dtype=torch.float32, device=x.device) if not rms else None
+        rstd = torch.empty(rows, dtype=torch.float32, device=x.device)
+        with torch.cuda.device(x.device):
+            _cabi.check(_cabi.lib().dlion_norm_fwd(
+                xc.data_ptr(), _cabi.ptr(rc), weight.data_ptr(), _cabi.ptr(bias), y.data_ptr(),
+                summed.data_ptr() if rc is not None else None, _cabi.ptr(mean), rstd.data_ptr(), rows, cols,
+                float(eps), int(rms), _cabi.dtype_code(x.dtype), _cabi.stream_ptr(x.device)), "norm_fwd")
+        ctx.save_for_backward(summed, weight, mean, rstd)
+        ctx.rms, ctx.has_res, ctx.has_bias = rms, residual is not None, bias is not None
+        ctx.set_materialize_grads(False)      # an unused residual output costs nothing in backward
+        return y, summed
+
+    @staticmethod
+    def backward(ctx, dy, dsum):
+        summed, weight, mean, rstd = ctx.saved_tensors
+        cols = summed.shape[-1]
+        rows = summed.numel() // cols
+        if dy is None:      # only the residual stream was consumed downstream
+            dy = torch.zeros_like(summed)
+        dyc = dy.contiguous()
+        dsc = dsum.contiguous() if dsum is not None else None
+        L = _cabi.lib()
+        parts = min(rows, int(L.dlion_norm_bwd_partial_rows()))
+        dx = torch.empty_like(summed)
+        dwp = torch.empty(parts, cols, dtype=torch.float32, device=dy.device)
+        dbp = torch.empty(parts, cols, dtype=torch.float32, device=dy.device) if ctx.has_bias else None
+        dw = torch.empty_like(weight)
+        db = torch.empty_like(weight) if ctx.has_bias else None
+        with torch.cuda.device(dy.device):
+            st = _cabi.stream_ptr(dy.device)
+            _cabi.check(L.dlion_norm_bwd(dyc.data_ptr(), _cabi.ptr(dsc), summed.data_ptr(), weight.data_ptr(),
+                                         _cabi.ptr(mean), rstd.data_ptr(), dx.data_ptr(), dwp.data_ptr(),
+                                         _cabi.ptr(dbp), rows, cols, int(ctx.rms), _cabi.dtype_code(dy.dtype), st),
+                        "norm_bwd")
+            _cabi.check(L.dlion_norm_bwd_finalize(dwp.data_ptr(), _cabi.ptr(dbp), dw.data_ptr(), _cabi.ptr(db),
+                                                  parts, cols, _cabi.dtype_code(weight.dtype), st), "norm_bwd_finalize")
+        return dx, (dx if ctx.has_res else None), dw, db, None, None
+
+
+def _ref_norm(x, residual, weight, bias, eps, rms):
+    s = x if residual is None else x + residual
+    if rms:
+        h = s.float()
+        h = h * torch.rsqrt(h.pow(2).mean(-1, keepdim=True) + eps)
+        return weight * h.to(s.dtype), s
+    return torch.nn.functional.layer_norm(s, (s.shape[-1],), weight, bias, eps), s
+
+
+def add_layer_norm(x: torch.Tensor, residual: Optional[torch.Tensor], weight: torch.Tensor,
+                   bias: Optional[torch.Tensor], eps: float = 1e-5) -> Tuple[torch.Tensor, torch.Tensor]:
+    if _use_kernel(x):
+        return _FusedNorm.apply(x, residual, weight, bias, eps, False)
+    return _ref_norm(x, residual, weight, bias, eps, False)
+
+
+def add_rms_norm(x: torch.Tensor, residual: Optional[torch.Tensor], weight: torch.Tensor,
+                 eps: float = 1e-5) -> Tuple[torch.Tensor, torch.Tensor]:
+    if _use_kernel(x):
+        return _FusedNorm.apply(x, residual, weight, None, eps, True)
+    return _ref_norm(x, residual, weight, None, eps, True)

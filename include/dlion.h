@@ -150,13 +150,14 @@ int dlion_norm_fwd(const void* x, const void* residual, const void* weight, cons
                    int dtype, void* stream);
 /* backward: dx (and d residual, identical) = norm-backward(dy) + dsum_in (may be NULL);
  * dweight/dbias partials are accumulated in fp32 `dw_partial`/`db_partial` of shape
- * [dlion_norm_bwd_partial_rows(), cols]; reduce with dlion_norm_bwd_finalize. */
+ * [min(rows, dlion_norm_bwd_partial_rows()), cols] (one row per CTA launched); reduce them
+ * with dlion_norm_bwd_finalize(parts = that row count). */
 int dlion_norm_bwd_partial_rows(void);
 int dlion_norm_bwd(const void* dy, const void* dsum_in, const void* xsum, const void* weight,
                    const float* mean, const float* rstd, void* dx, float* dw_partial, float* db_partial,
                    int64_t rows, int cols, int rms, int dtype, void* stream);
 int dlion_norm_bwd_finalize(const float* dw_partial, const float* db_partial, void* dweight, void* dbias,
-                            int cols, int dtype, void* stream);
+                            int parts, int cols, int dtype, void* stream);
 
 /* N4 — rotary embedding applied in place to q [tokens, q_heads, head_dim] and k
  * [tokens, k_heads, head_dim] (HF "rotate_half" pairing: i <-> i + head_dim/2); cos/sin are

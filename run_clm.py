@@ -1,0 +1,216 @@
+#!/usr/bin/env python
+"""Causal-LM (GPT-2) pre-training entry point:  torchrun --nproc_per_node N -m run_clm ...
+
+Same contract as the reference's run_clm.py (reference: run_clm.py:247-653 and the launch
+recipe README.md:19-37): ModelArguments / DataTrainingArguments / AsyncTrainingArguments
+parsed from the CLI or a single .json file, last-checkpoint detection, dataset → tokenise →
+fixed blocks with labels = input_ids, ``--lion`` picks ``Lion`` + cosine schedule,
+``--async_grad`` picks ``AsyncTrainer``, train → save → evaluate → perplexity → metrics files.
+
+Differences that are deliberate: ``--synthetic_data`` (random tokens of the right shape: there
+is no network or dataset cache on the B200 box); ``--torch_dtype`` is honoured also with
+``--config_name``; the non-Lion branch honours ``--weight_decay`` (D13); no W&B key
+is baked in (D15); ``--async_grad`` works on a single process (D8).
+"""
+from __future__ import annotations
+
+import logging
+import math
+import os
+import sys
+from dataclasses import dataclass, field
+from typing import Optional
+
+import torch
+
+from async_trainer import AsyncTrainer
+from distributed_lion import Lion
+from distributed_lion_pytorch_b200.models import build_model, config_for
+from distributed_lion_pytorch_b200.train import (AsyncTrainingArguments, SyntheticTokenDataset, Trainer,
+                                                 default_data_collator, get_cosine_schedule_with_warmup,
+                                                 get_last_checkpoint, load_tokenizer, parse_cli, set_seed)
+from distributed_lion_pytorch_b200.train.data import BlockDataset, group_texts, text_file_dataset
+
+logger = logging.getLogger("run_clm")
+
+
+@dataclass
+class ModelArguments:
+    """reference: run_clm.py:88-166"""
+    model_name_or_path: Optional[str] = field(default=None, metadata={"help": "checkpoint dir or preset for weights"})
+    model_type: Optional[str] = field(default=None, metadata={"help": "gpt2 | llama when training from scratch"})
+    config_overrides: Optional[str] = field(default=None, metadata={"help": "e.g. n_embd=10,n_layer=2"})
+    config_name: Optional[str] = field(default=None, metadata={"help": "preset / config dir (random init)"})
+    tokenizer_name: Optional[str] = None
+    cache_dir: Optional[str] = None
+    use_fast_tokenizer: bool = True
+    model_revision: str = "main"
+    use_auth_token: bool = False
+    torch_dtype: Optional[str] = field(default=None, metadata={"help": "auto | bfloat16 | float16 | float32"})
+    low_cpu_mem_usage: bool = False
+
+    def __post_init__(self):
+        if self.config_overrides is not None and (self.config_name is not None or self.model_name_or_path is not None):
+            raise ValueError("--config_overrides can't be used in combination with --config_name or --model_name_or_path")
+
+
+@dataclass
+class DataTrainingArguments:
+    """reference: run_clm.py:169-244"""
+    dataset_name: Optional[str] = None
+    dataset_config_name: Optional[str] = None
+    train_file: Optional[str] = None
+    validation_file: Optional[str] = None
+    max_train_samples: Optional[int] = None
+    max_eval_samples: Optional[int] = None
+    streaming: bool = False
+    block_size: Optional[int] = None
+    overwrite_cache: bool = False
+    validation_split_percentage: int = 5
+    preprocessing_num_workers: Optional[int] = None
+    keep_linebreaks: bool = True
+
+    def validate(self, synthetic: bool):
+        if synthetic:
+            return
+        if self.dataset_name is None and self.train_file is None and self.validation_file is None:
+            raise ValueError("Need either a dataset name, a training/validation file, or --synthetic_data.")
+        for f in (self.train_file, self.validation_file):
+            if f is not None and f.split(".")[-1] not in ("csv", "json", "txt"):
+                raise ValueError("`train_file`/`validation_file` should be a csv, a json or a txt file.")
+
+
+def _hub_dataset(data_args, tokenizer, block_size):
+    """openwebtext & co. through ``datasets`` when it is reachable (it is not on the B200 box)."""
+    from datasets import load_dataset
+    raw = load_dataset(data_args.dataset_name, data_args.dataset_config_name, streaming=data_args.streaming)
+    if "validation" not in raw:
+        pct = data_args.validation_split_percentage
+        raw = {"validation": load_dataset(data_args.dataset_name, data_args.dataset_config_name, split=f"train[:{pct}%]"),
+               "train": load_dataset(data_args.dataset_name, data_args.dataset_config_name, split=f"train[{pct}%:]")}
+    col = "text" if "text" in raw["train"].column_names else raw["train"].column_names[0]
+    out = {}
+    for split in ("train", "validation"):
+        toks = (tokenizer(t)["input_ids"] for t in raw[split][col])
+        out[split] = BlockDataset(group_texts(toks, block_size))
+    return out["train"], out["validation"]
+
+
+def main(argv=None):
+    model_args, data_args, training_args = parse_cli((ModelArguments, DataTrainingArguments, AsyncTrainingArguments), argv)
+    data_args.validate(training_args.synthetic_data)
+
+    logging.basicConfig(format="%(asctime)s - %(levelname)s - %(name)s - %(message)s", datefmt="%m/%d/%Y %H:%M:%S",
+                        handlers=[logging.StreamHandler(sys.stdout)], level=training_args.get_process_log_level())
+    device = training_args.torch_device      # brings the process group up under torchrun (run_clm.py:284 upstream)
+    logger.warning("Process rank: %s, device: %s, world: %s, bf16: %s", training_args.process_index, device,
+                   training_args.world_size, training_args.bf16 or model_args.torch_dtype == "bfloat16")
+
+    last_checkpoint = None
+    if os.path.isdir(training_args.output_dir) and training_args.do_train and not training_args.overwrite_output_dir:
+        last_checkpoint = get_last_checkpoint(training_args.output_dir)
+        if last_checkpoint is None and len(os.listdir(training_args.output_dir)) > 0:
+            raise ValueError(f"Output directory ({training_args.output_dir}) already exists and is not empty. "
+                             "Use --overwrite_output_dir to overcome.")
+        if last_checkpoint is not None and training_args.resume_from_checkpoint is None:
+            logger.info("Checkpoint detected, resuming training at %s.", last_checkpoint)
+    set_seed(training_args.seed)
+
+    # ---- model (random init from a config, or weights from a local checkpoint directory)
+    dtype = None
+    if model_args.torch_dtype not in (None, "auto"):
+        dtype = getattr(torch, model_args.torch_dtype)
+    name = model_args.model_name_or_path or model_args.config_name or model_args.model_type or "gpt2"
+    model = build_model(name, dtype=dtype, device=device, pretrained=model_args.model_name_or_path is not None,
+                        config_overrides=model_args.config_overrides)
+    cfg = model.config
+    logger.info("model %s: %.1fM parameters, dtype %s", name, model.num_parameters() / 1e6,
+                next(model.parameters()).dtype)
+
+    # ---- data
+    max_pos = getattr(cfg, "n_positions", None) or getattr(cfg, "max_position_embeddings", 1024)
+    block_size = min(data_args.block_size or 1024, max_pos, 1024 if data_args.block_size is None else 1 << 30)
+    tokenizer = None
+    if training_args.synthetic_data:
+        n_train = data_args.max_train_samples or training_args.synthetic_samples
+        n_eval = data_args.max_eval_samples or max(training_args.per_device_eval_batch_size * training_args.world_size * 2, 8)
+        train_dataset = SyntheticTokenDataset(cfg.vocab_size, block_size, n_train, seed=training_args.seed)
+        eval_dataset = SyntheticTokenDataset(cfg.vocab_size, block_size, n_eval, seed=training_args.seed + 1)
+    else:
+        tokenizer = load_tokenizer(model_args.tokenizer_name or model_args.model_name_or_path)
+        if len(tokenizer) > cfg.vocab_size:
+            raise ValueError(f"tokenizer has {len(tokenizer)} tokens but the model embeds {cfg.vocab_size}")
+        if data_args.dataset_name is not None:
+            train_dataset, eval_dataset = _hub_dataset(data_args, tokenizer, block_size)
+        else:
+            train_dataset = text_file_dataset(data_args.train_file, tokenizer, block_size, data_args.keep_linebreaks) \
+                if data_args.train_file else None
+            eval_dataset = text_file_dataset(data_args.validation_file, tokenizer, block_size,
+                                             data_args.keep_linebreaks) if data_args.validation_file else None
+        if data_args.max_train_samples and train_dataset is not None:
+            train_dataset.blocks = train_dataset.blocks[: data_args.max_train_samples]
+        if data_args.max_eval_samples and eval_dataset is not None:
+            eval_dataset.blocks = eval_dataset.blocks[: data_args.max_eval_samples]
+
+    def preprocess_logits_for_metrics(logits, labels):
+        return logits.argmax(dim=-1)
+
+    def compute_metrics(eval_preds):
+        preds, labels = eval_preds
+        labels, preds = labels[:, 1:].reshape(-1), preds[:, :-1].reshape(-1)      # shift, as run_clm.py:571-576
+        return {"accuracy": float((preds == labels).mean())}
+
+    # ---- optimizer + schedule (reference: run_clm.py:580-585)
+    optimizers = (None, None)
+    if training_args.lion:
+        if training_args.max_steps <= 0:
+            per_epoch = len(train_dataset) // (training_args.per_device_train_batch_size * training_args.world_size
+                                               * training_args.gradient_accumulation_steps)
+            training_args.max_steps = max(int(training_args.num_train_epochs * per_epoch), 1)
+        vote = "majority" if training_args.lion_vote == "stochastic" else training_args.lion_vote
+        mgn = training_args.lion_max_grad_norm or (1.0 if training_args.lion_vote == "stochastic" else None)
+        comm = training_args.comm if training_args.comm in ("auto", "fused", "nccl_1bit", "local") else "auto"
+        optimizer = Lion(model.parameters(), lr=training_args.learning_rate, weight_decay=training_args.weight_decay,
+                         max_grad_norm=mgn, vote=vote, tie=training_args.lion_tie, comm=comm, seed=training_args.seed)
+        optimizers = (optimizer, get_cosine_schedule_with_warmup(optimizer, training_args.warmup_steps,
+                                                                 training_args.max_steps))
+    trainer_class = AsyncTrainer if training_args.async_grad else Trainer     # reference: run_clm.py:587
+    trainer = trainer_class(model=model, args=training_args,
+                            train_dataset=train_dataset if training_args.do_train else None,
+                            eval_dataset=eval_dataset if training_args.do_eval else None, tokenizer=tokenizer,
+                            data_collator=default_data_collator,
+                            compute_metrics=compute_metrics if training_args.do_eval else None,
+                            preprocess_logits_for_metrics=preprocess_logits_for_metrics if training_args.do_eval else None,
+                            optimizers=optimizers)
+
+    results = {}
+    if training_args.do_train:
+        checkpoint = training_args.resume_from_checkpoint or last_checkpoint
+        train_result = trainer.train(resume_from_checkpoint=checkpoint)
+        trainer.save_model()
+        metrics = train_result.metrics
+        metrics["train_samples"] = len(train_dataset)
+        trainer.log_metrics("train", metrics)
+        trainer.save_metrics("train", metrics)
+        trainer.save_state()
+        results.update(metrics)
+    if training_args.do_eval:
+        metrics = trainer.evaluate()
+        try:
+            metrics["perplexity"] = math.exp(metrics["eval_loss"])
+        except OverflowError:
+            metrics["perplexity"] = float("inf")
+        trainer.log_metrics("eval", metrics)
+        trainer.save_metrics("eval", metrics)
+        results.update(metrics)
+    trainer.create_model_card(finetuned_from=model_args.model_name_or_path, tasks="text-generation",
+                              dataset=data_args.dataset_name or ("synthetic" if training_args.synthetic_data else "files"))
+    return results
+
+
+def _mp_fn(index):
+    main()
+
+
+if __name__ == "__main__":
+    main()
