@@ -66,3 +66,52 @@ def vote_update(p: torch.Tensor, g: torch.Tensor, m: torch.Tensor, gathered: tor
                                                   row_bytes // 4, world, mask, p.numel(), _cabi.dtype_code(p.dtype),
                                                   lr_, decay, b2, omb2, _cabi.VOTE_CODES[(vote, tie)],
                                                   _cabi.stream_ptr(p.device)), "vote_update")
+
+
+# --------------------------------------------------------------------------- N1 fused step
+def fused_tile(dtype: torch.dtype) -> int:
+    return int(_cabi.lib().dlion_fused_tile(_cabi.dtype_code(dtype)))
+
+
+def fused_max_grid(dtype: torch.dtype, device=None) -> int:
+    import ctypes as C
+    out = C.c_int(0)
+    with torch.cuda.device(device):
+        _cabi.check(_cabi.lib().dlion_fused_max_grid(_cabi.dtype_code(dtype), C.byref(out)), "fused_max_grid")
+    return out.value
+
+
+def fused_step(p: torch.Tensor, g: torch.Tensor, m: torch.Tensor, *, world: int, rank: int, arena_ptrs, flag_ptrs,
+               arena_words: int, epoch: int, grid: int, lr: float, wd: float, beta1: float, beta2: float,
+               vote: str = "majority", tie: str = "neg", live_mask: Optional[int] = None,
+               wait_mask: Optional[int] = None, max_grad_norm: Optional[float] = None, seed: int = 0, step: int = 0,
+               elem_base: int = 0, emulate_ranks: int = 0, emu_stride: int = 0, status: Optional[torch.Tensor] = None,
+               spin_limit: int = 0, n: Optional[int] = None) -> None:
+    """Launch the fused sign-pack-exchange-vote-update kernel on ``n`` elements of p/g/m.
+
+    ``arena_ptrs[r]`` / ``flag_ptrs[r]`` are device addresses of rank r's receive arena and
+    progress flags as mapped into THIS process (``parallel.symm``).  With ``emulate_ranks=W``
+    the W ranks are CTA groups of one launch on one GPU working on p/g/m + v*emu_stride."""
+    a = _cabi.FusedArgs()
+    a.p, a.g, a.m = p.data_ptr(), g.data_ptr(), m.data_ptr()
+    a.n = int(p.numel() if n is None else n)
+    a.elem_base = int(elem_base)
+    a.dtype = _cabi.dtype_code(p.dtype)
+    a.world, a.rank = int(world), int(rank)
+    full = (1 << world) - 1
+    a.live_mask = full if live_mask is None else int(live_mask) & full
+    a.wait_mask = full if wait_mask is None else int(wait_mask) & full
+    a.lr, a.decay, a.beta1, a.omb1, a.beta2, a.omb2 = _scalars(lr, wd, beta1, beta2)
+    a.vote = _cabi.VOTE_CODES[(vote, tie)]
+    a.stoch_r = stoch_radius(beta1, max_grad_norm)
+    a.seed, a.step, a.epoch = int(seed) & (2 ** 64 - 1), int(step) & 0xffffffff, int(epoch)
+    for r in range(world):
+        a.arena[r] = int(arena_ptrs[r])
+        a.flags[r] = int(flag_ptrs[r])
+    a.arena_words, a.grid = int(arena_words), int(grid)
+    a.emulate_ranks, a.emu_stride = int(emulate_ranks), int(emu_stride)
+    a.status = status.data_ptr() if status is not None else None
+    a.spin_limit = int(spin_limit)
+    import ctypes as C
+    with torch.cuda.device(p.device):
+        _cabi.check(_cabi.lib().dlion_fused_step(C.byref(a), _cabi.stream_ptr(p.device)), "fused_step")

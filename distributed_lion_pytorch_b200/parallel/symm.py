@@ -1,0 +1,200 @@
+"""Symmetric receive arenas and progress flags for the fused Distributed-Lion kernel.
+
+Every rank owns one arena ``uint32[2 parities][W][arena_words]`` and one flag table
+``uint64[W][DLION_FUSED_MAX_CTAS]`` in its own HBM and holds *peer-mapped device pointers* to
+all other ranks' copies, so the kernel (csrc/lion_fused_sm100.cu) can store packed sign words
+and release progress counters straight into peer memory over NVLink / NVSwitch.
+
+Two ways to obtain the peer mappings, tried in this order (override with ``DLION_SYMM``):
+
+``symm``  ``torch.distributed._symmetric_memory`` (CUDA VMM + fabric/fd handles; also exposes an
+          NVLS multicast pointer where the fabric supports it);
+``ipc``   legacy CUDA IPC handles exchanged through ``all_gather_object`` — same-node only,
+          works wherever ``cudaIpcOpenMemHandle`` does.
+
+reference: the only exchange upstream is ``dist.all_gather(all_updates, uint8_tensor)``
+(distributed_lion.py:80-81), one blocking NCCL collective per parameter tensor.
+"""
+from __future__ import annotations
+
+import os
+import socket
+from typing import List, Optional
+
+import torch
+import torch.distributed as dist
+
+from ..ops import _cabi, lion_ops
+
+CHUNK_ELEMS = 1 << 28          # elements per fused launch (arena = 2*W*chunk/8 bytes: 512 MiB at W=8)
+_KEEPALIVE = []                # peer-mapped storages must outlive every kernel that targets them
+
+
+def _same_node(pg) -> bool:
+    W = dist.get_world_size(pg)
+    names = [None] * W
+    dist.all_gather_object(names, socket.gethostname(), group=pg)
+    return len(set(names)) == 1
+
+
+def fused_supported(pg=None) -> bool:
+    """True when every rank of ``pg`` sits on one NVLink domain we can peer-map."""
+    if not (dist.is_available() and dist.is_initialized() and torch.cuda.is_available()):
+        return False
+    W = dist.get_world_size(pg)
+    if W < 2 or W > _cabi.MAX_RANKS:
+        return False
+    if os.environ.get("DLION_DISABLE_FUSED") == "1":
+        return False
+    try:
+        return _same_node(pg) and torch.cuda.device_count() >= 1
+    except Exception:
+        return False
+
+
+class PeerBuffer:
+    """A zero-initialised device buffer of ``nbytes`` on every rank + the addresses of all ranks'
+    copies as seen from this process (``ptrs[r]``; ``ptrs[rank]`` is the local one)."""
+
+    def __init__(self, nbytes: int, device: torch.device, pg=None, how: Optional[str] = None):
+        self.pg, self.device, self.nbytes = pg, device, int(nbytes)
+        self.rank, self.world = dist.get_rank(pg), dist.get_world_size(pg)
+        how = how or os.environ.get("DLION_SYMM", "auto")
+        self.how = None
+        self.multicast_ptr = 0
+        errs = []
+        order = ("symm", "ipc") if how == "auto" else (how,)
+        for h in order:
+            try:
+                getattr(self, f"_alloc_{h}")()
+                self.how = h
+                break
+            except Exception as e:   # fall through to the next mechanism, keep the reason
+                errs.append(f"{h}: {type(e).__name__}: {e}")
+        if self.how is None:
+            raise RuntimeError("could not peer-map device memory: " + " | ".join(errs))
+        torch.cuda.synchronize(device)
+        dist.barrier(group=pg)
+
+    def _alloc_symm(self):
+        import torch.distributed._symmetric_memory as symm_mem
+        group = self.pg if self.pg is not None else dist.group.WORLD
+        name = group.group_name
+        try:
+            symm_mem.enable_symm_mem_for_group(name)
+        except Exception:
+            pass
+        t = symm_mem.empty(self.nbytes, dtype=torch.uint8, device=self.device)
+        hdl = symm_mem.rendezvous(t, group=name)
+        t.zero_()
+        self.local = t
+        self.ptrs = [int(x) for x in hdl.buffer_ptrs]
+        try:
+            self.multicast_ptr = int(hdl.multicast_ptr or 0)
+        except Exception:
+            self.multicast_ptr = 0
+        self._hdl = hdl
+
+    def _alloc_ipc(self):
+        t = torch.zeros(self.nbytes, dtype=torch.uint8, device=self.device)
+        torch.cuda.synchronize(self.device)
+        handle = t.untyped_storage()._share_cuda_()
+        handles = [None] * self.world
+        dist.all_gather_object(handles, (self.rank, handle, t.storage_offset()), group=self.pg)
+        ptrs = [0] * self.world
+        for r, h, off in handles:
+            if r == self.rank:
+                ptrs[r] = t.data_ptr()
+                continue
+            st = torch.UntypedStorage._new_shared_cuda(*h)
+            _KEEPALIVE.append(st)
+            ptrs[r] = st.data_ptr() + off
+        self.local, self.ptrs = t, ptrs
+
+
+class FusedExchange:
+    """Owns the arenas/flags of one process group and launches the fused step bucket by bucket."""
+
+    def __init__(self, pg, device: torch.device, chunk_elems: int = CHUNK_ELEMS):
+        self.pg, self.device = pg, device
+        self.rank, self.world = dist.get_rank(pg), dist.get_world_size(pg)
+        self.chunk_elems = int(os.environ.get("DLION_CHUNK_ELEMS", chunk_elems))
+        self.epoch = 0
+        self.arena: Optional[PeerBuffer] = None
+        self.arena_words = 0
+        self.flags = PeerBuffer(self.world * _cabi.FUSED_MAX_CTAS * 8, device, pg)
+        self.status = torch.zeros(4, dtype=torch.int32, device=device)
+        self._grid = {}
+
+    def _ensure_arena(self, need_elems: int) -> None:
+        words = min(need_elems, self.chunk_elems) // 32
+        if self.arena is not None and words <= self.arena_words:
+            return
+        # collective: every rank reaches this with the same bucket size
+        self.arena = PeerBuffer(2 * self.world * words * 4, self.device, self.pg, how=self.flags.how)
+        self.arena_words = words
+
+    def grid_for(self, dtype: torch.dtype) -> int:
+        g = self._grid.get(dtype)
+        if g is None:
+            mine = min(lion_ops.fused_max_grid(dtype, self.device), _cabi.FUSED_MAX_CTAS)
+            t = torch.tensor([mine], dtype=torch.int32, device=self.device)
+            dist.all_reduce(t, op=dist.ReduceOp.MIN, group=self.pg)      # identical grid on every rank
+            g = int(t.item())
+            self._grid[dtype] = g
+        return g
+
+    def step(self, b, lr, wd, beta1, beta2, *, vote, tie, live_mask, max_grad_norm, seed, step_index) -> None:
+        tile = lion_ops.fused_tile(b.dtype)
+        assert b.numel % tile == 0, "bucket length must be a multiple of the fused tile"
+        chunk = self.chunk_elems - self.chunk_elems % tile
+        self._ensure_arena(b.numel)
+        grid = self.grid_for(b.dtype)
+        for off in range(0, b.numel, chunk):
+            n = min(chunk, b.numel - off)
+            self.epoch += 1
+            lion_ops.fused_step(b.flat_p[off:off + n], b.flat_g[off:off + n], b.flat_m[off:off + n],
+                                world=self.world, rank=self.rank, arena_ptrs=self.arena.ptrs,
+                                flag_ptrs=self.flags.ptrs, arena_words=self.arena_words, epoch=self.epoch,
+                                grid=grid, lr=lr, wd=wd, beta1=beta1, beta2=beta2, vote=vote, tie=tie,
+                                live_mask=live_mask, max_grad_norm=max_grad_norm, seed=seed, step=step_index,
+                                elem_base=off, status=self.status)
+
+    def check_status(self) -> None:
+        """Host-side health check (synchronises): raises if a flag wait timed out in any launch."""
+        st = self.status.tolist()
+        if st[0] != 0:
+            what = {1: f"rank {st[2]}'s progress flag never arrived at CTA {st[1]}",
+                    2: f"internal pipeline wait expired in CTA {st[1]} (role {st[2]})"}.get(st[0], str(st))
+            raise RuntimeError(f"fused Distributed-Lion kernel reported a stalled exchange: {what}")
+
+
+class EmulatedExchange:
+    """All W ranks inside ONE cooperative launch on one GPU (CTA groups act as ranks) — the way
+    the multi-rank protocol is tested without W GPUs (never as W separate kernels: separate
+    launches that wait on each other are not guaranteed to co-run)."""
+
+    def __init__(self, world: int, n: int, dtype: torch.dtype, device, grid: Optional[int] = None):
+        self.world, self.n, self.dtype, self.device = world, n, dtype, torch.device(device)
+        self.arena_words = n // 32
+        self.arenas = [torch.zeros(2 * world * self.arena_words, dtype=torch.int32, device=device) for _ in range(world)]
+        self.flags = [torch.zeros(world * _cabi.FUSED_MAX_CTAS, dtype=torch.int64, device=device) for _ in range(world)]
+        self.status = torch.zeros(4, dtype=torch.int32, device=device)
+        self.epoch = 0
+        maxg = lion_ops.fused_max_grid(dtype, self.device)
+        self.grid = grid or max(maxg // world, 1)
+
+    def step(self, P: torch.Tensor, Gd: torch.Tensor, M: torch.Tensor, lr, wd, beta1, beta2, **kw) -> None:
+        """P/Gd/M: contiguous [W, n] stacks of the ranks' buckets."""
+        assert P.shape == (self.world, self.n) and P.is_contiguous()
+        self.epoch += 1
+        lion_ops.fused_step(P, Gd, M, n=self.n, world=self.world, rank=0,
+                            arena_ptrs=[a.data_ptr() for a in self.arenas],
+                            flag_ptrs=[f.data_ptr() for f in self.flags], arena_words=self.arena_words,
+                            epoch=self.epoch, grid=self.grid, lr=lr, wd=wd, beta1=beta1, beta2=beta2,
+                            emulate_ranks=self.world, emu_stride=self.n, status=self.status, **kw)
+
+    def check_status(self):
+        st = self.status.tolist()
+        if st[0] != 0:
+            raise RuntimeError(f"emulated fused step stalled: {st}")

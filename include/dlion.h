@@ -93,7 +93,8 @@ typedef struct {
   void* p;
   const void* g;
   void* m;
-  int64_t n;
+  int64_t n;           /* elements in this launch (multiple of dlion_fused_tile(dtype)) */
+  int64_t elem_base;   /* index of p[0] within its bucket: keeps the Philox stream chunk-invariant */
   int dtype;
   int world;
   int rank;

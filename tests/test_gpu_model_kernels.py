@@ -1,0 +1,149 @@
+"""GPU tier: N3 (add+LayerNorm/RMSNorm), N4 (RoPE), N5 (chunked cross-entropy) against
+plain PyTorch fp32 references, forward and backward, plus the models built on them."""
+import pytest
+import torch
+import torch.nn.functional as F
+
+pytestmark = pytest.mark.gpu
+
+
+def _tol(dtype):
+    return dict(rtol=2e-2, atol=2e-2) if dtype == torch.bfloat16 else dict(rtol=1e-4, atol=1e-4)
+
+
+@pytest.mark.parametrize("dtype", [torch.float32, torch.bfloat16])
+@pytest.mark.parametrize("cols", [64, 768, 1024, 4096, 8192])
+@pytest.mark.parametrize("rms", [False, True])
+@pytest.mark.parametrize("with_res", [True, False])
+def test_add_norm_fwd_bwd(dtype, cols, rms, with_res):
+    from distributed_lion_pytorch_b200.ops.norm import add_layer_norm, add_rms_norm
+    torch.manual_seed(cols)
+    rows = 1000 if cols <= 1024 else 301
+    x = torch.randn(rows, cols, device="cuda").to(dtype).requires_grad_()
+    r = torch.randn(rows, cols, device="cuda").to(dtype).requires_grad_() if with_res else None
+    w = (1 + 0.1 * torch.randn(cols, device="cuda")).to(dtype).requires_grad_()
+    b = (0.1 * torch.randn(cols, device="cuda")).to(dtype).requires_grad_() if not rms else None
+    eps = 1e-5
+    y, s = (add_rms_norm(x, r, w, eps) if rms else add_layer_norm(x, r, w, b, eps))
+    dy = torch.randn_like(y)
+    ds = torch.randn_like(y)
+    (y.float() * dy.float()).sum().add((s.float() * ds.float()).sum()).backward()
+    # fp32 reference of the same op
+    xf, wf = x.detach().float().requires_grad_(), w.detach().float().requires_grad_()
+    rf = r.detach().float().requires_grad_() if with_res else None
+    bf = b.detach().float().requires_grad_() if b is not None else None
+    sf = xf + rf if with_res else xf
+    if dtype == torch.bfloat16 and with_res:
+        sf = sf + (sf.detach().to(dtype).float() - sf.detach())       # the stream is stored in bf16
+    if rms:
+        yf = wf * (sf * torch.rsqrt(sf.pow(2).mean(-1, keepdim=True) + eps))
+    else:
+        yf = F.layer_norm(sf, (cols,), wf, bf, eps)
+    (yf * dy.float()).sum().add((sf * ds.float()).sum()).backward()
+    t = _tol(dtype)
+    assert torch.allclose(y.float(), yf, **t)
+    assert torch.allclose(s.float(), sf.detach(), **t)
+    assert torch.allclose(x.grad.float(), xf.grad, **t)
+    if with_res:
+        assert torch.allclose(r.grad.float(), rf.grad, **t)
+    wt = dict(rtol=3e-2, atol=0.3) if dtype == torch.bfloat16 else dict(rtol=1e-3, atol=1e-2)
+    assert torch.allclose(w.grad.float(), wf.grad, **wt)
+    if b is not None:
+        assert torch.allclose(b.grad.float(), bf.grad, **wt)
+
+
+@pytest.mark.parametrize("dtype", [torch.float32, torch.bfloat16])
+@pytest.mark.parametrize("hq,hk,d", [(4, 4, 64), (8, 2, 128)])
+def test_rope_fwd_bwd(dtype, hq, hk, d):
+    from distributed_lion_pytorch_b200.ops.rope import apply_rope, rope_tables, _rope_functional
+    torch.manual_seed(0)
+    B, S = 3, 37
+    cos, sin = rope_tables(64, d, device="cuda")
+    q0 = torch.randn(B, S, hq * d, device="cuda").to(dtype)
+    k0 = torch.randn(B, S, hk * d, device="cuda").to(dtype)
+    ql = q0.clone().requires_grad_()
+    kl = k0.clone().requires_grad_()
+    q, k = apply_rope(ql * 1.0, kl * 1.0, cos, sin, d)      # the op owns (and overwrites) its inputs
+    dq, dk = torch.randn_like(q), torch.randn_like(k)
+    ((q.float() * dq.float()).sum() + (k.float() * dk.float()).sum()).backward()
+    qf, kf = q0.float().requires_grad_(), k0.float().requires_grad_()
+    qr = _rope_functional(qf, cos, sin, S, d)
+    kr = _rope_functional(kf, cos, sin, S, d)
+    ((qr * dq.float()).sum() + (kr * dk.float()).sum()).backward()
+    t = _tol(dtype)
+    assert torch.allclose(q.float(), qr, **t) and torch.allclose(k.float(), kr, **t)
+    assert torch.allclose(ql.grad.float(), qf.grad, **t) and torch.allclose(kl.grad.float(), kf.grad, **t)
+
+
+@pytest.mark.parametrize("dtype", [torch.float32, torch.bfloat16])
+@pytest.mark.parametrize("V", [512, 50257, 32000])
+def test_linear_cross_entropy_fwd_bwd(dtype, V):
+    from distributed_lion_pytorch_b200.ops.cross_entropy import linear_cross_entropy, linear_log_probs
+    torch.manual_seed(V)
+    N, H = 700, 96
+    h = (torch.randn(N, H, device="cuda") * 0.5).to(dtype).requires_grad_()
+    w = (torch.randn(V, H, device="cuda") * 0.2).to(dtype).requires_grad_()
+    labels = torch.randint(0, V, (N,), device="cuda")
+    labels[::7] = -100
+    loss = linear_cross_entropy(h, w, labels, chunk=256)
+    (loss * 0.5).backward()
+    hf, wf = h.detach().float().requires_grad_(), w.detach().float().requires_grad_()
+    lf = F.cross_entropy(hf @ wf.t(), labels, ignore_index=-100)
+    (lf * 0.5).backward()
+    t = dict(rtol=3e-2, atol=3e-3) if dtype == torch.bfloat16 else dict(rtol=1e-4, atol=1e-5)
+    assert torch.allclose(loss.float(), lf, rtol=t["rtol"], atol=2e-2 if dtype == torch.bfloat16 else 1e-4)
+    assert torch.allclose(h.grad.float(), hf.grad, **t)
+    assert torch.allclose(w.grad.float(), wf.grad, **t)
+    # per-token log-probs (DPO building block) with a non-uniform upstream gradient
+    h2 = h.detach().clone().requires_grad_()
+    w2 = w.detach().clone().requires_grad_()
+    lp = linear_log_probs(h2, w2, labels, chunk=300)
+    coef = torch.randn(N, device="cuda")
+    (lp * coef).sum().backward()
+    hf2, wf2 = h.detach().float().requires_grad_(), w.detach().float().requires_grad_()
+    lpf = -F.cross_entropy(hf2 @ wf2.t(), labels, ignore_index=-100, reduction="none")
+    (lpf * coef).sum().backward()
+    assert torch.allclose(lp, lpf, rtol=t["rtol"], atol=5e-2 if dtype == torch.bfloat16 else 1e-4)
+    assert torch.allclose(h2.grad.float(), hf2.grad, rtol=5e-2, atol=2e-2 if dtype == torch.bfloat16 else 1e-4)
+    assert torch.allclose(w2.grad.float(), wf2.grad, rtol=5e-2, atol=5e-2 if dtype == torch.bfloat16 else 1e-4)
+
+
+@pytest.mark.parametrize("family", ["gpt2-tiny", "llama-tiny"])
+def test_model_gpu_matches_cpu_reference_math(family):
+    """The kernel-backed model on the GPU against the same weights run through the plain
+    PyTorch fallbacks on the CPU (fp32)."""
+    from distributed_lion_pytorch_b200.models import build_model
+    torch.manual_seed(0)
+    m_cpu = build_model(family)
+    m_cpu.eval()
+    m_gpu = build_model(family)
+    m_gpu.load_state_dict(m_cpu.state_dict())
+    m_gpu = m_gpu.cuda().eval()
+    ids = torch.randint(0, 512, (2, 48))
+    out_c = m_cpu(ids, labels=ids)
+    out_g = m_gpu(ids.cuda(), labels=ids.cuda())
+    assert abs(float(out_c.loss) - float(out_g.loss)) < 2e-3
+    out_c.loss.backward()
+    out_g.loss.backward()
+    for (n1, p1), (_, p2) in zip(m_cpu.named_parameters(), m_gpu.named_parameters()):
+        assert torch.allclose(p1.grad, p2.grad.cpu(), rtol=2e-2, atol=2e-4), n1
+
+
+def test_lion_optimizer_on_gpu_uses_kernels_and_matches_reference(ref_mod):
+    from distributed_lion import Lion
+    from distributed_lion_pytorch_b200 import ops
+    torch.manual_seed(0)
+    net_a = torch.nn.Sequential(torch.nn.Linear(64, 256), torch.nn.Tanh(), torch.nn.Linear(256, 10)).cuda()
+    net_b = torch.nn.Sequential(torch.nn.Linear(64, 256), torch.nn.Tanh(), torch.nn.Linear(256, 10)).cuda()
+    net_b.load_state_dict(net_a.state_dict())
+    oa = ref_mod.Lion(net_a.parameters(), lr=1e-3, weight_decay=0.1)
+    ob = Lion(net_b.parameters(), lr=1e-3, weight_decay=0.1)
+    x = torch.randn(32, 64, device="cuda")
+    for _ in range(5):
+        for net, o in ((net_a, oa), (net_b, ob)):
+            o.zero_grad()
+            net(x).pow(2).mean().backward()
+            o.step()
+    assert ops.library_loaded()
+    for pa, pb in zip(net_a.parameters(), net_b.parameters()):
+        assert torch.allclose(pa, pb, rtol=0, atol=1e-7)

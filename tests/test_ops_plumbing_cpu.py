@@ -1,0 +1,75 @@
+"""CPU tier: the autograd plumbing around the kernels (chunking, padded vocab, in-place RoPE,
+gradient-in-forward cross-entropy) with torch stand-ins that honour the kernels' contracts."""
+import pytest
+import torch
+import torch.nn.functional as F
+
+
+@pytest.fixture()
+def emulate(monkeypatch):
+    from distributed_lion_pytorch_b200.ops import cross_entropy, rope
+    monkeypatch.setattr(cross_entropy, "_EMULATE", True)
+    monkeypatch.setattr(rope, "_EMULATE", True)
+
+
+@pytest.mark.parametrize("V", [97, 512])
+def test_linear_cross_entropy_plumbing(emulate, V):
+    from distributed_lion_pytorch_b200.ops.cross_entropy import linear_cross_entropy, linear_log_probs
+    torch.manual_seed(0)
+    N, H = 50, 16
+    h = torch.randn(N, H, requires_grad=True)
+    w = torch.randn(V, H, requires_grad=True)
+    labels = torch.randint(0, V, (N,))
+    labels[::5] = -100
+    loss = linear_cross_entropy(h, w, labels, chunk=16)
+    (loss * 0.25).backward()
+    h2, w2 = h.detach().clone().requires_grad_(), w.detach().clone().requires_grad_()
+    ref = F.cross_entropy(h2 @ w2.t(), labels, ignore_index=-100)
+    (ref * 0.25).backward()
+    assert torch.allclose(loss, ref, atol=1e-5)
+    assert torch.allclose(h.grad, h2.grad, atol=1e-5) and torch.allclose(w.grad, w2.grad, atol=1e-5)
+    h3, w3 = h.detach().clone().requires_grad_(), w.detach().clone().requires_grad_()
+    coef = torch.randn(N)
+    (linear_log_probs(h3, w3, labels, chunk=16) * coef).sum().backward()
+    h4, w4 = h.detach().clone().requires_grad_(), w.detach().clone().requires_grad_()
+    (-F.cross_entropy(h4 @ w4.t(), labels, ignore_index=-100, reduction="none") * coef).sum().backward()
+    assert torch.allclose(h3.grad, h4.grad, atol=1e-5) and torch.allclose(w3.grad, w4.grad, atol=1e-5)
+
+
+def test_llama_with_inplace_rope_matches_functional(emulate, monkeypatch):
+    from distributed_lion_pytorch_b200.models import build_model
+    from distributed_lion_pytorch_b200.ops import cross_entropy, rope
+    torch.manual_seed(0)
+    m = build_model("llama-tiny")
+    ids = torch.randint(0, 512, (2, 24))
+    calls = {"n": 0}
+    orig = rope._Rope.apply
+
+    def spy(*a):
+        calls["n"] += 1
+        return orig(*a)
+    monkeypatch.setattr(rope._Rope, "apply", staticmethod(spy))
+    m(ids, labels=ids).loss.backward()
+    g1 = [p.grad.clone() for p in m.parameters()]
+    assert calls["n"] == m.config.num_hidden_layers          # the in-place autograd path really ran
+    monkeypatch.setattr(rope, "_EMULATE", False)
+    monkeypatch.setattr(cross_entropy, "_EMULATE", False)
+    m.zero_grad()
+    m(ids, labels=ids).loss.backward()
+    for a, p in zip(g1, m.parameters()):
+        assert torch.allclose(a, p.grad, atol=1e-5)
+
+
+def test_gpt2_tied_embedding_gets_both_gradients(emulate):
+    from distributed_lion_pytorch_b200.models import build_model
+    torch.manual_seed(0)
+    m = build_model("gpt2-tiny")
+    m.eval()
+    assert m.lm_head.weight is m.transformer.wte.weight
+    ids = torch.randint(0, 512, (2, 16))
+    m(ids, labels=ids).loss.backward()
+    g = m.transformer.wte.weight.grad.clone()
+    m.zero_grad()
+    out = m(ids, return_logits=True)
+    F.cross_entropy(out.logits[:, :-1].reshape(-1, 512), ids[:, 1:].reshape(-1)).backward()
+    assert torch.allclose(g, m.transformer.wte.weight.grad, atol=1e-5)
