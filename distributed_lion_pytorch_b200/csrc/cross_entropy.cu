@@ -60,9 +60,10 @@ __global__ void __launch_bounds__(kCEThreads) ce_kernel(T* __restrict__ logits, 
     if (MODE == 2) scale = row_scale[row];
     if (ignored) {
       if (MODE != 2 && threadIdx.x == 0 && loss != nullptr) loss[row] = 0.f;
-      if (MODE != 0)
-        for (int j = threadIdx.x; j < (padded >> 3); j += kCEThreads)
-          *reinterpret_cast<uint4*>(x + j * 8) = make_uint4(0, 0, 0, 0);
+      if (MODE != 0) {
+        const float zeros[8] = {0.f, 0.f, 0.f, 0.f, 0.f, 0.f, 0.f, 0.f};
+        for (int j = threadIdx.x; j < (padded >> 3); j += kCEThreads) store8<T>(x + j * 8, zeros);
+      }
       continue;   // block-uniform branch
     }
     MaxSum acc{-CUDART_INF_F, 0.f};

@@ -16,7 +16,7 @@ import torch
 import torch.nn.functional as F
 
 from ..models.lora import LoraConfig, apply_lora
-from .trainer import AsyncTrainer, Trainer
+from .trainer import NoSyncMixin, Trainer
 
 IGNORE = -100
 
@@ -127,7 +127,5 @@ class DPOTrainer(Trainer):
         return m
 
 
-class AsyncDPOTrainer(DPOTrainer):
+class AsyncDPOTrainer(NoSyncMixin, DPOTrainer):
     """reference: async_trainer.py:65-90"""
-    sync_gradients = False
-    training_step = AsyncTrainer.training_step

@@ -15,7 +15,7 @@ import torch
 from ..models.lora import LoraConfig, apply_lora
 from ..optim.lion import Lion
 from .data import ConstantLengthDataset
-from .trainer import AsyncTrainer, Trainer
+from .trainer import NoSyncMixin, Trainer
 
 logger = logging.getLogger("dlion.sft")
 
@@ -47,7 +47,5 @@ class SFTTrainer(Trainer):
         self.packing, self.max_seq_length = packing, max_seq_length
 
 
-class AsyncSFTTrainer(SFTTrainer):
+class AsyncSFTTrainer(NoSyncMixin, SFTTrainer):
     """reference: async_trainer.py:37-62"""
-    sync_gradients = False
-    training_step = AsyncTrainer.training_step

@@ -507,16 +507,23 @@ class Trainer:
             logger.info("resumed from %s at step %d", d, self.state.global_step)
 
 
-class AsyncTrainer(Trainer):
-    """Never synchronises gradients (reference: async_trainer.py:8-34).  Upstream this is a
-    ``with model.no_sync():`` around HF's training_step and therefore needs a DDP-wrapped
-    model (SURVEY D8: it crashes on one process); here there is no reducer to silence, so
-    the same class works for any world size, and a DDP-wrapped model is still honoured."""
+class NoSyncMixin:
+    """``training_step`` that never lets gradients cross ranks: if the model is DDP-wrapped the
+    reducer is silenced with ``no_sync`` (exactly the reference's body, async_trainer.py:15);
+    otherwise there is nothing to silence.  ``sync_gradients = False`` also switches off this
+    package's own flat all-reduce."""
     sync_gradients = False
 
     def training_step(self, model, inputs, num_items_in_batch=None) -> torch.Tensor:
         no_sync = getattr(model, "no_sync", None)
         if callable(no_sync):
             with no_sync():
-                return super().training_step(model, inputs, num_items_in_batch)
-        return super().training_step(model, inputs, num_items_in_batch)
+                return Trainer.training_step(self, model, inputs, num_items_in_batch)
+        return Trainer.training_step(self, model, inputs, num_items_in_batch)
+
+
+class AsyncTrainer(NoSyncMixin, Trainer):
+    """Never synchronises gradients (reference: async_trainer.py:8-34).  Upstream this is a
+    ``with model.no_sync():`` around HF's training_step and therefore needs a DDP-wrapped
+    model (SURVEY D8: it crashes on one process); here there is no reducer to silence, so
+    the same class works for any world size, and a DDP-wrapped model is still honoured."""

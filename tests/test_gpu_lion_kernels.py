@@ -100,9 +100,6 @@ def test_vote_update_matches_reference(dtype, W, vote, tie, mask):
     lion_ops.vote_update(p, g, m, gathered, W, mask, HP["lr"], HP["wd"], HP["beta2"], vote, tie)
     _close(p, rp, dtype, "p")
     _close(m, rm, dtype, "m")
-    if vote == "majority" and tie == "neg":
-        step = (rp.double() - gpuref.rnd(p.double(), dtype)).abs()
-        assert step.max() > 0
 
 
 def test_stochastic_pack_statistics_and_determinism():
