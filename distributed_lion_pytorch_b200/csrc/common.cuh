@@ -124,22 +124,86 @@ __device__ __forceinline__ void store8<__half>(__half* __restrict__ ptr, const f
   *reinterpret_cast<uint4*>(ptr) = make_uint4(w[0], w[1], w[2], w[3]);
 }
 
-// ------------------------------------------------------------------ Lion math (one element)
-// blend: c = round(round(m*b1) + (1-b1)*g)   (reference: distributed_lion.py:54,68 —
-// exp_avg.clone().mul_(beta1).add(grad, alpha=1-beta1); ATen's add kernel is one fma in fp32)
+// ------------------------------------------------------------------ rounding through the storage type
+// round8: v[i] <- float(T(v[i])).  Packed converts (F2FP.*.PACK_AB, two values per ALU-pipe
+// instruction) instead of eight scalar F2F on the slow conversion pipe: with six roundings per
+// element the scalar form made the optimizer kernels conversion-bound (ncu: stall_mio on F2F).
+template <typename T>
+__device__ __forceinline__ void round8(float (&v)[8]);
+template <>
+__device__ __forceinline__ void round8<float>(float (&)[8]) {}
+template <>
+__device__ __forceinline__ void round8<__nv_bfloat16>(float (&v)[8]) {
+#pragma unroll
+  for (int i = 0; i < 4; ++i) {
+    const __nv_bfloat162 h = __floats2bfloat162_rn(v[2 * i], v[2 * i + 1]);
+    const uint32_t w = *reinterpret_cast<const uint32_t*>(&h);
+    v[2 * i] = __uint_as_float(w << 16);
+    v[2 * i + 1] = __uint_as_float(w & 0xffff0000u);
+  }
+}
+template <>
+__device__ __forceinline__ void round8<__half>(float (&v)[8]) {
+#pragma unroll
+  for (int i = 0; i < 4; ++i) {
+    const float2 f = __half22float2(__floats2half2_rn(v[2 * i], v[2 * i + 1]));
+    v[2 * i] = f.x;
+    v[2 * i + 1] = f.y;
+  }
+}
+// smallest |x| whose rounding to T is non-zero is just above this: round(x) > 0  <=>  x > tie_to_zero
+template <typename T> __device__ __forceinline__ float tie_to_zero();
+template <> __device__ __forceinline__ float tie_to_zero<float>() { return 0.f; }
+template <> __device__ __forceinline__ float tie_to_zero<__nv_bfloat16>() { return 0x1p-134f; }   // half of 2^-133
+template <> __device__ __forceinline__ float tie_to_zero<__half>() { return 0x1p-25f; }           // half of 2^-24
+
+// ------------------------------------------------------------------ Lion math (8 elements)
+// The reference rounds through the parameter dtype after every ATen op.  Three of those six
+// roundings are made by the store (store8 rounds to nearest even exactly like rnd) or only feed
+// a sign test (round(c) > 0 <=> c > tie_to_zero), so only m*b1, m*b2 and p*decay are rounded
+// explicitly; the results are bit-identical to the op-by-op sequence.
+//
+// blend: c = round(m*b1) + (1-b1)*g   (reference: distributed_lion.py:54,68 —
+// exp_avg.clone().mul_(beta1).add(grad, alpha=1-beta1); ATen's add kernel is one fp32 fma)
+template <typename T>
+__device__ __forceinline__ void blend8(const float (&m)[8], const float (&g)[8], float beta1, float omb1,
+                                       float (&c)[8]) {
+#pragma unroll
+  for (int i = 0; i < 8; ++i) c[i] = m[i] * beta1;
+  round8<T>(c);
+#pragma unroll
+  for (int i = 0; i < 8; ++i) c[i] = fmaf(omb1, g[i], c[i]);
+}
+// momentum: m' = round(m*b2) + (1-b2)*g, rounded by the store   (reference: distributed_lion.py:59,96)
+template <typename T>
+__device__ __forceinline__ void momentum8(float (&m)[8], const float (&g)[8], float beta2, float omb2) {
+#pragma unroll
+  for (int i = 0; i < 8; ++i) m[i] *= beta2;
+  round8<T>(m);
+#pragma unroll
+  for (int i = 0; i < 8; ++i) m[i] = fmaf(omb2, g[i], m[i]);
+}
+// parameter: p' = round(p*decay) - lr*u, rounded by the store   (reference: distributed_lion.py:51,55,64,92)
+template <typename T>
+__device__ __forceinline__ void apply8(float (&p)[8], const float (&u)[8], float lr, float decay) {
+#pragma unroll
+  for (int i = 0; i < 8; ++i) p[i] *= decay;
+  round8<T>(p);
+#pragma unroll
+  for (int i = 0; i < 8; ++i) p[i] = fmaf(-lr, u[i], p[i]);
+}
+// scalar forms for ragged tails
 template <typename T>
 __device__ __forceinline__ float lion_blend(float m, float g, float beta1, float omb1) {
-  return DT<T>::rnd(fmaf(omb1, g, DT<T>::rnd(m * beta1)));
+  return fmaf(omb1, g, DT<T>::rnd(m * beta1));
 }
-// momentum: m' = round(round(m*b2) + (1-b2)*g)   (reference: distributed_lion.py:59,96)
 template <typename T>
 __device__ __forceinline__ float lion_momentum(float m, float g, float beta2, float omb2) {
-  return DT<T>::rnd(fmaf(omb2, g, DT<T>::rnd(m * beta2)));
+  return fmaf(omb2, g, DT<T>::rnd(m * beta2));
 }
-// parameter: p' = round(round(p*decay) - lr*u)    (reference: distributed_lion.py:51,55,64,92)
 template <typename T>
 __device__ __forceinline__ float lion_apply(float p, float u, float lr, float decay) {
-  return DT<T>::rnd(fmaf(-lr, u, DT<T>::rnd(p * decay)));
+  return fmaf(-lr, u, DT<T>::rnd(p * decay));
 }
 
 // ------------------------------------------------------------------ Philox4x32-10
@@ -166,6 +230,8 @@ template <typename T>
 __device__ __forceinline__ uint32_t sign_byte(const float (&m)[8], const float (&g)[8], float beta1, float omb1,
                                               float stoch_r, uint64_t seed, uint32_t step, uint32_t rank,
                                               int64_t e0) {
+  float c[8];
+  blend8<T>(m, g, beta1, omb1, c);
   uint32_t byte = 0;
   if (stoch_r > 0.f) {
     const uint4 r0 = Philox::gen(seed, (uint64_t)e0, step, rank);
@@ -173,14 +239,11 @@ __device__ __forceinline__ uint32_t sign_byte(const float (&m)[8], const float (
     const uint32_t rr[8] = {r0.x, r0.y, r0.z, r0.w, r1.x, r1.y, r1.z, r1.w};
     const float inv = 1.0f / (2.0f * stoch_r);
 #pragma unroll
-    for (int i = 0; i < 8; ++i) {
-      const float c = lion_blend<T>(m[i], g[i], beta1, omb1);
-      const float prob = (c + stoch_r) * inv;
-      byte |= (Philox::u01(rr[i]) < prob ? 1u : 0u) << i;
-    }
+    for (int i = 0; i < 8; ++i) byte |= (Philox::u01(rr[i]) < (c[i] + stoch_r) * inv ? 1u : 0u) << i;
   } else {
+    const float thr = tie_to_zero<T>();
 #pragma unroll
-    for (int i = 0; i < 8; ++i) byte |= (lion_blend<T>(m[i], g[i], beta1, omb1) > 0.f ? 1u : 0u) << i;
+    for (int i = 0; i < 8; ++i) byte |= (c[i] > thr ? 1u : 0u) << i;
   }
   return byte;
 }

@@ -29,13 +29,13 @@ __global__ void __launch_bounds__(kThreads) lion_local_kernel(T* __restrict__ p,
     load8<T>(g + v * 8, gf);
     load8<T>(m + v * 8, mf);
     load8<T>(p + v * 8, pf);
+    float c[8], u[8];
+    blend8<T>(mf, gf, beta1, omb1, c);
+    const float thr = tie_to_zero<T>();
 #pragma unroll
-    for (int i = 0; i < 8; ++i) {
-      const float c = lion_blend<T>(mf[i], gf[i], beta1, omb1);
-      const float u = c > 0.f ? 1.f : (c < 0.f ? -1.f : 0.f);   // torch.sign: sign(0) = 0
-      pf[i] = lion_apply<T>(pf[i], u, lr, decay);
-      mf[i] = lion_momentum<T>(mf[i], gf[i], beta2, omb2);
-    }
+    for (int i = 0; i < 8; ++i) u[i] = c[i] > thr ? 1.f : (c[i] < -thr ? -1.f : 0.f);   // torch.sign: sign(0) = 0
+    apply8<T>(pf, u, lr, decay);
+    momentum8<T>(mf, gf, beta2, omb2);
     store8<T>(p + v * 8, pf);
     store8<T>(m + v * 8, mf);
   }
@@ -43,7 +43,7 @@ __global__ void __launch_bounds__(kThreads) lion_local_kernel(T* __restrict__ p,
   if (blockIdx.x == 0 && threadIdx.x == 0) {
     for (int64_t e = nvec << 3; e < n; ++e) {
       const float gf = DT<T>::to_f(g[e]), mf = DT<T>::to_f(m[e]), pf = DT<T>::to_f(p[e]);
-      const float c = lion_blend<T>(mf, gf, beta1, omb1);
+      const float c = DT<T>::rnd(lion_blend<T>(mf, gf, beta1, omb1));
       const float u = c > 0.f ? 1.f : (c < 0.f ? -1.f : 0.f);
       p[e] = DT<T>::from_f(lion_apply<T>(pf, u, lr, decay));
       m[e] = DT<T>::from_f(lion_momentum<T>(mf, gf, beta2, omb2));
@@ -127,14 +127,35 @@ __global__ void __launch_bounds__(kThreads) vote_update_kernel(T* __restrict__ p
         pf[i] = ok ? DT<T>::to_f(p[e0 + i]) : 0.f;
       }
     }
+    float uf[8];
+    if (vote == DLION_VOTE_AVERAGE) {
 #pragma unroll
-    for (int i = 0; i < 8; ++i) {
-      const int cnt = ((c0 >> i) & 1) | (((c1 >> i) & 1) << 1) | (((c2 >> i) & 1) << 2) | (((c3 >> i) & 1) << 3) |
-                      (((c4 >> i) & 1) << 4);
-      const float u = vote_dir(cnt, L, 0.f, vote);
-      pf[i] = lion_apply<T>(pf[i], u, lr, decay);
-      mf[i] = lion_momentum<T>(mf[i], gf[i], beta2, omb2);
+      for (int i = 0; i < 8; ++i) {
+        const int cnt = ((c0 >> i) & 1) | (((c1 >> i) & 1) << 1) | (((c2 >> i) & 1) << 2) | (((c3 >> i) & 1) << 3) |
+                        (((c4 >> i) & 1) << 4);
+        uf[i] = vote_dir(cnt, L, 0.f, vote);
+      }
+    } else {
+      // bit-sliced comparison of the 8 counts with the (uniform) thresholds: one byte of
+      // "majority" bits and one of "tie" bits instead of 8 reassembled integers
+      const uint32_t pc[5] = {c0, c1, c2, c3, c4};
+      const int thr = L / 2 + 1;
+      uint32_t gt = 0u, eq = 0xffu, tz = 0xffu;
+#pragma unroll
+      for (int k = 4; k >= 0; --k) {
+        const uint32_t kb = ((thr >> k) & 1) ? 0xffu : 0u;
+        const uint32_t hb = (((L / 2) >> k) & 1) ? 0xffu : 0u;
+        gt |= eq & pc[k] & ~kb;
+        eq &= ~(pc[k] ^ kb);
+        tz &= ~(pc[k] ^ hb);
+      }
+      const uint32_t maj = (gt | eq) & 0xffu;
+      const uint32_t tie = (vote == DLION_VOTE_MAJORITY_ZERO && (L & 1) == 0) ? (tz & 0xffu) : 0u;
+#pragma unroll
+      for (int i = 0; i < 8; ++i) uf[i] = ((tie >> i) & 1u) ? 0.f : (((maj >> i) & 1u) ? 1.f : -1.f);
     }
+    apply8<T>(pf, uf, lr, decay);
+    momentum8<T>(mf, gf, beta2, omb2);
     if (full) {
       store8<T>(p + e0, pf);
       store8<T>(m + e0, mf);

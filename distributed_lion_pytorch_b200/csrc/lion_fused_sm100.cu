@@ -1,35 +1,39 @@
 // lion_fused_sm100.cu — N1 / N7: the fused sign-pack-exchange-vote-update kernel.
 //
 // One persistent, cooperatively launched kernel per bucket chunk does the whole Distributed
-// Lion step of every rank at once; the sign exchange happens INSIDE the kernel as peer stores
-// over NVLink, there is no NCCL call and no second kernel:
+// Lion step of a rank; the sign exchange happens INSIDE the kernel as peer stores over
+// NVLink — there is no NCCL call and no second kernel.  The step is split into two streaming
+// pipelines that run concurrently in every CTA and are coupled only through the peers' flags:
 //
-//   warp 0  (loader)  one lane streams tiles of g, m, p from HBM into an 8-stage shared-memory
-//                     ring with cp.async.bulk (TMA, 1-D) completing on mbarriers;
-//   warps 2-9 (compute, software-pipelined LOOKAHEAD tiles deep):
-//      produce(t): sign(b1*m + (1-b1)*g) for the tile from smem -> 32 signs/word ->
-//                  one warp per destination rank stores the tile's words (16 B / lane, one
-//                  coalesced request) into that rank's receive arena -- a peer-mapped pointer,
-//                  so the store travels over NVSwitch -- then fence + st.release.sys of a
-//                  per-(source rank, CTA) progress counter on that rank;
-//      consume(t): after the voter has published the vote planes of tile t: decoupled weight
-//                  decay + voted update on p, momentum EMA on m, 16-byte stores to HBM;
-//   warp 1  (voter)   ld.acquire.sys-polls the local progress counters of all awaited ranks,
-//                     reads the W rows of packed words of the tile from the local arena,
-//                     adds them bit-sliced (5 carry-save planes = per-element ballot count
-//                     0..16), and publishes either {majority, tie} planes or the count planes.
+//   P pipeline (needs g, m):  sign(b1*m + (1-b1)*g) -> 32 signs / word -> words to every rank's
+//                             receive arena;   m' = b2*m + (1-b2)*g written back immediately.
+//   C pipeline (needs p):     wait for the tile's words from all awaited ranks -> bit-sliced
+//                             vote -> p' = p*(1 - lr*wd) - lr*u written back.
 //
-// Between produce(t) and consume(t) the CTA works on LOOKAHEAD other tiles, which hides the
-// NVLink store + flag latency; the loader keeps the remaining stages of the ring in flight,
-// which hides HBM latency.  HBM traffic is the minimum: read g, m, p once, write p, m once
-// (10 B/param in bf16) + W/8 B/param of gathered words.
+// Nothing is carried from P to C inside the CTA (a rank's own words go through its own arena
+// like everybody else's), so P may run arbitrarily far ahead of C: NVLink store + flag latency
+// is hidden by distance, not by shared-memory capacity.  HBM traffic is the minimum: read g, m,
+// p once, write m, p once (10 B/param in bf16) + W/8 B/param of gathered words.
 //
-// Liveness: every CTA is co-resident (cooperative launch, 1 CTA/SM) and each CTA issues
-// produce(t) strictly before consume(t), so a rank never waits for data whose producer is
-// blocked behind it.  Arenas are double-buffered by launch parity: a rank can be at most one
-// launch ahead of any peer (it needs the peer's flags of the current launch to finish it).
-// All waits are bounded: a flag that never arrives is reported in `status` and the kernel
-// runs to completion instead of hanging the GPU.
+// Warp roles (24 warps, 1 CTA per SM; every compute role has 2 warps per SM sub-partition):
+//   0      P-loader   one lane: cp.async.bulk (TMA 1-D) of g, m tiles into a 6-stage smem ring
+//   1      C-loader   one lane: cp.async.bulk of p tiles into an 8-stage smem ring
+//   2-3    senders    drain a smem ring of packed tiles in batches: one coalesced 16 B/lane
+//                     store per (tile, destination rank) into the peer-mapped arena, then ONE
+//                     fence.acq_rel.sys + progress-counter store per batch and destination.
+//                     The fence latency is paid by these warps only and amortised over the batch.
+//   4-7    voters     (tile i -> voter i % 4) ld.acquire.sys on the local progress counters, read
+//                     the W word rows of the tile from the local arena (all loads issued before
+//                     the first use), carry-save add them into 5 bit planes (ballot count 0..16
+//                     per element), publish {majority, tie} or the count planes
+//   8-15   P-compute  sign bytes + momentum from smem; words into the sender ring
+//   16-23  C-compute  decay + voted update from smem p and the vote planes
+//
+// Liveness: all CTAs are co-resident (cooperative launch); the P pipeline never waits on a
+// remote event, so every flag a peer waits for is eventually produced.  Arenas are
+// double-buffered by launch parity: a rank can be at most one launch ahead of a peer (it needs
+// the peer's flags of the current launch to finish it).  All waits are bounded: a flag that
+// never arrives is reported in `status` and the kernel runs to completion.
 //
 // reference: distributed_lion.py:61-96 (update_fn_distributed: ~52 ATen kernels, a blocking
 // dist.all_gather of an int64 tensor and torch.mode per parameter tensor) and :98-136
@@ -40,14 +44,21 @@
 
 namespace dlion {
 
-constexpr int kStages = 8;
-constexpr int kLookahead = 4;
-constexpr int kArrayBytes = 8192;            // bytes of g (or m, or p) per tile
-constexpr int kStageBytes = 3 * kArrayBytes;
-constexpr int kComputeWarps = 8;
-constexpr int kComputeThreads = kComputeWarps * 32;
-constexpr int kFusedThreads = 64 + kComputeThreads;   // loader warp + voter warp + compute warps
-constexpr int64_t kMbarSpinLimit = 1ll << 24;
+constexpr int kArrayBytes = 8192;                 // bytes of g (or m, or p) per tile
+constexpr int kPStages = 6;                       // g+m ring
+constexpr int kPStageBytes = 2 * kArrayBytes;
+constexpr int kCStages = 8;                       // p ring
+constexpr int kCStageBytes = kArrayBytes;
+constexpr int kWordRing = 32;                     // packed tiles buffered for the senders
+constexpr int kSenders = 2;
+constexpr int kVoters = 4;
+constexpr int kPWarps = 8, kCWarps = 8;
+constexpr int kPThreads = kPWarps * 32, kCThreads = kCWarps * 32;
+constexpr int kWarpPLoad = 0, kWarpCLoad = 1, kWarpSend0 = 2, kWarpVoter0 = kWarpSend0 + kSenders;
+constexpr int kWarpP0 = kWarpVoter0 + kVoters, kWarpC0 = kWarpP0 + kPWarps;
+constexpr int kFusedThreads = (kWarpC0 + kCWarps) * 32;     // 24 warps = 768 threads
+static_assert(kCStages % kVoters == 0, "a voter must always meet the same ring slots");
+constexpr int64_t kMbarSpinLimit = 1ll << 26;
 constexpr int64_t kDefaultFlagSpin = 1ll << 24;
 
 struct FusedParams {
@@ -119,12 +130,21 @@ __device__ __forceinline__ void bulk_load(uint32_t dst_smem, const void* src, ui
                "l"(src), "r"(bytes), "r"(bar)
                : "memory");
 }
-__device__ __forceinline__ void st_release_sys(uint64_t* ptr, uint64_t v) {
-  asm volatile("st.release.sys.global.u64 [%0], %1;" ::"l"(ptr), "l"(v) : "memory");
+__device__ __forceinline__ void st_relaxed_sys(uint64_t* ptr, uint64_t v) {
+  asm volatile("st.relaxed.sys.global.u64 [%0], %1;" ::"l"(ptr), "l"(v) : "memory");
 }
 __device__ __forceinline__ uint64_t ld_acquire_sys(const uint64_t* ptr) {
   uint64_t v;
   asm volatile("ld.acquire.sys.global.u64 %0, [%1];" : "=l"(v) : "l"(ptr) : "memory");
+  return v;
+}
+__device__ __forceinline__ void fence_acq_rel_sys() { asm volatile("fence.acq_rel.sys;" ::: "memory"); }
+__device__ __forceinline__ void st_release_cta(uint32_t* smem_ptr, uint32_t v) {
+  asm volatile("st.release.cta.shared.u32 [%0], %1;" ::"r"(smem_u32(smem_ptr)), "r"(v) : "memory");
+}
+__device__ __forceinline__ uint32_t ld_acquire_cta(const uint32_t* smem_ptr) {
+  uint32_t v;
+  asm volatile("ld.acquire.cta.shared.u32 %0, [%1];" : "=r"(v) : "r"(smem_u32(smem_ptr)) : "memory");
   return v;
 }
 __device__ __forceinline__ void named_bar_sync(int id, int threads) {
@@ -134,15 +154,25 @@ __device__ __forceinline__ void named_bar_sync(int id, int threads) {
 template <typename T>
 struct Cfg {
   static constexpr int TILE = kArrayBytes / (int)sizeof(T);   // 4096 (2-byte types) / 2048 (fp32)
-  static constexpr int UNITS = TILE / 8;                      // 8-element units per tile
+  static constexpr int UNITS = TILE / 8;                      // 8-element units per tile: 512 / 256
   static constexpr int WORDS = TILE / 32;                     // sign words per tile: 128 / 64
-  static constexpr int UPT = UNITS / kComputeThreads;         // units per compute thread: 2 / 1
+  static constexpr int UPT_P = UNITS / kPThreads;             // units per P-compute thread: 4 / 2
+  static constexpr int UPT_C = UNITS / kCThreads;
   static constexpr int WPL = WORDS / 32;                      // words per voter lane: 4 / 2
   static constexpr int PLANE_BYTES = WORDS * 4;
-  static constexpr int SMEM_PLANES = kStages * 5 * PLANE_BYTES;
-  static constexpr int SMEM_WBUF = kStages * PLANE_BYTES;
-  static constexpr int SMEM_TOTAL = kStages * kStageBytes + SMEM_PLANES + SMEM_WBUF + 3 * kStages * 8 + 16;
+  static constexpr int OFF_PRING = 0;
+  static constexpr int OFF_CRING = OFF_PRING + kPStages * kPStageBytes;
+  static constexpr int OFF_WRING = OFF_CRING + kCStages * kCStageBytes;
+  static constexpr int OFF_PLANES = OFF_WRING + kWordRing * PLANE_BYTES;
+  static constexpr int OFF_BARS = OFF_PLANES + kCStages * 5 * PLANE_BYTES;
+  static constexpr int NUM_BARS = 2 * kPStages + 3 * kCStages;
+  static constexpr int OFF_CTRS = OFF_BARS + NUM_BARS * 8;
+  static constexpr int SMEM_TOTAL = OFF_CTRS + 64;
 };
+
+template <int N> struct VecOf;
+template <> struct VecOf<4> { using type = uint4; };
+template <> struct VecOf<2> { using type = uint2; };
 
 // bit-sliced "count >= K" / "count == K" over 5 planes (count in 0..31), K uniform
 __device__ __forceinline__ uint32_t planes_ge(const uint32_t (&c)[5], int K) {
@@ -169,13 +199,19 @@ template <typename T>
 __global__ void __launch_bounds__(kFusedThreads, 1) lion_fused_kernel(const __grid_constant__ FusedParams P) {
   using C = Cfg<T>;
   extern __shared__ __align__(128) uint8_t smem[];
-  uint8_t* stage_base = smem;
-  uint32_t* planes = reinterpret_cast<uint32_t*>(smem + kStages * kStageBytes);
-  uint32_t* wbuf = reinterpret_cast<uint32_t*>(smem + kStages * kStageBytes + C::SMEM_PLANES);
-  uint64_t* bars = reinterpret_cast<uint64_t*>(smem + kStages * kStageBytes + C::SMEM_PLANES + C::SMEM_WBUF);
-  uint64_t* full_bar = bars;                 // TMA landed           (1 arrival + tx bytes)
-  uint64_t* empty_bar = bars + kStages;      // tile fully consumed  (kComputeWarps arrivals)
-  uint64_t* vote_bar = bars + 2 * kStages;   // vote planes ready    (1 arrival)
+  uint8_t* pring = smem + C::OFF_PRING;                                    // [kPStages][g | m]
+  uint8_t* cring = smem + C::OFF_CRING;                                    // [kCStages][p]
+  uint32_t* wring = reinterpret_cast<uint32_t*>(smem + C::OFF_WRING);      // [kWordRing][WORDS]
+  uint32_t* planes = reinterpret_cast<uint32_t*>(smem + C::OFF_PLANES);    // [kCStages][5][WORDS]
+  uint64_t* bars = reinterpret_cast<uint64_t*>(smem + C::OFF_BARS);
+  uint64_t* fullP = bars;                          // g, m landed              (1 arrival + tx)
+  uint64_t* emptyP = fullP + kPStages;             // P-compute done with slot (kPWarps arrivals)
+  uint64_t* fullC = emptyP + kPStages;             // p landed                 (1 arrival + tx)
+  uint64_t* emptyC = fullC + kCStages;             // C-compute done with slot (kCWarps arrivals)
+  uint64_t* voteC = emptyC + kCStages;             // vote planes ready        (1 arrival)
+  uint32_t* ctrs = reinterpret_cast<uint32_t*>(smem + C::OFF_CTRS);
+  uint32_t* words_done = ctrs;                     // tiles whose packed words are in wring
+  uint32_t* sent = ctrs + 1;                       // [kSenders] tiles each sender has pushed out
 
   const int G = P.grid;
   const bool emu = P.emulate_ranks > 0;
@@ -194,53 +230,74 @@ __global__ void __launch_bounds__(kFusedThreads, 1) lion_fused_kernel(const __gr
 
   const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
   if (threadIdx.x == 0) {
-#pragma unroll
-    for (int s = 0; s < kStages; ++s) {
-      mbar_init(smem_u32(full_bar + s), 1);
-      mbar_init(smem_u32(empty_bar + s), kComputeWarps);
-      mbar_init(smem_u32(vote_bar + s), 1);
+    for (int s = 0; s < kPStages; ++s) {
+      mbar_init(smem_u32(fullP + s), 1);
+      mbar_init(smem_u32(emptyP + s), kPWarps);
     }
+    for (int s = 0; s < kCStages; ++s) {
+      mbar_init(smem_u32(fullC + s), 1);
+      mbar_init(smem_u32(emptyC + s), kCWarps);
+      mbar_init(smem_u32(voteC + s), 1);
+    }
+    *words_done = 0u;
+    for (int s = 0; s < kSenders; ++s) sent[s] = 0u;
     asm volatile("fence.mbarrier_init.release.cluster;" ::: "memory");
     asm volatile("fence.proxy.async.shared::cta;" ::: "memory");
   }
   __syncthreads();
   if (n_my == 0) return;
 
-  if (warp == 0) {
-    // ============================ loader ============================
+  if (warp == kWarpPLoad) {
+    // ============================ P-loader: g, m ============================
     if (lane == 0) {
       for (int i = 0; i < n_my; ++i) {
-        const int slot = i % kStages, k = i / kStages;
-        if (k > 0) mbar_wait(smem_u32(empty_bar + slot), (uint32_t)((k - 1) & 1), P.status, 0);
+        const int slot = i % kPStages, k = i / kPStages;
+        if (k > 0) mbar_wait(smem_u32(emptyP + slot), (uint32_t)((k - 1) & 1), P.status, 0);
         const int64_t off = ((int64_t)cta + (int64_t)i * G) * C::TILE;
-        const uint32_t bar = smem_u32(full_bar + slot);
-        const uint32_t dst = smem_u32(stage_base + slot * kStageBytes);
-        mbar_arrive_expect_tx(bar, kStageBytes);
+        const uint32_t bar = smem_u32(fullP + slot);
+        const uint32_t dst = smem_u32(pring + slot * kPStageBytes);
+        mbar_arrive_expect_tx(bar, kPStageBytes);
         bulk_load(dst, g + off, kArrayBytes, bar);
         bulk_load(dst + kArrayBytes, m + off, kArrayBytes, bar);
-        bulk_load(dst + 2 * kArrayBytes, p + off, kArrayBytes, bar);
       }
     }
-  } else if (warp == 1) {
-    // ============================ voter ============================
+  } else if (warp == kWarpCLoad) {
+    // ============================ C-loader: p ============================
+    if (lane == 0) {
+      for (int i = 0; i < n_my; ++i) {
+        const int slot = i % kCStages, k = i / kCStages;
+        if (k > 0) mbar_wait(smem_u32(emptyC + slot), (uint32_t)((k - 1) & 1), P.status, 1);
+        const int64_t off = ((int64_t)cta + (int64_t)i * G) * C::TILE;
+        const uint32_t bar = smem_u32(fullC + slot);
+        mbar_arrive_expect_tx(bar, kCStageBytes);
+        bulk_load(smem_u32(cring + slot * kCStageBytes), p + off, kArrayBytes, bar);
+      }
+    }
+  } else if (warp >= kWarpVoter0 && warp < kWarpP0) {
+    // ============================ voters ============================
+    const int v = warp - kWarpVoter0;
     const uint64_t* my_flags = P.flags[my_rank];
-    const uint32_t* my_arena = P.arena[my_rank];
+    const uint32_t* my_arena = P.arena[my_rank] + (int64_t)parity_sel * W * P.arena_words;
     const int64_t spin_limit = P.spin_limit > 0 ? P.spin_limit : kDefaultFlagSpin;
     bool gave_up = false;
+    uint64_t seen = 0;                       // last progress value this lane observed for rank `lane`
     const int thr = P.L / 2 + 1;             // +1 iff 2*cnt > L  <=>  cnt >= floor(L/2)+1
-    for (int i = 0; i < n_my; ++i) {
-      const int slot = i % kStages, k = i / kStages;
-      if (k > 0) mbar_wait(smem_u32(empty_bar + slot), (uint32_t)((k - 1) & 1), P.status, 1);
+    const bool waits = lane < W && ((P.wait_mask >> lane) & 1u);
+    const uint64_t* f = my_flags + (int64_t)(lane < W ? lane : 0) * DLION_FUSED_MAX_CTAS + cta;
+    using WordVec = typename VecOf<C::WPL>::type;
+    for (int i = v; i < n_my; i += kVoters) {
+      const int slot = i % kCStages, k = i / kCStages;
+      if (k > 0) mbar_wait(smem_u32(emptyC + slot), (uint32_t)((k - 1) & 1), P.status, 2);
       const uint64_t target = epoch_hi | (uint64_t)(i + 1);
-      if (lane < W && ((P.wait_mask >> lane) & 1u) && !gave_up) {
-        const uint64_t* f = my_flags + (int64_t)lane * DLION_FUSED_MAX_CTAS + cta;
+      if (waits && !gave_up && seen < target) {
         int64_t it = 0;
-        while (ld_acquire_sys(f) < target) {
+        while ((seen = ld_acquire_sys(f)) < target) {
           if (++it > spin_limit) {
             report(P.status, 1, cta, lane);
             gave_up = true;
             break;
           }
+          __nanosleep(40);
         }
       }
       gave_up = __any_sync(0xffffffffu, gave_up);   // also orders every lane after the acquires
@@ -250,25 +307,27 @@ __global__ void __launch_bounds__(kFusedThreads, 1) lion_fused_kernel(const __gr
       for (int w = 0; w < C::WPL; ++w)
 #pragma unroll
         for (int k2 = 0; k2 < 5; ++k2) c[w][k2] = 0u;
-      for (int r = 0; r < W; ++r) {
-        if (!((P.live_mask >> r) & 1u)) continue;
-        const uint32_t* src = my_arena + ((int64_t)(parity_sel * W + r)) * P.arena_words + woff;
-        uint32_t x[C::WPL];
-        if constexpr (C::WPL == 4) {
-          const uint4 q = __ldcv(reinterpret_cast<const uint4*>(src));
-          x[0] = q.x; x[1] = q.y; x[2] = q.z; x[3] = q.w;
-        } else {
-          const uint2 q = __ldcv(reinterpret_cast<const uint2*>(src));
-          x[0] = q.x; x[1] = q.y;
+      for (int r0 = 0; r0 < W; r0 += 8) {
+        WordVec x[8];
+#pragma unroll
+        for (int j = 0; j < 8; ++j) {               // all loads in flight before the first use
+          const int r = r0 + j;
+          const bool on = r < W && ((P.live_mask >> r) & 1u);
+          x[j] = on ? __ldcv(reinterpret_cast<const WordVec*>(my_arena + (int64_t)r * P.arena_words + woff))
+                    : WordVec{};
         }
 #pragma unroll
-        for (int w = 0; w < C::WPL; ++w) {   // carry-save add of one ballot bit per element
-          uint32_t carry = x[w];
+        for (int j = 0; j < 8; ++j) {
+          const uint32_t* xw = reinterpret_cast<const uint32_t*>(&x[j]);
 #pragma unroll
-          for (int k2 = 0; k2 < 5; ++k2) {
-            const uint32_t t = c[w][k2] & carry;
-            c[w][k2] ^= carry;
-            carry = t;
+          for (int w = 0; w < C::WPL; ++w) {        // carry-save add of one ballot bit per element
+            uint32_t carry = xw[w];
+#pragma unroll
+            for (int k2 = 0; k2 < 5; ++k2) {
+              const uint32_t t = c[w][k2] & carry;
+              c[w][k2] ^= carry;
+              carry = t;
+            }
           }
         }
       }
@@ -287,23 +346,76 @@ __global__ void __launch_bounds__(kFusedThreads, 1) lion_fused_kernel(const __gr
         }
       }
       __syncwarp();
-      if (lane == 0) mbar_arrive(smem_u32(vote_bar + slot));
+      if (lane == 0) mbar_arrive(smem_u32(voteC + slot));
     }
-  } else {
-    // ============================ compute ============================
-    const int ct = threadIdx.x - 64;
-    const int cw = warp - 2;
-
-    auto produce = [&](int i) {
-      const int slot = i % kStages, k = i / kStages;
-      mbar_wait(smem_u32(full_bar + slot), (uint32_t)(k & 1), P.status, 2);
-      const T* sg = reinterpret_cast<const T*>(stage_base + slot * kStageBytes);
-      const T* sm = reinterpret_cast<const T*>(stage_base + slot * kStageBytes + kArrayBytes);
-      const int64_t tile = (int64_t)cta + (int64_t)i * G;
-      uint32_t* wb = wbuf + slot * C::WORDS;
+  } else if (warp >= kWarpSend0 && warp < kWarpVoter0) {
+    // ============================ senders ============================
+    const int s = warp - kWarpSend0;
+    uint32_t done_sent = 0;
+    int64_t idle = 0;
+    while (done_sent < (uint32_t)n_my) {
+      uint32_t done = 0;
+      if (lane == 0) done = ld_acquire_cta(words_done);
+      done = __shfl_sync(0xffffffffu, done, 0);      // the shuffle also orders the ring reads after the acquire
+      if (done == done_sent) {
+        if (++idle > kMbarSpinLimit) {
+          report(P.status, 2, (int)blockIdx.x, 3);
+          __trap();
+        }
+        __nanosleep(64);
+        continue;
+      }
+      idle = 0;
+      for (uint32_t t = done_sent; t < done; ++t) {
+        const uint4* src = reinterpret_cast<const uint4*>(wring + (t % kWordRing) * C::WORDS);
+        const int64_t woff = ((int64_t)cta + (int64_t)t * G) * C::WORDS;
+        uint4 v = make_uint4(0, 0, 0, 0);
+        if (lane < C::WORDS / 4) v = src[lane];
+        for (int r = s; r < W; r += kSenders) {
+          uint32_t* dst = P.arena[r] + ((int64_t)(parity_sel * W + my_rank)) * P.arena_words + woff;
+          if (lane < C::WORDS / 4) reinterpret_cast<uint4*>(dst)[lane] = v;   // one coalesced request per tile
+        }
+      }
+      __syncwarp();
+      if (lane == 0) {
+        fence_acq_rel_sys();                         // one fence per batch: everything above is visible first
+        for (int r = s; r < W; r += kSenders)
+          st_relaxed_sys(P.flags[r] + (int64_t)my_rank * DLION_FUSED_MAX_CTAS + cta, epoch_hi | (uint64_t)done);
+        st_release_cta(sent + s, done);              // ring slots below `done` may be reused
+      }
+      __syncwarp();
+      done_sent = done;
+    }
+  } else if (warp < kWarpC0) {
+    // ============================ P-compute ============================
+    const int pt = threadIdx.x - kWarpP0 * 32;
+    for (int i = 0; i < n_my; ++i) {
+      const int slot = i % kPStages, k = i / kPStages;
+      if (i >= kWordRing) {                           // ring capacity: tile i-kWordRing must have left
+        int64_t it = 0;
+        for (;;) {
+          uint32_t lo = ld_acquire_cta(sent);
 #pragma unroll
-      for (int u = 0; u < C::UPT; ++u) {
-        const int unit = ct + u * kComputeThreads;
+          for (int s2 = 1; s2 < kSenders; ++s2) {
+            const uint32_t v = ld_acquire_cta(sent + s2);
+            lo = v < lo ? v : lo;
+          }
+          if (lo + kWordRing > (uint32_t)i) break;
+          if (++it > kMbarSpinLimit) {
+            report(P.status, 2, (int)blockIdx.x, 4);
+            __trap();
+          }
+          __nanosleep(64);
+        }
+      }
+      mbar_wait(smem_u32(fullP + slot), (uint32_t)(k & 1), P.status, 5);
+      const T* sg = reinterpret_cast<const T*>(pring + slot * kPStageBytes);
+      const T* sm = reinterpret_cast<const T*>(pring + slot * kPStageBytes + kArrayBytes);
+      const int64_t tile = (int64_t)cta + (int64_t)i * G;
+      uint32_t* wb = wring + (i % kWordRing) * C::WORDS;
+#pragma unroll
+      for (int u = 0; u < C::UPT_P; ++u) {
+        const int unit = pt + u * kPThreads;
         float gf[8], mf[8];
         load8<T>(sg + unit * 8, gf);
         load8<T>(sm + unit * 8, mf);
@@ -313,36 +425,30 @@ __global__ void __launch_bounds__(kFusedThreads, 1) lion_fused_kernel(const __gr
         wv |= __shfl_xor_sync(0xffffffffu, wv, 1);
         wv |= __shfl_xor_sync(0xffffffffu, wv, 2);
         if ((lane & 3) == 0) wb[unit >> 2] = wv;
+        momentum8<T>(mf, gf, P.beta2, P.omb2);
+        store8<T>(m + tile * C::TILE + unit * 8, mf);
       }
-      named_bar_sync(1, kComputeThreads);
-      // one warp per destination rank: a single coalesced 16-byte-per-lane store, then publish
-      for (int r = cw; r < W; r += kComputeWarps) {
-        uint32_t* dst = P.arena[r] + ((int64_t)(parity_sel * W + my_rank)) * P.arena_words + tile * C::WORDS;
-        if (lane < C::WORDS / 4)
-          reinterpret_cast<uint4*>(dst)[lane] = reinterpret_cast<const uint4*>(wb)[lane];
-        __syncwarp();
-        if (lane == 0) {
-          __threadfence_system();
-          st_release_sys(P.flags[r] + (int64_t)my_rank * DLION_FUSED_MAX_CTAS + cta, epoch_hi | (uint64_t)(i + 1));
-        }
-      }
-    };
-
-    auto consume = [&](int i) {
-      const int slot = i % kStages, k = i / kStages;
-      mbar_wait(smem_u32(vote_bar + slot), (uint32_t)(k & 1), P.status, 3);
-      const T* sg = reinterpret_cast<const T*>(stage_base + slot * kStageBytes);
-      const T* sm = reinterpret_cast<const T*>(stage_base + slot * kStageBytes + kArrayBytes);
-      const T* sp = reinterpret_cast<const T*>(stage_base + slot * kStageBytes + 2 * kArrayBytes);
+      __syncwarp();
+      if (lane == 0) mbar_arrive(smem_u32(emptyP + slot));
+      named_bar_sync(1, kPThreads);                  // every word of tile i is in the ring
+      if (pt == 0) st_release_cta(words_done, (uint32_t)(i + 1));
+    }
+  } else {
+    // ============================ C-compute ============================
+    const int ct = threadIdx.x - kWarpC0 * 32;
+    for (int i = 0; i < n_my; ++i) {
+      const int slot = i % kCStages, k = i / kCStages;
+      mbar_wait(smem_u32(fullC + slot), (uint32_t)(k & 1), P.status, 6);
+      mbar_wait(smem_u32(voteC + slot), (uint32_t)(k & 1), P.status, 7);
+      const T* sp = reinterpret_cast<const T*>(cring + slot * kCStageBytes);
       const uint8_t* pl = reinterpret_cast<const uint8_t*>(planes + slot * 5 * C::WORDS);
       const int64_t off = ((int64_t)cta + (int64_t)i * G) * C::TILE;
 #pragma unroll
-      for (int u = 0; u < C::UPT; ++u) {
-        const int unit = ct + u * kComputeThreads;
-        float gf[8], mf[8], pf[8];
-        load8<T>(sg + unit * 8, gf);
-        load8<T>(sm + unit * 8, mf);
+      for (int u = 0; u < C::UPT_C; ++u) {
+        const int unit = ct + u * kCThreads;
+        float pf[8];
         load8<T>(sp + unit * 8, pf);
+        float uf[8];
         if (P.vote == DLION_VOTE_AVERAGE) {
           uint32_t b[5];
 #pragma unroll
@@ -351,31 +457,18 @@ __global__ void __launch_bounds__(kFusedThreads, 1) lion_fused_kernel(const __gr
           for (int e = 0; e < 8; ++e) {
             const int cnt = ((b[0] >> e) & 1) | (((b[1] >> e) & 1) << 1) | (((b[2] >> e) & 1) << 2) |
                             (((b[3] >> e) & 1) << 3) | (((b[4] >> e) & 1) << 4);
-            const float uu = __fdiv_rn((float)(2 * cnt - P.L), (float)P.L);
-            pf[e] = lion_apply<T>(pf[e], uu, P.lr, P.decay);
-            mf[e] = lion_momentum<T>(mf[e], gf[e], P.beta2, P.omb2);
+            uf[e] = __fdiv_rn((float)(2 * cnt - P.L), (float)P.L);
           }
         } else {
           const uint32_t a = pl[unit], z = pl[C::PLANE_BYTES + unit];
 #pragma unroll
-          for (int e = 0; e < 8; ++e) {
-            const float uu = ((z >> e) & 1u) ? 0.f : (((a >> e) & 1u) ? 1.f : -1.f);
-            pf[e] = lion_apply<T>(pf[e], uu, P.lr, P.decay);
-            mf[e] = lion_momentum<T>(mf[e], gf[e], P.beta2, P.omb2);
-          }
+          for (int e = 0; e < 8; ++e) uf[e] = ((z >> e) & 1u) ? 0.f : (((a >> e) & 1u) ? 1.f : -1.f);
         }
+        apply8<T>(pf, uf, P.lr, P.decay);
         store8<T>(p + off + unit * 8, pf);
-        store8<T>(m + off + unit * 8, mf);
       }
       __syncwarp();
-      if (lane == 0) mbar_arrive(smem_u32(empty_bar + slot));
-    };
-
-    const int pro = n_my < kLookahead ? n_my : kLookahead;
-    for (int i = 0; i < pro; ++i) produce(i);
-    for (int j = 0; j < n_my; ++j) {
-      if (j + kLookahead < n_my) produce(j + kLookahead);
-      consume(j);
+      if (lane == 0) mbar_arrive(smem_u32(emptyC + slot));
     }
   }
 }

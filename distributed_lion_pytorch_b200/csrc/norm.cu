@@ -13,7 +13,7 @@
 
 namespace dlion {
 
-constexpr int kNormBwdParts = kNumSMs * 4;
+constexpr int kNormBwdParts = kNumSMs * 8;
 
 template <int BLOCK>
 __device__ __forceinline__ float block_allreduce_sum(float v, float* smem) {
@@ -67,7 +67,8 @@ __global__ void __launch_bounds__(BLOCK) norm_fwd_kernel(const T* __restrict__ x
           float r[8];
           load8<T>(res + row * cols + j * 8, r);
 #pragma unroll
-          for (int i = 0; i < 8; ++i) s[k][i] = DT<T>::rnd(s[k][i] + r[i]);   // the residual stream lives in T
+          for (int i = 0; i < 8; ++i) s[k][i] += r[i];
+          round8<T>(s[k]);                                                    // the residual stream lives in T
         }
         if (sum_out != nullptr) store8<T>(sum_out + row * cols + j * 8, s[k]);
 #pragma unroll
@@ -104,10 +105,15 @@ __global__ void __launch_bounds__(BLOCK) norm_fwd_kernel(const T* __restrict__ x
       const int j = threadIdx.x + k * BLOCK;
       if (j < nvec) {
         float o[8];
+        if (RMS) {                                                        // HF: weight * h.to(input_dtype)
 #pragma unroll
-        for (int i = 0; i < 8; ++i) {
-          if (RMS) o[i] = wv[k][i] * DT<T>::rnd(s[k][i] * rstd);          // HF: weight * h.to(input_dtype)
-          else o[i] = fmaf((s[k][i] - mean) * rstd, wv[k][i], bv[k][i]);
+          for (int i = 0; i < 8; ++i) o[i] = s[k][i] * rstd;
+          round8<T>(o);
+#pragma unroll
+          for (int i = 0; i < 8; ++i) o[i] *= wv[k][i];
+        } else {
+#pragma unroll
+          for (int i = 0; i < 8; ++i) o[i] = fmaf((s[k][i] - mean) * rstd, wv[k][i], bv[k][i]);
         }
         store8<T>(y + row * cols + j * 8, o);
       }
@@ -115,14 +121,41 @@ __global__ void __launch_bounds__(BLOCK) norm_fwd_kernel(const T* __restrict__ x
   }
 }
 
-template <typename T, int VPT, int BLOCK, bool RMS>
+// Sum NV values per thread over the block; every thread gets all NV totals.
+template <int BLOCK, int NV>
+__device__ __forceinline__ void block_allreduce_sum_n(float (&v)[NV], float* smem /* [NV][32] */) {
+#pragma unroll
+  for (int q = 0; q < NV; ++q)
+#pragma unroll
+    for (int o = 16; o > 0; o >>= 1) v[q] += __shfl_xor_sync(0xffffffffu, v[q], o);
+  if constexpr (BLOCK > 32) {
+    const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
+    __syncthreads();
+    if (lane == 0) {
+#pragma unroll
+      for (int q = 0; q < NV; ++q) smem[q * 32 + warp] = v[q];
+    }
+    __syncthreads();
+#pragma unroll
+    for (int q = 0; q < NV; ++q) {
+      v[q] = lane < (BLOCK >> 5) ? smem[q * 32 + lane] : 0.f;
+#pragma unroll
+      for (int o = 16; o > 0; o >>= 1) v[q] += __shfl_xor_sync(0xffffffffu, v[q], o);
+    }
+  }
+}
+
+// ROWS rows are processed per trip so that ROWS x (dy, xs, dsum) loads are in flight per thread
+// before the first block reduction: the kernel is latency-bound otherwise (cols = 768 leaves
+// only 96 threads per row).
+template <typename T, int VPT, int BLOCK, bool RMS, int ROWS>
 __global__ void __launch_bounds__(BLOCK) norm_bwd_kernel(const T* __restrict__ dy, const T* __restrict__ dsum_in,
                                                          const T* __restrict__ xs, const T* __restrict__ w,
                                                          const float* __restrict__ mean_in,
                                                          const float* __restrict__ rstd_in, T* __restrict__ dx,
                                                          float* __restrict__ dw_part, float* __restrict__ db_part,
                                                          int64_t rows, int cols) {
-  __shared__ float red[32];
+  __shared__ float red[2 * ROWS * 32];
   const int nvec = cols >> 3;
   float wv[VPT][8], dwv[VPT][8], dbv[VPT][8];
 #pragma unroll
@@ -133,45 +166,57 @@ __global__ void __launch_bounds__(BLOCK) norm_bwd_kernel(const T* __restrict__ d
     for (int i = 0; i < 8; ++i) dwv[k][i] = 0.f, dbv[k][i] = 0.f;
   }
   const float inv_cols = 1.0f / (float)cols;
-  for (int64_t row = blockIdx.x; row < rows; row += gridDim.x) {
-    const float mean = RMS ? 0.f : mean_in[row];
-    const float rstd = rstd_in[row];
-    float g[VPT][8], xh[VPT][8];
-    float sg = 0.f, sgx = 0.f;
+  for (int64_t row0 = (int64_t)blockIdx.x * ROWS; row0 < rows; row0 += (int64_t)gridDim.x * ROWS) {
+    float g[ROWS][VPT][8], xh[ROWS][VPT][8], rs[ROWS][VPT][8];
+    float sums[2 * ROWS];
+    float rstd[ROWS];
 #pragma unroll
-    for (int k = 0; k < VPT; ++k) {
-      const int j = threadIdx.x + k * BLOCK;
-      if (j < nvec) {
-        float d[8], s[8];
-        load8<T>(dy + row * cols + j * 8, d);
-        load8<T>(xs + row * cols + j * 8, s);
+    for (int r = 0; r < ROWS; ++r) {
+      const int64_t row = row0 + r;
+      const bool live = row < rows;
+      const float mean = (RMS || !live) ? 0.f : mean_in[row];
+      rstd[r] = live ? rstd_in[row] : 0.f;
+      sums[2 * r] = 0.f;
+      sums[2 * r + 1] = 0.f;
 #pragma unroll
-        for (int i = 0; i < 8; ++i) {
-          xh[k][i] = (s[i] - mean) * rstd;
-          g[k][i] = d[i] * wv[k][i];
-          dwv[k][i] = fmaf(d[i], RMS ? DT<T>::rnd(xh[k][i]) : xh[k][i], dwv[k][i]);
-          dbv[k][i] += d[i];
-          sg += g[k][i];
-          sgx = fmaf(g[k][i], xh[k][i], sgx);
+      for (int k = 0; k < VPT; ++k) {
+        const int j = threadIdx.x + k * BLOCK;
+        if (j < nvec && live) {
+          float d[8], s[8];
+          load8<T>(dy + row * cols + j * 8, d);
+          load8<T>(xs + row * cols + j * 8, s);
+          if (dsum_in != nullptr) load8<T>(dsum_in + row * cols + j * 8, rs[r][k]);
+#pragma unroll
+          for (int i = 0; i < 8; ++i) {
+            xh[r][k][i] = (s[i] - mean) * rstd[r];
+            g[r][k][i] = d[i] * wv[k][i];
+            dwv[k][i] = fmaf(d[i], RMS ? DT<T>::rnd(xh[r][k][i]) : xh[r][k][i], dwv[k][i]);
+            dbv[k][i] += d[i];
+            sums[2 * r] += g[r][k][i];
+            sums[2 * r + 1] = fmaf(g[r][k][i], xh[r][k][i], sums[2 * r + 1]);
+          }
         }
       }
     }
-    const float mg = RMS ? 0.f : block_allreduce_sum<BLOCK>(sg, red) * inv_cols;
-    const float mgx = block_allreduce_sum<BLOCK>(sgx, red) * inv_cols;
+    block_allreduce_sum_n<BLOCK, 2 * ROWS>(sums, red);
 #pragma unroll
-    for (int k = 0; k < VPT; ++k) {
-      const int j = threadIdx.x + k * BLOCK;
-      if (j < nvec) {
-        float o[8];
+    for (int r = 0; r < ROWS; ++r) {
+      const int64_t row = row0 + r;
+      if (row >= rows) break;
+      const float mg = RMS ? 0.f : sums[2 * r] * inv_cols;
+      const float mgx = sums[2 * r + 1] * inv_cols;
 #pragma unroll
-        for (int i = 0; i < 8; ++i) o[i] = rstd * (g[k][i] - mg - xh[k][i] * mgx);
-        if (dsum_in != nullptr) {
-          float r[8];
-          load8<T>(dsum_in + row * cols + j * 8, r);
+      for (int k = 0; k < VPT; ++k) {
+        const int j = threadIdx.x + k * BLOCK;
+        if (j < nvec) {
+          float o[8];
 #pragma unroll
-          for (int i = 0; i < 8; ++i) o[i] += r[i];
+          for (int i = 0; i < 8; ++i) {
+            o[i] = rstd[r] * (g[r][k][i] - mg - xh[r][k][i] * mgx);
+            if (dsum_in != nullptr) o[i] += rs[r][k][i];
+          }
+          store8<T>(dx + row * cols + j * 8, o);
         }
-        store8<T>(dx + row * cols + j * 8, o);
       }
     }
   }
@@ -191,15 +236,15 @@ __global__ void __launch_bounds__(BLOCK) norm_bwd_kernel(const T* __restrict__ d
   }
 }
 
-// partials [parts, cols] -> dweight/dbias (T).  blockDim (32, 8): 32 columns x 8 row slices.
+// partials [parts, cols] -> dweight/dbias (T).  blockDim (32, 32): 32 columns x 32 row slices.
 template <typename T>
 __global__ void norm_bwd_finalize_kernel(const float* __restrict__ dw_part, const float* __restrict__ db_part,
                                          T* __restrict__ dw, T* __restrict__ db, int parts, int cols) {
-  __shared__ float sw[8][33], sb[8][33];
+  __shared__ float sw[32][33], sb[32][33];
   const int c = blockIdx.x * 32 + threadIdx.x;
   float aw = 0.f, ab = 0.f;
   if (c < cols)
-    for (int r = threadIdx.y; r < parts; r += 8) {
+    for (int r = threadIdx.y; r < parts; r += 32) {
       aw += dw_part[(int64_t)r * cols + c];
       if (db_part != nullptr) ab += db_part[(int64_t)r * cols + c];
     }
@@ -208,7 +253,7 @@ __global__ void norm_bwd_finalize_kernel(const float* __restrict__ dw_part, cons
   __syncthreads();
   if (threadIdx.y == 0 && c < cols) {
 #pragma unroll
-    for (int r = 1; r < 8; ++r) aw += sw[r][threadIdx.x], ab += sb[r][threadIdx.x];
+    for (int r = 1; r < 32; ++r) aw += sw[r][threadIdx.x], ab += sb[r][threadIdx.x];
     dw[c] = DT<T>::from_f(aw);
     if (db != nullptr && db_part != nullptr) db[c] = DT<T>::from_f(ab);
   }
@@ -233,14 +278,15 @@ template <typename T, int VPT, int BLOCK>
 static int launch_bwd(const void* dy, const void* dsum_in, const void* xs, const void* w, const float* mean,
                       const float* rstd, void* dx, float* dwp, float* dbp, int64_t rows, int cols, int rms,
                       cudaStream_t s) {
-  const int grid = (int)(rows < kNormBwdParts ? rows : kNormBwdParts);
+  constexpr int ROWS = VPT == 1 ? 2 : 1;
+  const int64_t trips = (rows + ROWS - 1) / ROWS;
+  const int grid = (int)(trips < kNormBwdParts ? trips : kNormBwdParts);
   if (rms)
-    norm_bwd_kernel<T, VPT, BLOCK, true><<<grid, BLOCK, 0, s>>>((const T*)dy, (const T*)dsum_in, (const T*)xs,
-                                                                (const T*)w, mean, rstd, (T*)dx, dwp, dbp, rows, cols);
+    norm_bwd_kernel<T, VPT, BLOCK, true, ROWS><<<grid, BLOCK, 0, s>>>(
+        (const T*)dy, (const T*)dsum_in, (const T*)xs, (const T*)w, mean, rstd, (T*)dx, dwp, dbp, rows, cols);
   else
-    norm_bwd_kernel<T, VPT, BLOCK, false><<<grid, BLOCK, 0, s>>>((const T*)dy, (const T*)dsum_in, (const T*)xs,
-                                                                 (const T*)w, mean, rstd, (T*)dx, dwp, dbp, rows,
-                                                                 cols);
+    norm_bwd_kernel<T, VPT, BLOCK, false, ROWS><<<grid, BLOCK, 0, s>>>(
+        (const T*)dy, (const T*)dsum_in, (const T*)xs, (const T*)w, mean, rstd, (T*)dx, dwp, dbp, rows, cols);
   return DLION_LAUNCH_CHECK("dlion_norm_bwd");
 }
 
@@ -298,6 +344,12 @@ extern "C" int dlion_norm_fwd(const void* x, const void* residual, const void* w
 
 extern "C" int dlion_norm_bwd_partial_rows(void) { return kNormBwdParts; }
 
+extern "C" int dlion_norm_bwd_parts(int64_t rows, int cols) {
+  const int rows_per_trip = (cols >> 3) <= 256 ? 2 : 1;     // must mirror launch_bwd: ROWS = (VPT == 1 ? 2 : 1)
+  const int64_t trips = (rows + rows_per_trip - 1) / rows_per_trip;
+  return (int)(trips < kNormBwdParts ? trips : kNormBwdParts);
+}
+
 extern "C" int dlion_norm_bwd(const void* dy, const void* dsum_in, const void* xsum, const void* weight,
                               const float* mean, const float* rstd, void* dx, float* dw_partial, float* db_partial,
                               int64_t rows, int cols, int rms, int dtype, void* stream) {
@@ -325,7 +377,7 @@ extern "C" int dlion_norm_bwd_finalize(const float* dw_partial, const float* db_
                                        int parts, int cols, int dtype, void* stream) {
   DLION_CHECK_ARG(parts > 0 && cols > 0 && dw_partial && dweight, "dlion_norm_bwd_finalize: bad arguments");
   cudaStream_t s = (cudaStream_t)stream;
-  const dim3 block(32, 8);
+  const dim3 block(32, 32);
   const int grid = (cols + 31) / 32;
   DISPATCH_DTYPE(dtype, norm_bwd_finalize_kernel<T><<<grid, block, 0, s>>>(dw_partial, db_partial, (T*)dweight,
                                                                              (T*)dbias, parts, cols));

@@ -72,6 +72,7 @@ def _declare(L: C.CDLL) -> None:
         "dlion_clip_scale": [vp, i64, i32, vp, f32, vp],
         "dlion_norm_fwd": [vp, vp, vp, vp, vp, vp, vp, vp, i64, i32, f32, i32, i32, vp],
         "dlion_norm_bwd": [vp, vp, vp, vp, vp, vp, vp, vp, vp, i64, i32, i32, i32, vp],
+        "dlion_norm_bwd_parts": [i64, i32],
         "dlion_norm_bwd_finalize": [vp, vp, vp, vp, i32, i32, i32, vp],
         "dlion_rope": [vp, vp, vp, vp, i64, i32, i32, i32, i32, i64, i64, i32, i32, vp],
         "dlion_ce_fwd_bwd": [vp, vp, vp, i64, i32, i64, i64, f32, i32, i32, vp],

@@ -51,7 +51,7 @@ class _FusedNorm(torch.autograd.Function):
         dyc = dy.contiguous()
         dsc = dsum.contiguous() if dsum is not None else None
         L = _cabi.lib()
-        parts = min(rows, int(L.dlion_norm_bwd_partial_rows()))
+        parts = int(L.dlion_norm_bwd_parts(rows, cols))
         dx = torch.empty_like(summed)
         dwp = torch.empty(parts, cols, dtype=torch.float32, device=dy.device)
         dbp = torch.empty(parts, cols, dtype=torch.float32, device=dy.device) if ctx.has_bias else None

@@ -151,9 +151,11 @@ int dlion_norm_fwd(const void* x, const void* residual, const void* weight, cons
                    int dtype, void* stream);
 /* backward: dx (and d residual, identical) = norm-backward(dy) + dsum_in (may be NULL);
  * dweight/dbias partials are accumulated in fp32 `dw_partial`/`db_partial` of shape
- * [min(rows, dlion_norm_bwd_partial_rows()), cols] (one row per CTA launched); reduce them
- * with dlion_norm_bwd_finalize(parts = that row count). */
+ * [dlion_norm_bwd_parts(rows, cols), cols] (one row per CTA launched, at most
+ * dlion_norm_bwd_partial_rows()); reduce them with dlion_norm_bwd_finalize(parts = that count). */
 int dlion_norm_bwd_partial_rows(void);
+/* number of partial rows dlion_norm_bwd writes for this shape (= CTAs it launches) */
+int dlion_norm_bwd_parts(int64_t rows, int cols);
 int dlion_norm_bwd(const void* dy, const void* dsum_in, const void* xsum, const void* weight,
                    const float* mean, const float* rstd, void* dx, float* dw_partial, float* db_partial,
                    int64_t rows, int cols, int rms, int dtype, void* stream);
