@@ -4,6 +4,8 @@
 //   dlion_clip_scale   : x *= min(1, max_norm / (||x|| + 1e-6)) with the norm read on device
 // reference: the per-tensor Python loop in distributed_lion.py:179-198 and flatten_and_pad
 // (:14-24); gradient clipping is HF Trainer's (max_grad_norm=1.0 default), inherited upstream.
+#include <mutex>
+
 #include "common.cuh"
 
 namespace dlion {
@@ -186,4 +188,93 @@ extern "C" int dlion_clip_scale(void* x, int64_t n, int dtype, const float* sums
   const int grid = (int)(want < 1 ? 1 : (want > kNumSMs * 16 ? kNumSMs * 16 : want));
   DISPATCH_DTYPE(dtype, clip_scale_kernel<T><<<grid, 256, 0, s>>>((T*)x, n, sumsq, max_norm));
   return DLION_LAUNCH_CHECK("dlion_clip_scale");
+}
+
+// ====================================================================================
+// dlion_sumsq_static — sum of squares for callers that cannot allocate device memory.
+//
+// dlion_sumsq() needs a caller-provided scratch buffer (a ticket word plus one fp32 partial
+// per CTA).  Some callers have no way to obtain one.  Examples: a plugin living inside a host
+// application that has handed its whole device-memory budget out at start-up and forbids
+// cudaMalloc afterwards (serving stacks and real-time pipelines often work like that); a
+// monitoring hook that wants a gradient norm but must not disturb the framework's caching
+// allocator; a plain C program that links this library and has no allocator layer of its
+// own.  For them the scratch lives in the file-scope array below, which every GPU that loads
+// the library keeps resident until the process exits (kSumsqStaticBytes = 16,640 bytes per
+// device).
+//
+// Size limit: one CTA sums one fixed chunk of kSumsqStaticChunk = 65,536 elements and owns one
+// partial slot, and there are kSumsqStaticSlots = 4,096 slots, so a call may cover at most
+// DLION_SUMSQ_STATIC_MAX_N = 4,096 * 65,536 = 268,435,456 elements (one fused-optimizer
+// chunk).  Larger n is refused with DLION_E_TOOBIG and a message; nothing is launched.
+//
+// Rules of use
+//  * The array name is only a host-side handle: the kernel needs the DEVICE address, which is
+//    looked up with cudaGetSymbolAddress once per device, with that device current, the first
+//    time the entry point is called on it.  Make that first call outside any stream capture.
+//  * No cudaMalloc / cudaFree / allocating library routine is called, here or on later calls.
+//  * All calls on a device share the one array and it keeps the previous call's contents: the
+//    ticket word is cleared (cudaMemsetAsync on `stream`) before every launch, the partial slots
+//    are fully overwritten before they are read.  Two calls that overlap on the GPU (different
+//    streams, no dependency between them) race on the array and give undefined results —
+//    serialise them.
+namespace dlion {
+
+constexpr int kSumsqStaticSlots = 4096;
+constexpr int64_t kSumsqStaticChunk = 65536;
+constexpr int64_t kSumsqStaticBytes = 256 + (int64_t)kSumsqStaticSlots * 4;   // ticket (padded) + partials
+constexpr int kMaxDevices = 64;
+
+static __device__ __align__(256) unsigned char g_sumsq_static_scratch[kSumsqStaticBytes];
+
+static void* g_sumsq_static_ptr[kMaxDevices];     // device address of the array, per device ordinal
+static bool g_sumsq_static_ready[kMaxDevices];
+static std::mutex g_sumsq_static_mu;              // two host threads may make "the first call" at once
+
+static int sumsq_static_address(void** out) {
+  int dev = 0;
+  int rc = check_cuda(cudaGetDevice(&dev), "cudaGetDevice");
+  if (rc) return rc;
+  if (dev < 0 || dev >= kMaxDevices) {
+    set_error("dlion_sumsq_static: device ordinal %d outside [0, %d)", dev, kMaxDevices);
+    return DLION_E_UNSUPPORTED;
+  }
+  std::lock_guard<std::mutex> lock(g_sumsq_static_mu);
+  if (!g_sumsq_static_ready[dev]) {
+    void* ptr = nullptr;
+    rc = check_cuda(cudaGetSymbolAddress(&ptr, g_sumsq_static_scratch),
+                    "cudaGetSymbolAddress(g_sumsq_static_scratch) — first call on a device must be outside stream capture");
+    if (rc) return rc;
+    g_sumsq_static_ptr[dev] = ptr;
+    g_sumsq_static_ready[dev] = true;
+  }
+  *out = g_sumsq_static_ptr[dev];
+  return 0;
+}
+
+}  // namespace dlion
+
+extern "C" int64_t dlion_sumsq_static_max_n(void) { return (int64_t)kSumsqStaticSlots * kSumsqStaticChunk; }
+
+extern "C" int dlion_sumsq_static(const void* x, int64_t n, int dtype, float* out, void* stream) {
+  DLION_CHECK_ARG(n >= 0 && out != nullptr, "dlion_sumsq_static: bad arguments");
+  DLION_CHECK_ARG(aligned16(x), "dlion_sumsq_static: x must be 16-byte aligned");
+  if (n > dlion_sumsq_static_max_n()) {
+    set_error("dlion_sumsq_static: n = %lld exceeds the built-in scratch (%d slots x %lld elements = %lld); "
+              "split the input or use dlion_sumsq with your own scratch buffer",
+              (long long)n, kSumsqStaticSlots, (long long)kSumsqStaticChunk, (long long)dlion_sumsq_static_max_n());
+    return DLION_E_TOOBIG;
+  }
+  void* base = nullptr;
+  int rc = sumsq_static_address(&base);
+  if (rc) return rc;
+  cudaStream_t s = (cudaStream_t)stream;
+  unsigned int* ticket = (unsigned int*)base;
+  float* partials = (float*)((unsigned char*)base + 256);
+  rc = check_cuda(cudaMemsetAsync(ticket, 0, 256, s), "cudaMemsetAsync(ticket)");   // must start at zero
+  if (rc) return rc;
+  int64_t want = (n + kSumsqStaticChunk - 1) / kSumsqStaticChunk;
+  const int grid = (int)(want < 1 ? 1 : want);                                      // <= kSumsqStaticSlots by the check above
+  DISPATCH_DTYPE(dtype, sumsq_kernel<T><<<grid, 256, 0, s>>>((const T*)x, n, ticket, partials, out));
+  return DLION_LAUNCH_CHECK("dlion_sumsq_static");
 }

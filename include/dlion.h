@@ -137,6 +137,18 @@ int dlion_multi_gather(const void* const* srcs, void* const* dsts, const int64_t
  * which the reference inherits: SURVEY §3.1). */
 int64_t dlion_sumsq_scratch_bytes(void);
 int dlion_sumsq(const void* x, int64_t n, int dtype, void* scratch, float* out, void* stream);
+/* Same result as dlion_sumsq, for callers that cannot hand over a scratch buffer because they
+ * cannot allocate device memory: a plugin inside a host application that gave its whole
+ * device-memory budget out at start-up and forbids cudaMalloc afterwards, a monitoring hook
+ * that must not disturb the framework's caching allocator, a plain C caller without an
+ * allocator layer.  The scratch is a 16,640-byte array built into the library image on every
+ * GPU that loads it.  Limit: n <= dlion_sumsq_static_max_n() = 268,435,456 elements, larger n is
+ * refused with DLION_E_TOOBIG.  The first call on each device looks the array's device address
+ * up (cudaGetSymbolAddress) and must therefore be made outside stream capture.  Calls share the
+ * array: serialise them — two calls overlapping on the GPU race.  Never allocates.
+ * (No counterpart in the reference: it has no native code and clips through HF's Trainer.) */
+int64_t dlion_sumsq_static_max_n(void);
+int dlion_sumsq_static(const void* x, int64_t n, int dtype, float* out, void* stream);
 /* x *= min(1, max_norm / (sqrt(*sumsq) + 1e-6)) — torch.nn.utils.clip_grad_norm_'s coefficient */
 int dlion_clip_scale(void* x, int64_t n, int dtype, const float* sumsq, float max_norm, void* stream);
 
