@@ -1,0 +1,76 @@
+// colsum.cu — bias gradient: column sums of a [rows, cols] activation-gradient matrix.
+//
+// ATen's generic reduce_kernel reaches about a quarter of the HBM roofline on these tall,
+// narrow-ish bf16 matrices (ncu launch list, profiles/launches_gpt2_microstep_run1.csv: 1.9 ms
+// per GPT-2 micro-step for 48 bias gradients).  Here a warp reads 512 contiguous bytes of a row
+// (32 lanes x 8 columns), 8 row lanes per CTA walk the rows, every thread keeps 8 fp32 sums; the
+// CTA folds its 8 row lanes through shared memory and writes one fp32 partial row; the partial
+// rows are folded by dlion_norm_bwd_finalize's kernel.
+// reference: the `grad_output.sum(0)` of every biased HF GPT-2 Conv1D in backward, reached from
+// accelerator.backward (async_trainer.py:33).
+#include "common.cuh"
+
+namespace dlion {
+
+constexpr int kColsumParts = kNumSMs * 4;
+
+template <typename T>
+__global__ void __launch_bounds__(256) colsum_kernel(const T* __restrict__ x, float* __restrict__ partial,
+                                                     int64_t rows, int cols) {
+  __shared__ float sm[8][32][9];
+  const int lane = threadIdx.x & 31, rl = threadIdx.x >> 5;
+  const int cg = blockIdx.x * 32 + lane;          // 8-column group
+  const bool live = cg * 8 < cols;
+  float acc[8] = {0.f, 0.f, 0.f, 0.f, 0.f, 0.f, 0.f, 0.f};
+  if (live) {
+    const int64_t step = (int64_t)gridDim.y * 8;
+    int64_t r = (int64_t)blockIdx.y * 8 + rl;
+    for (; r + step < rows; r += 2 * step) {      // two rows in flight per thread
+      float a[8], b[8];
+      load8<T>(x + r * cols + cg * 8, a);
+      load8<T>(x + (r + step) * cols + cg * 8, b);
+#pragma unroll
+      for (int i = 0; i < 8; ++i) acc[i] += a[i] + b[i];
+    }
+    if (r < rows) {
+      float a[8];
+      load8<T>(x + r * cols + cg * 8, a);
+#pragma unroll
+      for (int i = 0; i < 8; ++i) acc[i] += a[i];
+    }
+  }
+#pragma unroll
+  for (int i = 0; i < 8; ++i) sm[rl][lane][i] = acc[i];
+  __syncthreads();
+  // thread t folds column (t) of this block's 256 columns over the 8 row lanes
+  const int c = threadIdx.x;
+  const int col = blockIdx.x * 256 + c;
+  if (col < cols) {
+    float s = 0.f;
+#pragma unroll
+    for (int q = 0; q < 8; ++q) s += sm[q][c >> 3][c & 7];
+    partial[(int64_t)blockIdx.y * cols + col] = s;
+  }
+}
+
+}  // namespace dlion
+
+using namespace dlion;
+
+extern "C" int dlion_colsum_parts(int64_t rows, int cols) {
+  const int gx = (cols + 255) / 256;
+  int gy = kColsumParts / (gx > 0 ? gx : 1);
+  const int64_t max_y = (rows + 7) / 8;
+  if (gy > max_y) gy = (int)max_y;
+  return gy < 1 ? 1 : gy;
+}
+
+extern "C" int dlion_colsum(const void* x, int64_t rows, int cols, float* partial, int dtype, void* stream) {
+  DLION_CHECK_ARG(rows >= 0 && cols > 0 && (cols & 7) == 0, "dlion_colsum: cols (%d) must be a positive multiple of 8", cols);
+  DLION_CHECK_ARG(aligned16(x) && partial != nullptr, "dlion_colsum: bad pointers");
+  if (rows == 0) return 0;
+  const dim3 grid((cols + 255) / 256, dlion_colsum_parts(rows, cols));
+  cudaStream_t s = (cudaStream_t)stream;
+  DISPATCH_DTYPE(dtype, colsum_kernel<T><<<grid, 256, 0, s>>>((const T*)x, partial, rows, cols));
+  return DLION_LAUNCH_CHECK("dlion_colsum");
+}

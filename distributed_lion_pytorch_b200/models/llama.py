@@ -16,6 +16,7 @@ import torch.nn.functional as F
 from torch.utils.checkpoint import checkpoint
 
 from ..ops.cross_entropy import linear_cross_entropy, linear_log_probs
+from ..ops.linear import fused_linear
 from ..ops.norm import add_rms_norm
 from ..ops.rope import apply_rope, rope_tables
 from .common import CausalLMOutput, ConfigBase, PreTrainedMixin, shift_labels
@@ -53,6 +54,14 @@ LLAMA_PRESETS = {
 }
 
 
+class Linear(nn.Linear):
+    """nn.Linear (HF parameter names, LoRA-wrappable) whose backward accumulates the weight
+    gradient inside the GEMM when a gradient buffer already exists (ops/linear.py)."""
+
+    def forward(self, x):
+        return fused_linear(x, self.weight, self.bias, in_out=False)
+
+
 class RMSNormParams(nn.Module):
     def __init__(self, n: int, eps: float):
         super().__init__()
@@ -69,10 +78,10 @@ class LlamaAttention(nn.Module):
         H = cfg.hidden_size
         self.n_head, self.n_kv = cfg.num_attention_heads, cfg.num_key_value_heads
         self.head_dim = H // self.n_head
-        self.q_proj = nn.Linear(H, self.n_head * self.head_dim, bias=False)
-        self.k_proj = nn.Linear(H, self.n_kv * self.head_dim, bias=False)
-        self.v_proj = nn.Linear(H, self.n_kv * self.head_dim, bias=False)
-        self.o_proj = nn.Linear(self.n_head * self.head_dim, H, bias=False)
+        self.q_proj = Linear(H, self.n_head * self.head_dim, bias=False)
+        self.k_proj = Linear(H, self.n_kv * self.head_dim, bias=False)
+        self.v_proj = Linear(H, self.n_kv * self.head_dim, bias=False)
+        self.o_proj = Linear(self.n_head * self.head_dim, H, bias=False)
 
     def forward(self, x, cos, sin, attn_mask=None):
         B, S, _ = x.shape
@@ -89,9 +98,9 @@ class LlamaAttention(nn.Module):
 class LlamaMLP(nn.Module):
     def __init__(self, cfg: LlamaConfig):
         super().__init__()
-        self.gate_proj = nn.Linear(cfg.hidden_size, cfg.intermediate_size, bias=False)
-        self.up_proj = nn.Linear(cfg.hidden_size, cfg.intermediate_size, bias=False)
-        self.down_proj = nn.Linear(cfg.intermediate_size, cfg.hidden_size, bias=False)
+        self.gate_proj = Linear(cfg.hidden_size, cfg.intermediate_size, bias=False)
+        self.up_proj = Linear(cfg.hidden_size, cfg.intermediate_size, bias=False)
+        self.down_proj = Linear(cfg.intermediate_size, cfg.hidden_size, bias=False)
 
     def forward(self, x):
         return self.down_proj(F.silu(self.gate_proj(x)) * self.up_proj(x))

@@ -174,6 +174,13 @@ int dlion_norm_bwd(const void* dy, const void* dsum_in, const void* xsum, const 
 int dlion_norm_bwd_finalize(const float* dw_partial, const float* db_partial, void* dweight, void* dbias,
                             int parts, int cols, int dtype, void* stream);
 
+/* Bias gradient: fp32 partial column sums of x [rows, cols] (cols % 8 == 0) into
+ * partial[dlion_colsum_parts(rows, cols)][cols]; fold them with dlion_norm_bwd_finalize
+ * (db_partial = NULL).  reference: `grad_output.sum(0)` of every biased Conv1D in HF GPT-2's
+ * backward, reached from accelerator.backward (async_trainer.py:33). */
+int dlion_colsum_parts(int64_t rows, int cols);
+int dlion_colsum(const void* x, int64_t rows, int cols, float* partial, int dtype, void* stream);
+
 /* N4 — rotary embedding applied in place to q [tokens, q_heads, head_dim] and k
  * [tokens, k_heads, head_dim] (HF "rotate_half" pairing: i <-> i + head_dim/2); cos/sin are
  * fp32 [seq, head_dim/2]; pos = token index % seq_len.  inverse != 0 applies the transpose

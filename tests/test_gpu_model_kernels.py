@@ -147,3 +147,40 @@ def test_lion_optimizer_on_gpu_uses_kernels_and_matches_reference(ref_mod):
     assert ops.library_loaded()
     for pa, pb in zip(net_a.parameters(), net_b.parameters()):
         assert torch.allclose(pa, pb, rtol=0, atol=1e-7)
+
+
+@pytest.mark.parametrize("dtype", [torch.float32, torch.bfloat16])
+@pytest.mark.parametrize("in_out", [True, False])
+@pytest.mark.parametrize("with_bias", [True, False])
+def test_fused_linear_accumulates_into_existing_grads(dtype, in_out, with_bias):
+    """Weight gradient accumulated by the GEMM epilogue into a pre-existing .grad, bias gradient
+    from the column-sum kernel — against plain autograd in fp32."""
+    from distributed_lion_pytorch_b200.ops.linear import column_sum, fused_linear
+    torch.manual_seed(0)
+    rows, cin, cout = 3001, 256, 776
+    x = torch.randn(7, rows // 7 + 1, cin, device="cuda").to(dtype).requires_grad_()
+    w = (torch.randn(cin, cout, device="cuda") * 0.05).to(dtype)
+    w = (w if in_out else w.t().contiguous()).requires_grad_()
+    b = torch.randn(cout, device="cuda").to(dtype).requires_grad_() if with_bias else None
+    g0 = torch.randn_like(w)
+    w.grad = g0.clone()                               # what Lion's flat gradient bucket provides
+    if with_bias:
+        b.grad = torch.ones_like(b)
+    dy = torch.randn(*x.shape[:-1], cout, device="cuda").to(dtype)
+    for _ in range(2):                                # two micro-batches accumulate
+        y = fused_linear(x, w, b, in_out)
+        y.backward(dy)
+    xf, wf = x.detach().float().requires_grad_(), w.detach().float().requires_grad_()
+    bf = b.detach().float().requires_grad_() if with_bias else None
+    yf = xf @ (wf if in_out else wf.t())
+    if with_bias:
+        yf = yf + bf
+    yf.backward(dy.float())
+    t = dict(rtol=3e-2, atol=0.5) if dtype == torch.bfloat16 else dict(rtol=1e-3, atol=1e-2)
+    assert torch.allclose(y.float(), yf, rtol=3e-2 if dtype == torch.bfloat16 else 1e-4, atol=3e-2)
+    assert torch.allclose(x.grad.float(), 2 * xf.grad, **t)
+    assert torch.allclose(w.grad.float(), g0.float() + 2 * wf.grad, **t)
+    if with_bias:
+        assert torch.allclose(b.grad.float(), 1 + 2 * bf.grad, **t)
+    cs = column_sum(dy.reshape(-1, cout), torch.float32)
+    assert torch.allclose(cs, dy.reshape(-1, cout).float().sum(0), rtol=1e-3, atol=1e-2)
