@@ -64,6 +64,22 @@ def barrier() -> None:
         dist.barrier()
 
 
+import contextlib
+
+
+@contextlib.contextmanager
+def main_process_first():
+    """Rank 0 runs the block first, the others after it (dataset preparation that fills a cache);
+    reference: ``training_args.main_process_first`` at run_clm.py:474,531."""
+    if is_dist() and rank() != 0:
+        dist.barrier()
+    try:
+        yield
+    finally:
+        if is_dist() and rank() == 0:
+            dist.barrier()
+
+
 def shutdown() -> None:
     global _DEVICE
     if dist.is_available() and dist.is_initialized():

@@ -66,6 +66,8 @@ class TrainingArguments:
     lion_drop_prob: float = field(default=0.0, metadata={"help": "simulated per-step worker drop-out probability"})
     lion_live_mask: Optional[str] = field(default=None, metadata={"help": "fixed live-worker mask, e.g. 0b1011"})
     comm: str = field(default="auto", metadata={"help": "auto | fused | nccl_1bit | nccl_allreduce"})
+    lion_bucket_mb: Optional[int] = field(default=None, metadata={"help": "MiB of bf16 parameters per fused launch"})
+    profile_steps: bool = field(default=False, metadata={"help": "log device-timed forward/backward/optimizer ms"})
     per_rank_optimizer_state: bool = field(default=False, metadata={"help": "also save optimizer_rank<r>.pt"})
     synthetic_data: bool = field(default=False, metadata={"help": "random tokens of the right shape"})
     synthetic_samples: int = 4096

@@ -38,6 +38,7 @@ import torch.distributed as dist
 from ..optim.lion import Lion
 from ..parallel import runtime as rt
 from ..parallel.fault import DropoutSchedule
+from ..utils.profiling import StepTimer, nvtx_range
 from .args import TrainingArguments
 from .data import build_loader, default_data_collator
 from .schedules import get_scheduler
@@ -55,6 +56,17 @@ def get_last_checkpoint(folder: str) -> Optional[str]:
     if not cks:
         return None
     return os.path.join(folder, max(cks, key=lambda x: int(_re_ckpt.search(x).group(1))))
+
+
+def lion_comm_for(args, sync_gradients: bool) -> str:
+    """Map ``--comm`` onto a Lion back-end.  ``nccl_allreduce`` is the synchronous-gradient
+    baseline: gradients are averaged first, every rank then holds the same gradient, so the
+    plain local Lion step keeps replicas identical (SURVEY X5 / BASELINE B2)."""
+    if getattr(args, "lion_bucket_mb", None):
+        os.environ["DLION_CHUNK_ELEMS"] = str(int(args.lion_bucket_mb) * (1 << 20) // 2)
+    if args.comm == "nccl_allreduce" or (sync_gradients and rt.world_size() > 1):
+        return "local"
+    return args.comm if args.comm in ("auto", "fused", "nccl_1bit", "local") else "auto"
 
 
 def set_seed(seed: int) -> None:
@@ -115,7 +127,7 @@ class Trainer:
         self.state = TrainerState()
         self.is_world_process_zero = rt.rank() == 0
         self._dropout_schedule: Optional[DropoutSchedule] = None
-        self._timers: Dict[str, float] = {}
+        self.timer = StepTimer(enabled=bool(getattr(self.args, "profile_steps", False)))
         self._wandb = None
         if self.args.gradient_checkpointing and hasattr(self.model, "gradient_checkpointing_enable"):
             self.model.gradient_checkpointing_enable()
@@ -128,7 +140,7 @@ class Trainer:
             if a.lion:
                 vote = "majority" if a.lion_vote == "stochastic" else a.lion_vote
                 mgn = a.lion_max_grad_norm if a.lion_vote != "stochastic" else (a.lion_max_grad_norm or 1.0)
-                comm = a.comm if a.comm in ("auto", "fused", "nccl_1bit", "local") else "auto"
+                comm = lion_comm_for(a, self.sync_gradients)
                 self.optimizer = Lion(params, lr=a.learning_rate, weight_decay=a.weight_decay, max_grad_norm=mgn,
                                       vote=vote, tie=a.lion_tie, comm=comm, seed=a.seed)
             else:   # reference: run_clm.py:584 (hard-codes weight_decay=0.1 there — D13; we honour the flag)
@@ -174,10 +186,11 @@ class Trainer:
         class synchronises them once per optimizer step in :meth:`_sync_gradients`."""
         model.train()
         inputs = self._prepare_inputs(inputs)
-        with self.autocast():
+        with self.timer.phase("forward"), self.autocast():
             loss = self.compute_loss(model, inputs)
         ga = self.args.gradient_accumulation_steps
-        (loss / ga if ga > 1 else loss).backward()
+        with self.timer.phase("backward"):
+            (loss / ga if ga > 1 else loss).backward()
         return loss.detach() / ga
 
     def _flat_grads(self) -> List[torch.Tensor]:
@@ -273,9 +286,12 @@ class Trainer:
                 micro += 1
                 if micro % ga:
                     continue
-                self._sync_gradients()
-                grad_norm = self._clip_gradients()
-                self._optimizer_step()
+                with self.timer.phase("grad_sync"):
+                    self._sync_gradients()
+                with self.timer.phase("clip"):
+                    grad_norm = self._clip_gradients()
+                with self.timer.phase("optimizer"):
+                    self._optimizer_step()
                 self.state.global_step += 1
                 self.state.epoch = epoch + (micro / ga) / steps_per_epoch if steps_per_epoch else 0.0
                 if tokens_per_micro:
@@ -290,6 +306,7 @@ class Trainer:
                     if isinstance(self.optimizer, Lion) and self._dropout_schedule is not None:
                         logs["live_workers"] = self._dropout_schedule.live_count(step - 1)
                     logged_loss, logged_step = cur, step
+                    logs.update(self.timer.summary())          # device-timed phase means (only with --profile_steps)
                     self.log(logs)
                 if a.evaluation_strategy == "steps" and a.eval_steps and step % a.eval_steps == 0 \
                         and self.eval_dataset is not None:

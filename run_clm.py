@@ -140,8 +140,10 @@ def main(argv=None):
         tokenizer = load_tokenizer(model_args.tokenizer_name or model_args.model_name_or_path)
         if len(tokenizer) > cfg.vocab_size:
             raise ValueError(f"tokenizer has {len(tokenizer)} tokens but the model embeds {cfg.vocab_size}")
+        from distributed_lion_pytorch_b200.parallel.runtime import main_process_first
         if data_args.dataset_name is not None:
-            train_dataset, eval_dataset = _hub_dataset(data_args, tokenizer, block_size)
+            with main_process_first():            # reference: run_clm.py:474,531
+                train_dataset, eval_dataset = _hub_dataset(data_args, tokenizer, block_size)
         else:
             train_dataset = text_file_dataset(data_args.train_file, tokenizer, block_size, data_args.keep_linebreaks) \
                 if data_args.train_file else None
@@ -169,12 +171,15 @@ def main(argv=None):
             training_args.max_steps = max(int(training_args.num_train_epochs * per_epoch), 1)
         vote = "majority" if training_args.lion_vote == "stochastic" else training_args.lion_vote
         mgn = training_args.lion_max_grad_norm or (1.0 if training_args.lion_vote == "stochastic" else None)
-        comm = training_args.comm if training_args.comm in ("auto", "fused", "nccl_1bit", "local") else "auto"
+        from distributed_lion_pytorch_b200.train.trainer import lion_comm_for
+        sync = (not training_args.async_grad) or training_args.comm == "nccl_allreduce"
+        comm = lion_comm_for(training_args, sync)
         optimizer = Lion(model.parameters(), lr=training_args.learning_rate, weight_decay=training_args.weight_decay,
                          max_grad_norm=mgn, vote=vote, tie=training_args.lion_tie, comm=comm, seed=training_args.seed)
         optimizers = (optimizer, get_cosine_schedule_with_warmup(optimizer, training_args.warmup_steps,
                                                                  training_args.max_steps))
-    trainer_class = AsyncTrainer if training_args.async_grad else Trainer     # reference: run_clm.py:587
+    # reference: run_clm.py:587; --comm nccl_allreduce forces the synchronous-gradient baseline
+    trainer_class = AsyncTrainer if training_args.async_grad and training_args.comm != "nccl_allreduce" else Trainer
     trainer = trainer_class(model=model, args=training_args,
                             train_dataset=train_dataset if training_args.do_train else None,
                             eval_dataset=eval_dataset if training_args.do_eval else None, tokenizer=tokenizer,

@@ -68,8 +68,19 @@ def _entry(rank, world, port, backend, fn, args, q):
                 pass
 
 
-def run_distributed(fn, world: int, *args, backend: str = "gloo", timeout: float = 180.0):
-    """Run ``fn(rank, world, *args)`` in ``world`` spawned processes; returns results by rank."""
+def run_distributed(fn, world: int, *args, backend: str = "gloo", timeout: float = 180.0, _retries: int = 2):
+    """Run ``fn(rank, world, *args)`` in ``world`` spawned processes; returns results by rank.
+    A rendezvous that loses the race for its TCP port (seen once on an 8-GPU box) is retried."""
+    try:
+        return _run_once(fn, world, args, backend, timeout)
+    except RuntimeError as e:
+        msg = str(e)
+        if _retries > 0 and ("TCPStore" in msg or "EADDRINUSE" in msg or "address already in use" in msg.lower()):
+            return run_distributed(fn, world, *args, backend=backend, timeout=timeout, _retries=_retries - 1)
+        raise
+
+
+def _run_once(fn, world, args, backend, timeout):
     ctx = mp.get_context("spawn")
     q = ctx.Queue()
     port = free_port()

@@ -157,3 +157,24 @@ def test_constructor_validation():
     assert o.defaults == {"lr": 1e-4, "betas": (0.9, 0.99), "weight_decay": 0.0} or \
         {k: o.defaults[k] for k in ("lr", "betas", "weight_decay")} == {"lr": 1e-4, "betas": (0.9, 0.99), "weight_decay": 0.0}
     assert o.backend_name == "local"
+
+
+def test_module_level_helpers_match_reference(ref_mod):
+    import distributed_lion as ours
+    t = torch.arange(13).reshape(13) > 5
+    a, sa = ours.flatten_and_pad(t)
+    b, sb = ref_mod.flatten_and_pad(t)
+    assert torch.equal(a, b) and sa == sb and a.numel() == 16
+    assert torch.equal(ours.restore_flattened_tensor(a, sa), ref_mod.restore_flattened_tensor(b, sb))
+    g = torch.Generator().manual_seed(0)
+    for W in (1, 2, 3, 4, 7, 8):
+        votes = [torch.rand(40, generator=g) > 0.5 for _ in range(W)]
+        assert torch.equal(ours.majority_vote(votes), ref_mod.majority_vote(votes))
+    assert ours.exists(0) and not ours.exists(None)
+    p1, p2 = torch.randn(50), None
+    p2 = p1.clone()
+    gr, m1 = torch.randn(50), torch.randn(50) * 0.1
+    m2 = m1.clone()
+    ref_mod.update_fn(p1, gr, m1, 1e-3, 0.1, 0.9, 0.99)
+    ours.update_fn(p2, gr, m2, 1e-3, 0.1, 0.9, 0.99)
+    assert torch.equal(p1, p2) and torch.equal(m1, m2)

@@ -140,3 +140,29 @@ def _worker_grad_none(rank, world):
 def test_grad_none_on_one_rank_does_not_hang():
     outs = run_distributed(_worker_grad_none, 2)
     assert torch.equal(outs[0], outs[1])
+
+
+def _worker_functional(rank, world):
+    import distributed_lion as ours
+    from conftest import load_reference_module
+    ref = load_reference_module()
+    torch.manual_seed(0)
+    p1 = torch.randn(37, 3)
+    p2 = p1.clone()
+    g = torch.Generator().manual_seed(50 + rank)
+    m1 = torch.zeros_like(p1)
+    m2 = torch.zeros_like(p1)
+    for _ in range(3):
+        gr = torch.randn(37, 3, generator=g)
+        ref.update_fn_distributed(p1, gr, m1, 1e-2, 0.1, 0.9, 0.99)
+        ours.update_fn_distributed(p2, gr, m2, 1e-2, 0.1, 0.9, 0.99)
+    same = torch.equal(p1, p2) and torch.equal(m1, m2)
+    ours.update_fn_distributed_stoc(p2, gr, m2, 1e-2, 0.1, 0.9, 0.99, 1.0)     # runs (dead code upstream)
+    return dict(same=same, p_ref=p1, p_stoc=p2)
+
+
+def test_functional_update_fn_distributed_matches_reference():
+    outs = run_distributed(_worker_functional, 3)
+    assert all(o["same"] for o in outs)                                # bit-exact vs the reference, per tensor
+    assert torch.equal(outs[0]["p_ref"], outs[1]["p_ref"])
+    assert torch.equal(outs[0]["p_stoc"], outs[2]["p_stoc"])           # stochastic ballots still give one common update
