@@ -74,13 +74,18 @@ def main():
     for mp in [float(x) for x in a.sizes.split(",")]:
         n = int(mp * 1e6) // 8192 * 8192
         res = {"n": n, "world": W}
-        for comm in ("fused", "nccl_1bit"):
+        for comm in ("fused", "fused_multicast", "nccl_1bit"):
+            import os
+            os.environ["DLION_MULTICAST"] = "1" if comm == "fused_multicast" else "0"
             p = torch.nn.Parameter(torch.randn(n, device=device).bfloat16())
             p.grad = torch.randn(n, device=device).bfloat16()
-            opt = Lion([p], lr=1e-4, weight_decay=0.1, comm=comm)
-            res[comm] = timeit(lambda: opt.step(), a.iters, 3, device)
-            if comm == "fused":
+            opt = Lion([p], lr=1e-4, weight_decay=0.1, comm="fused" if comm.startswith("fused") else comm)
+            t = timeit(lambda: opt.step(), a.iters, 3, device)
+            if comm.startswith("fused"):
                 opt._backend._ctx.check_status()
+                if comm == "fused_multicast" and not opt._backend._ctx.uses_multicast:
+                    t = None                      # fabric exposes no multicast pointer
+            res[comm] = t
             del opt, p
             torch.cuda.empty_cache()
         p = torch.randn(n, device=device).bfloat16()

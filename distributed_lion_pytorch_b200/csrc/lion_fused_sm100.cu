@@ -78,6 +78,7 @@ struct FusedParams {
   uint64_t epoch;
   uint32_t* arena[DLION_MAX_RANKS];
   uint64_t* flags[DLION_MAX_RANKS];
+  uint32_t* mc_arena;
   int64_t arena_words;
   int grid;
   int emulate_ranks;
@@ -137,6 +138,12 @@ __device__ __forceinline__ uint64_t ld_acquire_sys(const uint64_t* ptr) {
   uint64_t v;
   asm volatile("ld.acquire.sys.global.u64 %0, [%1];" : "=l"(v) : "l"(ptr) : "memory");
   return v;
+}
+// one 16-byte store to an NVLS multicast address: the switch writes it into every rank's replica
+__device__ __forceinline__ void multimem_st_v4(uint32_t* mc_ptr, const uint4& v) {
+  asm volatile("multimem.st.relaxed.sys.global.v4.f32 [%0], {%1, %2, %3, %4};" ::"l"(mc_ptr), "f"(__uint_as_float(v.x)),
+               "f"(__uint_as_float(v.y)), "f"(__uint_as_float(v.z)), "f"(__uint_as_float(v.w))
+               : "memory");
 }
 __device__ __forceinline__ void fence_acq_rel_sys() { asm volatile("fence.acq_rel.sys;" ::: "memory"); }
 __device__ __forceinline__ void st_release_cta(uint32_t* smem_ptr, uint32_t v) {
@@ -371,15 +378,24 @@ __global__ void __launch_bounds__(kFusedThreads, 1) lion_fused_kernel(const __gr
         const int64_t woff = ((int64_t)cta + (int64_t)t * G) * C::WORDS;
         uint4 v = make_uint4(0, 0, 0, 0);
         if (lane < C::WORDS / 4) v = src[lane];
-        for (int r = s; r < W; r += kSenders) {
-          uint32_t* dst = P.arena[r] + ((int64_t)(parity_sel * W + my_rank)) * P.arena_words + woff;
-          if (lane < C::WORDS / 4) reinterpret_cast<uint4*>(dst)[lane] = v;   // one coalesced request per tile
+        if (P.mc_arena != nullptr) {                 // NVLS: sender 0 stores once, the switch replicates
+          if (s == 0 && lane < C::WORDS / 4)
+            multimem_st_v4(P.mc_arena + ((int64_t)(parity_sel * W + my_rank)) * P.arena_words + woff + lane * 4, v);
+        } else {
+          for (int r = s; r < W; r += kSenders) {
+            uint32_t* dst = P.arena[r] + ((int64_t)(parity_sel * W + my_rank)) * P.arena_words + woff;
+            if (lane < C::WORDS / 4) reinterpret_cast<uint4*>(dst)[lane] = v;   // one coalesced request per tile
+          }
         }
       }
       __syncwarp();
       if (lane == 0) {
         fence_acq_rel_sys();                         // one fence per batch: everything above is visible first
-        for (int r = s; r < W; r += kSenders)
+        // progress counters stay unicast (one 8-byte store per destination); with multicast data
+        // sender 0 issued every data store, so it also publishes to every destination
+        const int r_begin = P.mc_arena != nullptr ? (s == 0 ? 0 : W) : s;
+        const int r_step = P.mc_arena != nullptr ? 1 : kSenders;
+        for (int r = r_begin; r < W; r += r_step)
           st_relaxed_sys(P.flags[r] + (int64_t)my_rank * DLION_FUSED_MAX_CTAS + cta, epoch_hi | (uint64_t)done);
         st_release_cta(sent + s, done);              // ring slots below `done` may be reused
       }
@@ -534,6 +550,7 @@ static int launch_fused(const dlion_fused_args* a, cudaStream_t s) {
   for (int r = 0; r < a->world; ++r)
     DLION_CHECK_ARG(P.arena[r] != nullptr && P.flags[r] != nullptr && aligned16(P.arena[r]),
                     "dlion_fused_step: arena/flags pointer of rank %d is null or unaligned", r);
+  P.mc_arena = a->emulate_ranks > 0 ? nullptr : a->mc_arena;
   P.arena_words = a->arena_words; P.grid = a->grid; P.emulate_ranks = a->emulate_ranks; P.emu_stride = a->emu_stride;
   P.status = a->status; P.spin_limit = a->spin_limit;
   void* kargs[] = {(void*)&P};

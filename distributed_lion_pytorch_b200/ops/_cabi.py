@@ -32,7 +32,7 @@ class FusedArgs(C.Structure):
         ("beta2", C.c_float), ("omb2", C.c_float),
         ("vote", C.c_int), ("stoch_r", C.c_float), ("seed", C.c_uint64), ("step", C.c_uint32),
         ("epoch", C.c_uint64),
-        ("arena", C.c_void_p * MAX_RANKS), ("flags", C.c_void_p * MAX_RANKS),
+        ("arena", C.c_void_p * MAX_RANKS), ("flags", C.c_void_p * MAX_RANKS), ("mc_arena", C.c_void_p),
         ("arena_words", C.c_int64), ("grid", C.c_int), ("emulate_ranks", C.c_int),
         ("emu_stride", C.c_int64), ("status", C.c_void_p), ("spin_limit", C.c_int64),
     ]

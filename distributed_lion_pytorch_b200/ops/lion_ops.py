@@ -86,7 +86,7 @@ def fused_step(p: torch.Tensor, g: torch.Tensor, m: torch.Tensor, *, world: int,
                vote: str = "majority", tie: str = "neg", live_mask: Optional[int] = None,
                wait_mask: Optional[int] = None, max_grad_norm: Optional[float] = None, seed: int = 0, step: int = 0,
                elem_base: int = 0, emulate_ranks: int = 0, emu_stride: int = 0, status: Optional[torch.Tensor] = None,
-               spin_limit: int = 0, n: Optional[int] = None) -> None:
+               spin_limit: int = 0, n: Optional[int] = None, mc_arena_ptr: int = 0) -> None:
     """Launch the fused sign-pack-exchange-vote-update kernel on ``n`` elements of p/g/m.
 
     ``arena_ptrs[r]`` / ``flag_ptrs[r]`` are device addresses of rank r's receive arena and
@@ -108,6 +108,7 @@ def fused_step(p: torch.Tensor, g: torch.Tensor, m: torch.Tensor, *, world: int,
     for r in range(world):
         a.arena[r] = int(arena_ptrs[r])
         a.flags[r] = int(flag_ptrs[r])
+    a.mc_arena = int(mc_arena_ptr) if mc_arena_ptr else None
     a.arena_words, a.grid = int(arena_words), int(grid)
     a.emulate_ranks, a.emu_stride = int(emulate_ranks), int(emu_stride)
     a.status = status.data_ptr() if status is not None else None

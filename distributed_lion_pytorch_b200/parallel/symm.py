@@ -158,7 +158,18 @@ class FusedExchange:
                                 flag_ptrs=self.flags.ptrs, arena_words=self.arena_words, epoch=self.epoch,
                                 grid=grid, lr=lr, wd=wd, beta1=beta1, beta2=beta2, vote=vote, tie=tie,
                                 live_mask=live_mask, max_grad_norm=max_grad_norm, seed=seed, step=step_index,
-                                elem_base=off, status=self.status)
+                                elem_base=off, status=self.status, mc_arena_ptr=self._mc_ptr())
+
+    def _mc_ptr(self) -> int:
+        """NVLS multicast alias of the arena, when the fabric exposes one and DLION_MULTICAST allows it
+        (``1`` = use it, ``0`` = never; default ``0`` until validated on the target fabric)."""
+        if os.environ.get("DLION_MULTICAST", "0") != "1" or self.arena is None:
+            return 0
+        return int(getattr(self.arena, "multicast_ptr", 0) or 0)
+
+    @property
+    def uses_multicast(self) -> bool:
+        return self._mc_ptr() != 0
 
     def check_status(self) -> None:
         """Host-side health check (synchronises): raises if a flag wait timed out in any launch."""

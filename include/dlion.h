@@ -108,6 +108,8 @@ typedef struct {
   uint64_t epoch;
   uint32_t* arena[DLION_MAX_RANKS];
   uint64_t* flags[DLION_MAX_RANKS];
+  uint32_t* mc_arena;  /* optional NVLS multicast alias of the arenas (same layout on every rank): the packed
+                          words then leave the GPU once (multimem.st) and the switch replicates them; NULL = unicast */
   int64_t arena_words;
   int grid;            /* CTAs per (virtual) rank; identical on every rank */
   int emulate_ranks;

@@ -16,8 +16,10 @@ def _net(seed, dtype):
     return m.to(dtype)
 
 
-def _worker(rank, world, dtype_name, vote, tie, mask, steps, skew):
+def _worker(rank, world, dtype_name, vote, tie, mask, steps, skew, multicast=False):
+    import os
     import time
+    os.environ["DLION_MULTICAST"] = "1" if multicast else "0"
     from distributed_lion import Lion
     dtype = getattr(torch, dtype_name)
     dev = torch.device("cuda", rank)
@@ -41,7 +43,7 @@ def _worker(rank, world, dtype_name, vote, tie, mask, steps, skew):
     flat = {c: torch.cat([p.detach().float().flatten() for p in nets[c].parameters()]).cpu() for c in nets}
     mom = torch.cat([opts["fused"].state[p]["exp_avg"].float().flatten() for p in nets["fused"].parameters()]).cpu()
     return dict(fused=flat["fused"], split=flat["nccl_1bit"], mom=mom, backend=opts["fused"].backend_name,
-                how=opts["fused"]._backend._ctx.flags.how)
+                how=opts["fused"]._backend._ctx.flags.how, mc=opts["fused"]._backend._ctx.uses_multicast)
 
 
 @pytest.mark.parametrize("dtype", ["bfloat16", "float32"])
@@ -73,3 +75,15 @@ def test_auto_picks_fused_on_one_node():
     world = min(torch.cuda.device_count(), 8)
     outs = run_distributed(_worker_auto, world, backend="nccl", timeout=300)
     assert all(o == "fused" for o in outs)
+
+
+def test_fused_nvls_multicast_send_path():
+    """DLION_MULTICAST=1: the packed words leave the GPU once (multimem.st) and NVSwitch replicates
+    them into every arena.  Must give exactly the bits of the split path; skipped where the fabric
+    exposes no multicast pointer."""
+    world = min(torch.cuda.device_count(), 8)
+    outs = run_distributed(_worker, world, "bfloat16", "majority", "neg", None, 8, True, True, backend="nccl", timeout=300)
+    if not outs[0]["mc"]:
+        pytest.skip("no NVLS multicast pointer on this fabric")
+    for o in outs:
+        assert torch.equal(o["fused"], o["split"]) and torch.equal(o["fused"], outs[0]["fused"])
