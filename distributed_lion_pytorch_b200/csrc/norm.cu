@@ -31,13 +31,29 @@ __device__ __forceinline__ float block_allreduce_sum(float v, float* smem) {
   return v;
 }
 
+// Dropout fused into the residual add: keep-mask bits for the 8 elements of vector `vec` of the
+// whole [rows, cols] tensor, regenerated (not stored) in the backward from (seed, vec).  One
+// Philox4x32-10 call yields eight 16-bit uniforms; keep iff u16 >= p * 65536.
+__device__ __forceinline__ uint32_t keep_mask8(uint64_t seed, int64_t vec, uint32_t thr16) {
+  const uint4 r = Philox::gen(seed, (uint64_t)vec, 0x0d120u, 0u);
+  const uint32_t w[4] = {r.x, r.y, r.z, r.w};
+  uint32_t mask = 0;
+#pragma unroll
+  for (int i = 0; i < 4; ++i) {
+    mask |= ((w[i] & 0xffffu) >= thr16 ? 1u : 0u) << (2 * i);
+    mask |= ((w[i] >> 16) >= thr16 ? 1u : 0u) << (2 * i + 1);
+  }
+  return mask;
+}
+
 // Thread t owns vectors t, t+BLOCK, ... (VPT of them); vector j covers columns [8j, 8j+8).
-template <typename T, int VPT, int BLOCK, bool RMS>
+template <typename T, int VPT, int BLOCK, bool RMS, bool DROP>
 __global__ void __launch_bounds__(BLOCK) norm_fwd_kernel(const T* __restrict__ x, const T* __restrict__ res,
                                                          const T* __restrict__ w, const T* __restrict__ b,
                                                          T* __restrict__ y, T* __restrict__ sum_out,
                                                          float* __restrict__ mean_out, float* __restrict__ rstd_out,
-                                                         int64_t rows, int cols, float eps) {
+                                                         int64_t rows, int cols, float eps, float inv_keep,
+                                                         uint32_t thr16, uint64_t seed) {
   __shared__ float red[32];
   const int nvec = cols >> 3;
   float wv[VPT][8], bv[VPT][8];
@@ -63,6 +79,12 @@ __global__ void __launch_bounds__(BLOCK) norm_fwd_kernel(const T* __restrict__ x
       const int j = threadIdx.x + k * BLOCK;
       if (j < nvec) {
         load8<T>(xr + j * 8, s[k]);
+        if (DROP) {                                                         // y = dropout(x) in T, like unfused PyTorch
+          const uint32_t keep = keep_mask8(seed, row * nvec + j, thr16);
+#pragma unroll
+          for (int i = 0; i < 8; ++i) s[k][i] = ((keep >> i) & 1u) ? s[k][i] * inv_keep : 0.f;
+          round8<T>(s[k]);
+        }
         if (res != nullptr) {
           float r[8];
           load8<T>(res + row * cols + j * 8, r);
@@ -148,13 +170,14 @@ __device__ __forceinline__ void block_allreduce_sum_n(float (&v)[NV], float* sme
 // ROWS rows are processed per trip so that ROWS x (dy, xs, dsum) loads are in flight per thread
 // before the first block reduction: the kernel is latency-bound otherwise (cols = 768 leaves
 // only 96 threads per row).
-template <typename T, int VPT, int BLOCK, bool RMS, int ROWS>
+template <typename T, int VPT, int BLOCK, bool RMS, int ROWS, bool DROP>
 __global__ void __launch_bounds__(BLOCK) norm_bwd_kernel(const T* __restrict__ dy, const T* __restrict__ dsum_in,
                                                          const T* __restrict__ xs, const T* __restrict__ w,
                                                          const float* __restrict__ mean_in,
                                                          const float* __restrict__ rstd_in, T* __restrict__ dx,
-                                                         float* __restrict__ dw_part, float* __restrict__ db_part,
-                                                         int64_t rows, int cols) {
+                                                         T* __restrict__ dres, float* __restrict__ dw_part,
+                                                         float* __restrict__ db_part, int64_t rows, int cols,
+                                                         float inv_keep, uint32_t thr16, uint64_t seed) {
   __shared__ float red[2 * ROWS * 32];
   const int nvec = cols >> 3;
   float wv[VPT][8], dwv[VPT][8], dbv[VPT][8];
@@ -215,6 +238,12 @@ __global__ void __launch_bounds__(BLOCK) norm_bwd_kernel(const T* __restrict__ d
             o[i] = rstd[r] * (g[r][k][i] - mg - xh[r][k][i] * mgx);
             if (dsum_in != nullptr) o[i] += rs[r][k][i];
           }
+          if (DROP) {                       // d residual = o ; d x = o * keep / (1 - p)
+            if (dres != nullptr) store8<T>(dres + row * cols + j * 8, o);
+            const uint32_t keep = keep_mask8(seed, row * nvec + j, thr16);
+#pragma unroll
+            for (int i = 0; i < 8; ++i) o[i] = ((keep >> i) & 1u) ? o[i] * inv_keep : 0.f;
+          }
           store8<T>(dx + row * cols + j * 8, o);
         }
       }
@@ -259,34 +288,44 @@ __global__ void norm_bwd_finalize_kernel(const float* __restrict__ dw_part, cons
   }
 }
 
+struct DropArgs {
+  float inv_keep;
+  uint32_t thr16;
+  uint64_t seed;
+  bool on;
+};
+
 template <typename T, int VPT, int BLOCK>
 static int launch_fwd(const void* x, const void* res, const void* w, const void* b, void* y, void* sum_out,
-                      float* mean, float* rstd, int64_t rows, int cols, float eps, int rms, cudaStream_t s) {
+                      float* mean, float* rstd, int64_t rows, int cols, float eps, int rms, DropArgs d,
+                      cudaStream_t s) {
   const int64_t cap = (int64_t)kNumSMs * (2048 / BLOCK);
   const int grid = (int)(rows < cap ? rows : cap);
-  if (rms)
-    norm_fwd_kernel<T, VPT, BLOCK, true><<<grid, BLOCK, 0, s>>>((const T*)x, (const T*)res, (const T*)w, nullptr,
-                                                                (T*)y, (T*)sum_out, mean, rstd, rows, cols, eps);
-  else
-    norm_fwd_kernel<T, VPT, BLOCK, false><<<grid, BLOCK, 0, s>>>((const T*)x, (const T*)res, (const T*)w,
-                                                                 (const T*)b, (T*)y, (T*)sum_out, mean, rstd, rows,
-                                                                 cols, eps);
+#define DLION_NORM_FWD(RMS_, DROP_)                                                                              \
+  norm_fwd_kernel<T, VPT, BLOCK, RMS_, DROP_><<<grid, BLOCK, 0, s>>>((const T*)x, (const T*)res, (const T*)w,      \
+                                                                     RMS_ ? nullptr : (const T*)b, (T*)y,          \
+                                                                     (T*)sum_out, mean, rstd, rows, cols, eps,     \
+                                                                     d.inv_keep, d.thr16, d.seed)
+  if (rms) { if (d.on) DLION_NORM_FWD(true, true); else DLION_NORM_FWD(true, false); }
+  else     { if (d.on) DLION_NORM_FWD(false, true); else DLION_NORM_FWD(false, false); }
+#undef DLION_NORM_FWD
   return DLION_LAUNCH_CHECK("dlion_norm_fwd");
 }
 
 template <typename T, int VPT, int BLOCK>
 static int launch_bwd(const void* dy, const void* dsum_in, const void* xs, const void* w, const float* mean,
-                      const float* rstd, void* dx, float* dwp, float* dbp, int64_t rows, int cols, int rms,
-                      cudaStream_t s) {
+                      const float* rstd, void* dx, void* dres, float* dwp, float* dbp, int64_t rows, int cols, int rms,
+                      DropArgs d, cudaStream_t s) {
   constexpr int ROWS = VPT == 1 ? 2 : 1;
   const int64_t trips = (rows + ROWS - 1) / ROWS;
   const int grid = (int)(trips < kNormBwdParts ? trips : kNormBwdParts);
-  if (rms)
-    norm_bwd_kernel<T, VPT, BLOCK, true, ROWS><<<grid, BLOCK, 0, s>>>(
-        (const T*)dy, (const T*)dsum_in, (const T*)xs, (const T*)w, mean, rstd, (T*)dx, dwp, dbp, rows, cols);
-  else
-    norm_bwd_kernel<T, VPT, BLOCK, false, ROWS><<<grid, BLOCK, 0, s>>>(
-        (const T*)dy, (const T*)dsum_in, (const T*)xs, (const T*)w, mean, rstd, (T*)dx, dwp, dbp, rows, cols);
+#define DLION_NORM_BWD(RMS_, DROP_)                                                                              \
+  norm_bwd_kernel<T, VPT, BLOCK, RMS_, ROWS, DROP_><<<grid, BLOCK, 0, s>>>(                                         \
+      (const T*)dy, (const T*)dsum_in, (const T*)xs, (const T*)w, mean, rstd, (T*)dx, (T*)dres, dwp, dbp, rows,    \
+      cols, d.inv_keep, d.thr16, d.seed)
+  if (rms) { if (d.on) DLION_NORM_BWD(true, true); else DLION_NORM_BWD(true, false); }
+  else     { if (d.on) DLION_NORM_BWD(false, true); else DLION_NORM_BWD(false, false); }
+#undef DLION_NORM_BWD
   return DLION_LAUNCH_CHECK("dlion_norm_bwd");
 }
 
@@ -307,14 +346,24 @@ static int launch_bwd(const void* dy, const void* dsum_in, const void* xs, const
 
 template <typename T>
 static int fwd_t(const void* x, const void* res, const void* w, const void* b, void* y, void* sum_out, float* mean,
-                 float* rstd, int64_t rows, int cols, float eps, int rms, cudaStream_t s) {
-  NORM_SHAPE_DISPATCH(launch_fwd, x, res, w, b, y, sum_out, mean, rstd, rows, cols, eps, rms, s);
+                 float* rstd, int64_t rows, int cols, float eps, int rms, DropArgs d, cudaStream_t s) {
+  NORM_SHAPE_DISPATCH(launch_fwd, x, res, w, b, y, sum_out, mean, rstd, rows, cols, eps, rms, d, s);
 }
 template <typename T>
 static int bwd_t(const void* dy, const void* dsum_in, const void* xs, const void* w, const float* mean,
-                 const float* rstd, void* dx, float* dwp, float* dbp, int64_t rows, int cols, int rms,
-                 cudaStream_t s) {
-  NORM_SHAPE_DISPATCH(launch_bwd, dy, dsum_in, xs, w, mean, rstd, dx, dwp, dbp, rows, cols, rms, s);
+                 const float* rstd, void* dx, void* dres, float* dwp, float* dbp, int64_t rows, int cols, int rms,
+                 DropArgs d, cudaStream_t s) {
+  NORM_SHAPE_DISPATCH(launch_bwd, dy, dsum_in, xs, w, mean, rstd, dx, dres, dwp, dbp, rows, cols, rms, d, s);
+}
+
+static DropArgs make_drop(float p, uint64_t seed) {
+  DropArgs d;
+  d.on = p > 0.f;
+  d.inv_keep = d.on ? 1.0f / (1.0f - p) : 1.0f;
+  float t = p * 65536.0f;
+  d.thr16 = t >= 65535.f ? 65535u : (uint32_t)(t + 0.5f);
+  d.seed = seed;
+  return d;
 }
 
 }  // namespace dlion
@@ -323,20 +372,23 @@ using namespace dlion;
 
 extern "C" int dlion_norm_fwd(const void* x, const void* residual, const void* weight, const void* bias, void* y,
                               void* sum_out, float* mean, float* rstd, int64_t rows, int cols, float eps, int rms,
-                              int dtype, void* stream) {
+                              float drop_p, uint64_t drop_seed, int dtype, void* stream) {
   DLION_CHECK_ARG(rows >= 0 && cols > 0 && (cols & 7) == 0, "dlion_norm_fwd: cols (%d) must be a positive multiple of 8",
                   cols);
   DLION_CHECK_ARG(aligned16(x) && aligned16(y) && aligned16(weight) && aligned16(residual) && aligned16(sum_out) &&
                       aligned16(bias),
                   "dlion_norm_fwd: pointers must be 16-byte aligned");
   DLION_CHECK_ARG(rstd != nullptr && (rms || mean != nullptr), "dlion_norm_fwd: mean/rstd outputs required");
+  DLION_CHECK_ARG(drop_p >= 0.f && drop_p < 1.f, "dlion_norm_fwd: dropout probability %f outside [0, 1)", drop_p);
+  DLION_CHECK_ARG(drop_p == 0.f || sum_out != nullptr, "dlion_norm_fwd: dropout needs sum_out (the pre-norm stream)");
   if (rows == 0) return 0;
   cudaStream_t s = (cudaStream_t)stream;
+  const DropArgs d = make_drop(drop_p, drop_seed);
   switch (dtype) {
-    case DLION_F32: return fwd_t<float>(x, residual, weight, bias, y, sum_out, mean, rstd, rows, cols, eps, rms, s);
+    case DLION_F32: return fwd_t<float>(x, residual, weight, bias, y, sum_out, mean, rstd, rows, cols, eps, rms, d, s);
     case DLION_BF16:
-      return fwd_t<__nv_bfloat16>(x, residual, weight, bias, y, sum_out, mean, rstd, rows, cols, eps, rms, s);
-    case DLION_F16: return fwd_t<__half>(x, residual, weight, bias, y, sum_out, mean, rstd, rows, cols, eps, rms, s);
+      return fwd_t<__nv_bfloat16>(x, residual, weight, bias, y, sum_out, mean, rstd, rows, cols, eps, rms, d, s);
+    case DLION_F16: return fwd_t<__half>(x, residual, weight, bias, y, sum_out, mean, rstd, rows, cols, eps, rms, d, s);
   }
   set_error("dlion_norm_fwd: unsupported dtype %d", dtype);
   return DLION_E_UNSUPPORTED;
@@ -351,23 +403,27 @@ extern "C" int dlion_norm_bwd_parts(int64_t rows, int cols) {
 }
 
 extern "C" int dlion_norm_bwd(const void* dy, const void* dsum_in, const void* xsum, const void* weight,
-                              const float* mean, const float* rstd, void* dx, float* dw_partial, float* db_partial,
-                              int64_t rows, int cols, int rms, int dtype, void* stream) {
+                              const float* mean, const float* rstd, void* dx, void* dres, float* dw_partial,
+                              float* db_partial, int64_t rows, int cols, int rms, float drop_p, uint64_t drop_seed,
+                              int dtype, void* stream) {
   DLION_CHECK_ARG(rows >= 0 && cols > 0 && (cols & 7) == 0, "dlion_norm_bwd: cols (%d) must be a positive multiple of 8",
                   cols);
   DLION_CHECK_ARG(aligned16(dy) && aligned16(dsum_in) && aligned16(xsum) && aligned16(weight) && aligned16(dx) &&
-                      aligned16(dw_partial) && aligned16(db_partial),
+                      aligned16(dres) && aligned16(dw_partial) && aligned16(db_partial),
                   "dlion_norm_bwd: pointers must be 16-byte aligned");
+  DLION_CHECK_ARG(drop_p >= 0.f && drop_p < 1.f, "dlion_norm_bwd: dropout probability %f outside [0, 1)", drop_p);
   if (rows == 0) return 0;
   cudaStream_t s = (cudaStream_t)stream;
+  const DropArgs d = make_drop(drop_p, drop_seed);
   switch (dtype) {
     case DLION_F32:
-      return bwd_t<float>(dy, dsum_in, xsum, weight, mean, rstd, dx, dw_partial, db_partial, rows, cols, rms, s);
+      return bwd_t<float>(dy, dsum_in, xsum, weight, mean, rstd, dx, dres, dw_partial, db_partial, rows, cols, rms, d, s);
     case DLION_BF16:
-      return bwd_t<__nv_bfloat16>(dy, dsum_in, xsum, weight, mean, rstd, dx, dw_partial, db_partial, rows, cols, rms,
-                                  s);
+      return bwd_t<__nv_bfloat16>(dy, dsum_in, xsum, weight, mean, rstd, dx, dres, dw_partial, db_partial, rows, cols,
+                                  rms, d, s);
     case DLION_F16:
-      return bwd_t<__half>(dy, dsum_in, xsum, weight, mean, rstd, dx, dw_partial, db_partial, rows, cols, rms, s);
+      return bwd_t<__half>(dy, dsum_in, xsum, weight, mean, rstd, dx, dres, dw_partial, db_partial, rows, cols, rms, d,
+                           s);
   }
   set_error("dlion_norm_bwd: unsupported dtype %d", dtype);
   return DLION_E_UNSUPPORTED;

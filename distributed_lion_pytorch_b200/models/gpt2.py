@@ -81,8 +81,9 @@ class LayerNormParams(nn.Module):
         self.bias = nn.Parameter(torch.zeros(n))
         self.eps = eps
 
-    def forward(self, x, residual=None):
-        return add_layer_norm(x, residual, self.weight, self.bias, self.eps)
+    def forward(self, x, residual=None, dropout_p: float = 0.0):
+        """LayerNorm(dropout(x) + residual); the dropout of the branch output is fused in."""
+        return add_layer_norm(x, residual, self.weight, self.bias, self.eps, dropout_p, self.training)
 
 
 class GPT2Attention(nn.Module):
@@ -125,17 +126,14 @@ class GPT2Block(nn.Module):
         self.mlp = GPT2MLP(cfg)
         self.resid_pdrop = cfg.resid_pdrop
 
-    def forward(self, hidden, residual, attn_mask=None):
-        """(branch output, residual stream) in → same out; the add lives inside the norm kernel."""
-        x, residual = self.ln_1(hidden, residual)
+    def forward(self, hidden, residual, attn_mask=None, in_dropout: float = 0.0):
+        """(branch output, residual stream) in → same out.  The residual add AND the dropout of the
+        incoming branch output live inside the norm kernel; this block's own MLP output is returned
+        un-dropped and is dropped by whoever normalises it next (the next block's ln_1, or ln_f)."""
+        x, residual = self.ln_1(hidden, residual, in_dropout)
         a = self.attn(x, attn_mask)
-        if self.training and self.resid_pdrop > 0:
-            a = F.dropout(a, self.resid_pdrop, True)
-        x, residual = self.ln_2(a, residual)
-        m = self.mlp(x)
-        if self.training and self.resid_pdrop > 0:
-            m = F.dropout(m, self.resid_pdrop, True)
-        return m, residual
+        x, residual = self.ln_2(a, residual, self.resid_pdrop)
+        return self.mlp(x), residual
 
 
 class GPT2Model(nn.Module):
@@ -183,19 +181,19 @@ class GPT2LMHeadModel(nn.Module, PreTrainedMixin):
         t = self.transformer
         pos = torch.arange(S, device=input_ids.device)
         h = t.wte(input_ids) + t.wpe(pos)
-        if self.training and t.embd_pdrop > 0:
-            h = F.dropout(h, t.embd_pdrop, True)
         mask = None
         if attention_mask is not None and not bool(attention_mask.all()):
             causal = torch.ones(S, S, dtype=torch.bool, device=h.device).tril()
             mask = causal[None, None] & attention_mask[:, None, None, :].bool()
         hidden, residual = h, None
+        p_in = t.embd_pdrop                      # layer 0 drops the embedding sum, later layers the previous MLP output
         for blk in t.h:
             if self.gradient_checkpointing and self.training:
-                hidden, residual = checkpoint(blk, hidden, residual, mask, use_reentrant=False)
+                hidden, residual = checkpoint(blk, hidden, residual, mask, p_in, use_reentrant=False)
             else:
-                hidden, residual = blk(hidden, residual, mask)
-        out, _ = t.ln_f(hidden, residual)
+                hidden, residual = blk(hidden, residual, mask, p_in)
+            p_in = blk.resid_pdrop
+        out, _ = t.ln_f(hidden, residual, p_in)
         return out
 
     def forward(self, input_ids, labels=None, attention_mask=None, return_logits: Optional[bool] = None, **_):

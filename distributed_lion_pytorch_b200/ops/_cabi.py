@@ -70,8 +70,8 @@ def _declare(L: C.CDLL) -> None:
         "dlion_multi_gather": [C.POINTER(vp), C.POINTER(vp), C.POINTER(i64), i32, i32, i32, vp],
         "dlion_sumsq": [vp, i64, i32, vp, vp, vp],
         "dlion_clip_scale": [vp, i64, i32, vp, f32, vp],
-        "dlion_norm_fwd": [vp, vp, vp, vp, vp, vp, vp, vp, i64, i32, f32, i32, i32, vp],
-        "dlion_norm_bwd": [vp, vp, vp, vp, vp, vp, vp, vp, vp, i64, i32, i32, i32, vp],
+        "dlion_norm_fwd": [vp, vp, vp, vp, vp, vp, vp, vp, i64, i32, f32, i32, f32, u64, i32, vp],
+        "dlion_norm_bwd": [vp, vp, vp, vp, vp, vp, vp, vp, vp, vp, i64, i32, i32, f32, u64, i32, vp],
         "dlion_norm_bwd_parts": [i64, i32],
         "dlion_norm_bwd_finalize": [vp, vp, vp, vp, i32, i32, i32, vp],
         "dlion_colsum_parts": [i64, i32],

@@ -24,7 +24,7 @@ import torch.nn.functional as F
 from . import _cabi, require_library
 
 IGNORE_INDEX = -100
-_DEFAULT_CHUNK = 4096
+_DEFAULT_CHUNK = int(os.environ.get("DLION_CE_CHUNK", "4096"))   # rows of logits alive at a time
 
 
 def _pad_rows(weight: torch.Tensor, mult: int = 64) -> torch.Tensor:

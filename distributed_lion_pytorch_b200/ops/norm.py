@@ -22,22 +22,24 @@ def _use_kernel(x: torch.Tensor) -> bool:
 
 class _FusedNorm(torch.autograd.Function):
     @staticmethod
-    def forward(ctx, x, residual, weight, bias, eps: float, rms: bool):
+    def forward(ctx, x, residual, weight, bias, eps: float, rms: bool, drop_p: float, seed: int):
         cols = x.shape[-1]
         xc = x.contiguous()
         rc = residual.contiguous() if residual is not None else None
         rows = xc.numel() // cols
         y = torch.empty_like(xc)
-        summed = torch.empty_like(xc) if rc is not None else xc
+        summed = torch.empty_like(xc) if (rc is not None or drop_p > 0) else xc
         mean = torch.empty(rows, dtype=torch.float32, device=x.device) if not rms else None
         rstd = torch.empty(rows, dtype=torch.float32, device=x.device)
         with torch.cuda.device(x.device):
             _cabi.check(_cabi.lib().dlion_norm_fwd(
                 xc.data_ptr(), _cabi.ptr(rc), weight.data_ptr(), _cabi.ptr(bias), y.data_ptr(),
-                summed.data_ptr() if rc is not None else None, _cabi.ptr(mean), rstd.data_ptr(), rows, cols,
-                float(eps), int(rms), _cabi.dtype_code(x.dtype), _cabi.stream_ptr(x.device)), "norm_fwd")
+                summed.data_ptr() if summed is not xc else None, _cabi.ptr(mean), rstd.data_ptr(), rows, cols,
+                float(eps), int(rms), float(drop_p), int(seed), _cabi.dtype_code(x.dtype),
+                _cabi.stream_ptr(x.device)), "norm_fwd")
         ctx.save_for_backward(summed, weight, mean, rstd)
         ctx.rms, ctx.has_res, ctx.has_bias = rms, residual is not None, bias is not None
+        ctx.drop_p, ctx.seed = float(drop_p), int(seed)
         ctx.set_materialize_grads(False)      # an unused residual output costs nothing in backward
         return y, summed
 
@@ -53,6 +55,8 @@ class _FusedNorm(torch.autograd.Function):
         L = _cabi.lib()
         parts = int(L.dlion_norm_bwd_parts(rows, cols))
         dx = torch.empty_like(summed)
+        drop = ctx.drop_p > 0
+        dres = torch.empty_like(summed) if (drop and ctx.has_res) else None
         dwp = torch.empty(parts, cols, dtype=torch.float32, device=dy.device)
         dbp = torch.empty(parts, cols, dtype=torch.float32, device=dy.device) if ctx.has_bias else None
         dw = torch.empty_like(weight)
@@ -60,15 +64,28 @@ class _FusedNorm(torch.autograd.Function):
         with torch.cuda.device(dy.device):
             st = _cabi.stream_ptr(dy.device)
             _cabi.check(L.dlion_norm_bwd(dyc.data_ptr(), _cabi.ptr(dsc), summed.data_ptr(), weight.data_ptr(),
-                                         _cabi.ptr(mean), rstd.data_ptr(), dx.data_ptr(), dwp.data_ptr(),
-                                         _cabi.ptr(dbp), rows, cols, int(ctx.rms), _cabi.dtype_code(dy.dtype), st),
-                        "norm_bwd")
+                                         _cabi.ptr(mean), rstd.data_ptr(), dx.data_ptr(), _cabi.ptr(dres),
+                                         dwp.data_ptr(), _cabi.ptr(dbp), rows, cols, int(ctx.rms), ctx.drop_p, ctx.seed,
+                                         _cabi.dtype_code(dy.dtype), st), "norm_bwd")
             _cabi.check(L.dlion_norm_bwd_finalize(dwp.data_ptr(), _cabi.ptr(dbp), dw.data_ptr(), _cabi.ptr(db),
                                                   parts, cols, _cabi.dtype_code(weight.dtype), st), "norm_bwd_finalize")
-        return dx, (dx if ctx.has_res else None), dw, db, None, None
+        if ctx.has_res:
+            g_res = dres if drop else dx
+        else:
+            g_res = None
+        return dx, g_res, dw, db, None, None, None, None
 
 
-def _ref_norm(x, residual, weight, bias, eps, rms):
+def _draw_seed() -> int:
+    """Seed for the in-kernel dropout mask, drawn from torch's CPU generator: cheap, reproducible
+    under ``set_seed`` / checkpointed RNG state, and replayed identically by activation
+    checkpointing (which restores the generator before recomputing)."""
+    return int(torch.randint(0, 2 ** 62, (1,)).item())
+
+
+def _ref_norm(x, residual, weight, bias, eps, rms, drop_p=0.0):
+    if drop_p > 0:
+        x = torch.nn.functional.dropout(x, drop_p, True)
     s = x if residual is None else x + residual
     if rms:
         h = s.float()
@@ -78,14 +95,18 @@ def _ref_norm(x, residual, weight, bias, eps, rms):
 
 
 def add_layer_norm(x: torch.Tensor, residual: Optional[torch.Tensor], weight: torch.Tensor,
-                   bias: Optional[torch.Tensor], eps: float = 1e-5) -> Tuple[torch.Tensor, torch.Tensor]:
+                   bias: Optional[torch.Tensor], eps: float = 1e-5, dropout_p: float = 0.0,
+                   training: bool = False) -> Tuple[torch.Tensor, torch.Tensor]:
+    """``s = dropout(x) + residual``; returns ``(LayerNorm(s), s)``.  One kernel on CUDA."""
+    p = float(dropout_p) if training else 0.0
     if _use_kernel(x):
-        return _FusedNorm.apply(x, residual, weight, bias, eps, False)
-    return _ref_norm(x, residual, weight, bias, eps, False)
+        return _FusedNorm.apply(x, residual, weight, bias, eps, False, p, _draw_seed() if p > 0 else 0)
+    return _ref_norm(x, residual, weight, bias, eps, False, p)
 
 
 def add_rms_norm(x: torch.Tensor, residual: Optional[torch.Tensor], weight: torch.Tensor,
-                 eps: float = 1e-5) -> Tuple[torch.Tensor, torch.Tensor]:
+                 eps: float = 1e-5, dropout_p: float = 0.0, training: bool = False) -> Tuple[torch.Tensor, torch.Tensor]:
+    p = float(dropout_p) if training else 0.0
     if _use_kernel(x):
-        return _FusedNorm.apply(x, residual, weight, None, eps, True)
-    return _ref_norm(x, residual, weight, None, eps, True)
+        return _FusedNorm.apply(x, residual, weight, None, eps, True, p, _draw_seed() if p > 0 else 0)
+    return _ref_norm(x, residual, weight, None, eps, True, p)

@@ -156,23 +156,27 @@ int dlion_clip_scale(void* x, int64_t n, int dtype, const float* sumsq, float ma
 
 /* ---------------------------------------------------------------- model kernels */
 
-/* N3 — y = LayerNorm(x + residual) (residual may be NULL); also writes the pre-norm sum to
- * `sum_out` (may alias nothing or be NULL when residual is NULL) and saves mean/rstd (fp32,
- * one per row).  RMSNorm when `bias == NULL && rms != 0`.
- * reference: HF GPT2Block / LlamaDecoderLayer reached via async_trainer.py:24. */
+/* N3 — y = LayerNorm(dropout(x) + residual) (residual may be NULL; drop_p = 0 disables dropout); also
+ * writes the pre-norm sum to `sum_out` (may be NULL only when residual is NULL and drop_p = 0) and
+ * saves mean/rstd (fp32, one per row).  RMSNorm when `rms != 0` (bias ignored).  The dropout
+ * keep-mask is a pure function of (drop_seed, element index): it is regenerated, not stored.
+ * reference: HF GPT2Block / LlamaDecoderLayer reached via async_trainer.py:24 — resid_dropout,
+ * the residual add and ln_1 / ln_2 are three ATen kernels and a mask tensor there. */
 int dlion_norm_fwd(const void* x, const void* residual, const void* weight, const void* bias, void* y,
                    void* sum_out, float* mean, float* rstd, int64_t rows, int cols, float eps, int rms,
-                   int dtype, void* stream);
-/* backward: dx (and d residual, identical) = norm-backward(dy) + dsum_in (may be NULL);
- * dweight/dbias partials are accumulated in fp32 `dw_partial`/`db_partial` of shape
- * [dlion_norm_bwd_parts(rows, cols), cols] (one row per CTA launched, at most
- * dlion_norm_bwd_partial_rows()); reduce them with dlion_norm_bwd_finalize(parts = that count). */
+                   float drop_p, uint64_t drop_seed, int dtype, void* stream);
+/* backward: d(sum) = norm-backward(dy) + dsum_in (may be NULL).  Without dropout dx = d(sum) (it is
+ * also the residual's gradient).  With dropout dres (may be NULL) receives d(sum) and
+ * dx = d(sum) * keep / (1 - p).  dweight/dbias partials are accumulated in fp32
+ * `dw_partial`/`db_partial` of shape [dlion_norm_bwd_parts(rows, cols), cols] (one row per CTA
+ * launched, at most dlion_norm_bwd_partial_rows()); reduce them with dlion_norm_bwd_finalize. */
 int dlion_norm_bwd_partial_rows(void);
 /* number of partial rows dlion_norm_bwd writes for this shape (= CTAs it launches) */
 int dlion_norm_bwd_parts(int64_t rows, int cols);
 int dlion_norm_bwd(const void* dy, const void* dsum_in, const void* xsum, const void* weight,
-                   const float* mean, const float* rstd, void* dx, float* dw_partial, float* db_partial,
-                   int64_t rows, int cols, int rms, int dtype, void* stream);
+                   const float* mean, const float* rstd, void* dx, void* dres, float* dw_partial,
+                   float* db_partial, int64_t rows, int cols, int rms, float drop_p, uint64_t drop_seed,
+                   int dtype, void* stream);
 int dlion_norm_bwd_finalize(const float* dw_partial, const float* db_partial, void* dweight, void* dbias,
                             int parts, int cols, int dtype, void* stream);
 

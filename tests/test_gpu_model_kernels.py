@@ -184,3 +184,47 @@ def test_fused_linear_accumulates_into_existing_grads(dtype, in_out, with_bias):
         assert torch.allclose(b.grad.float(), 1 + 2 * bf.grad, **t)
     cs = column_sum(dy.reshape(-1, cout), torch.float32)
     assert torch.allclose(cs, dy.reshape(-1, cout).float().sum(0), rtol=1e-3, atol=1e-2)
+
+
+@pytest.mark.parametrize("dtype", [torch.float32, torch.bfloat16])
+@pytest.mark.parametrize("rms,with_res,cols", [(False, True, 768), (False, False, 768), (True, True, 4096)])
+def test_add_norm_with_fused_dropout(dtype, rms, with_res, cols):
+    """dropout(x) + residual + norm in one kernel: the keep-mask is regenerated from the seed in
+    the backward.  The mask is recovered from the kernel's own output and the op is then compared
+    with plain autograd using that fixed mask."""
+    from distributed_lion_pytorch_b200.ops.norm import _FusedNorm
+    torch.manual_seed(1)
+    rows, p, seed = 512, 0.3, 12345
+    x = (torch.randn(rows, cols, device="cuda") + 8.0).to(dtype).requires_grad_()       # kept values stay far from zero
+    r = torch.randn(rows, cols, device="cuda").to(dtype).requires_grad_() if with_res else None
+    w = (1 + 0.1 * torch.randn(cols, device="cuda")).to(dtype).requires_grad_()
+    b = None if rms else (0.1 * torch.randn(cols, device="cuda")).to(dtype).requires_grad_()
+    y, s = _FusedNorm.apply(x, r, w, b, 1e-5, rms, p, seed)
+    y2, s2 = _FusedNorm.apply(x.detach(), None if r is None else r.detach(), w.detach(), None if b is None else b.detach(),
+                              1e-5, rms, p, seed)
+    assert torch.equal(y, y2) and torch.equal(s, s2)                                     # same seed, same mask
+    y3, _ = _FusedNorm.apply(x.detach(), None if r is None else r.detach(), w.detach(), None if b is None else b.detach(),
+                             1e-5, rms, p, seed + 1)
+    assert not torch.equal(y, y3)
+    base = s.detach().float() - (r.detach().float() if with_res else 0)
+    keep = base.abs() > (0.5 if dtype == torch.bfloat16 else 1e-3)                        # x ~ N(8,1)/0.7: kept values are large
+    frac = keep.float().mean().item()
+    assert abs(frac - (1 - p)) < 0.01, frac
+    dy, ds = torch.randn_like(y), torch.randn_like(y)
+    (y.float() * dy.float()).sum().add((s.float() * ds.float()).sum()).backward()
+    xf, wf = x.detach().float().requires_grad_(), w.detach().float().requires_grad_()
+    rf = r.detach().float().requires_grad_() if with_res else None
+    bf = b.detach().float().requires_grad_() if b is not None else None
+    xd = xf * keep.float() / (1 - p)
+    sf = xd + rf if with_res else xd
+    if rms:
+        yf = wf * (sf * torch.rsqrt(sf.pow(2).mean(-1, keepdim=True) + 1e-5))
+    else:
+        yf = F.layer_norm(sf, (cols,), wf, bf, 1e-5)
+    (yf * dy.float()).sum().add((sf * ds.float()).sum()).backward()
+    t = dict(rtol=3e-2, atol=6e-2) if dtype == torch.bfloat16 else dict(rtol=1e-4, atol=1e-4)
+    assert torch.allclose(y.float(), yf, **t)
+    assert torch.allclose(x.grad.float(), xf.grad, **t)
+    assert (x.grad[~keep] == 0).all()                                                     # dropped inputs get no gradient
+    if with_res:
+        assert torch.allclose(r.grad.float(), rf.grad, **t)
