@@ -9,6 +9,8 @@
 // reference: the HF GPT2Block (ln_1 / ln_2 around residual adds) and LlamaDecoderLayer
 // (input_layernorm / post_attention_layernorm) that the reference reaches through
 // Trainer.compute_loss (async_trainer.py:24,52,80) as separate add + layer_norm ATen kernels.
+#include <stdlib.h>
+
 #include "common.cuh"
 
 namespace dlion {
@@ -32,16 +34,23 @@ __device__ __forceinline__ float block_allreduce_sum(float v, float* smem) {
 }
 
 // Dropout fused into the residual add: keep-mask bits for the 8 elements of vector `vec` of the
-// whole [rows, cols] tensor, regenerated (not stored) in the backward from (seed, vec).  One
-// Philox4x32-10 call yields eight 16-bit uniforms; keep iff u16 >= p * 65536.
+// whole [rows, cols] tensor, regenerated (not stored) in the backward from (seed, vec): keep iff a
+// 16-bit uniform >= p * 65536.
+__device__ __forceinline__ uint32_t mix32(uint32_t x) {   // "lowbias32" integer hash: full avalanche in 5 ops
+  x ^= x >> 16; x *= 0x7feb352du; x ^= x >> 15; x *= 0x846ca68bu; x ^= x >> 16;
+  return x;
+}
 __device__ __forceinline__ uint32_t keep_mask8(uint64_t seed, int64_t vec, uint32_t thr16) {
-  const uint4 r = Philox::gen(seed, (uint64_t)vec, 0x0d120u, 0u);
-  const uint32_t w[4] = {r.x, r.y, r.z, r.w};
+  // four counter-based 32-bit hashes -> eight 16-bit uniforms (Philox4x32-10 here made the norm
+  // kernels issue-bound: ~70 instructions per 8 elements against ~25 for this)
+  const uint32_t lo = (uint32_t)seed, hi = (uint32_t)(seed >> 32);
+  const uint32_t base = mix32((uint32_t)vec * 0x9E3779B9u + lo) ^ mix32((uint32_t)(vec >> 32) + hi);
   uint32_t mask = 0;
 #pragma unroll
   for (int i = 0; i < 4; ++i) {
-    mask |= ((w[i] & 0xffffu) >= thr16 ? 1u : 0u) << (2 * i);
-    mask |= ((w[i] >> 16) >= thr16 ? 1u : 0u) << (2 * i + 1);
+    const uint32_t w = mix32(base + (uint32_t)i * 0x85EBCA6Bu + hi);
+    mask |= ((w & 0xffffu) >= thr16 ? 1u : 0u) << (2 * i);
+    mask |= ((w >> 16) >= thr16 ? 1u : 0u) << (2 * i + 1);
   }
   return mask;
 }
@@ -312,19 +321,41 @@ static int launch_fwd(const void* x, const void* res, const void* w, const void*
   return DLION_LAUNCH_CHECK("dlion_norm_fwd");
 }
 
+static int tuning(const char* name, int dflt) {
+  const char* v = getenv(name);
+  return v ? atoi(v) : dflt;
+}
+static int bwd_rows_per_trip(int cols) {           // VPT == 1 shapes can afford 2 rows of registers
+  static const int forced = tuning("DLION_NORM_BWD_ROWS", 0);
+  if ((cols >> 3) > 256) return 1;
+  return forced == 1 || forced == 2 ? forced : 2;
+}
+static int bwd_max_parts() {
+  static const int mult = tuning("DLION_NORM_BWD_PARTS_PER_SM", 8);
+  const int m = mult < 1 ? 1 : (mult > 16 ? 16 : mult);
+  return kNumSMs * m;
+}
+
 template <typename T, int VPT, int BLOCK>
 static int launch_bwd(const void* dy, const void* dsum_in, const void* xs, const void* w, const float* mean,
                       const float* rstd, void* dx, void* dres, float* dwp, float* dbp, int64_t rows, int cols, int rms,
                       DropArgs d, cudaStream_t s) {
-  constexpr int ROWS = VPT == 1 ? 2 : 1;
-  const int64_t trips = (rows + ROWS - 1) / ROWS;
-  const int grid = (int)(trips < kNormBwdParts ? trips : kNormBwdParts);
-#define DLION_NORM_BWD(RMS_, DROP_)                                                                              \
-  norm_bwd_kernel<T, VPT, BLOCK, RMS_, ROWS, DROP_><<<grid, BLOCK, 0, s>>>(                                         \
+  const int rows_per_trip = bwd_rows_per_trip(cols);
+  const int64_t trips = (rows + rows_per_trip - 1) / rows_per_trip;
+  const int cap = bwd_max_parts();
+  const int grid = (int)(trips < cap ? trips : cap);
+#define DLION_NORM_BWD(RMS_, DROP_, ROWS_)                                                                        \
+  norm_bwd_kernel<T, VPT, BLOCK, RMS_, ROWS_, DROP_><<<grid, BLOCK, 0, s>>>(                                        \
       (const T*)dy, (const T*)dsum_in, (const T*)xs, (const T*)w, mean, rstd, (T*)dx, (T*)dres, dwp, dbp, rows,    \
       cols, d.inv_keep, d.thr16, d.seed)
-  if (rms) { if (d.on) DLION_NORM_BWD(true, true); else DLION_NORM_BWD(true, false); }
-  else     { if (d.on) DLION_NORM_BWD(false, true); else DLION_NORM_BWD(false, false); }
+#define DLION_NORM_BWD_R(RMS_, DROP_)                                                                            \
+  do {                                                                                                           \
+    if (VPT == 1 && rows_per_trip == 2) DLION_NORM_BWD(RMS_, DROP_, (VPT == 1 ? 2 : 1));                         \
+    else DLION_NORM_BWD(RMS_, DROP_, 1);                                                                         \
+  } while (0)
+  if (rms) { if (d.on) DLION_NORM_BWD_R(true, true); else DLION_NORM_BWD_R(true, false); }
+  else     { if (d.on) DLION_NORM_BWD_R(false, true); else DLION_NORM_BWD_R(false, false); }
+#undef DLION_NORM_BWD_R
 #undef DLION_NORM_BWD
   return DLION_LAUNCH_CHECK("dlion_norm_bwd");
 }
@@ -394,12 +425,13 @@ extern "C" int dlion_norm_fwd(const void* x, const void* residual, const void* w
   return DLION_E_UNSUPPORTED;
 }
 
-extern "C" int dlion_norm_bwd_partial_rows(void) { return kNormBwdParts; }
+extern "C" int dlion_norm_bwd_partial_rows(void) { return kNumSMs * 16; }
 
 extern "C" int dlion_norm_bwd_parts(int64_t rows, int cols) {
-  const int rows_per_trip = (cols >> 3) <= 256 ? 2 : 1;     // must mirror launch_bwd: ROWS = (VPT == 1 ? 2 : 1)
+  const int rows_per_trip = bwd_rows_per_trip(cols);        // must mirror launch_bwd
   const int64_t trips = (rows + rows_per_trip - 1) / rows_per_trip;
-  return (int)(trips < kNormBwdParts ? trips : kNormBwdParts);
+  const int cap = bwd_max_parts();
+  return (int)(trips < cap ? trips : cap);
 }
 
 extern "C" int dlion_norm_bwd(const void* dy, const void* dsum_in, const void* xsum, const void* weight,
