@@ -179,8 +179,16 @@ __device__ __forceinline__ void block_allreduce_sum_n(float (&v)[NV], float* sme
 // ROWS rows are processed per trip so that ROWS x (dy, xs, dsum) loads are in flight per thread
 // before the first block reduction: the kernel is latency-bound otherwise (cols = 768 leaves
 // only 96 threads per row).
+// Resident CTAs per SM the backward is compiled for: the kernel is latency-bound (ncu: 53 % of
+// stall samples on long scoreboard at 21 % warp occupancy when it was register-limited to 7
+// CTAs/SM and launched as 1.14 waves), so registers are capped for ~30 warps/SM and the grid is
+// exactly one wave.
+constexpr int bwd_ctas_per_sm(int vpt, int block) {
+  return vpt == 1 ? (1024 / block > 16 ? 16 : 1024 / block) : (vpt == 2 ? 3 : 2);
+}
+
 template <typename T, int VPT, int BLOCK, bool RMS, int ROWS, bool DROP>
-__global__ void __launch_bounds__(BLOCK) norm_bwd_kernel(const T* __restrict__ dy, const T* __restrict__ dsum_in,
+__global__ void __launch_bounds__(BLOCK, bwd_ctas_per_sm(VPT, BLOCK)) norm_bwd_kernel(const T* __restrict__ dy, const T* __restrict__ dsum_in,
                                                          const T* __restrict__ xs, const T* __restrict__ w,
                                                          const float* __restrict__ mean_in,
                                                          const float* __restrict__ rstd_in, T* __restrict__ dx,
@@ -325,15 +333,21 @@ static int tuning(const char* name, int dflt) {
   const char* v = getenv(name);
   return v ? atoi(v) : dflt;
 }
-static int bwd_rows_per_trip(int cols) {           // VPT == 1 shapes can afford 2 rows of registers
-  static const int forced = tuning("DLION_NORM_BWD_ROWS", 0);
+static int bwd_rows_per_trip(int cols) {           // 1 by default; 2 trades occupancy for loads in flight per thread
+  static const int forced = tuning("DLION_NORM_BWD_ROWS", 1);
   if ((cols >> 3) > 256) return 1;
-  return forced == 1 || forced == 2 ? forced : 2;
+  return forced == 2 ? 2 : 1;
 }
-static int bwd_max_parts() {
-  static const int mult = tuning("DLION_NORM_BWD_PARTS_PER_SM", 8);
-  const int m = mult < 1 ? 1 : (mult > 16 ? 16 : mult);
-  return kNumSMs * m;
+// mirrors NORM_SHAPE_DISPATCH: (VPT, BLOCK) for a column count
+static void norm_shape(int cols, int* vpt, int* block) {
+  const int nvec = cols >> 3;
+  *vpt = nvec <= 256 ? 1 : (nvec <= 512 ? 2 : 4);
+  *block = nvec <= 32 ? 32 : nvec <= 64 ? 64 : nvec <= 96 ? 96 : nvec <= 128 ? 128 : 256;
+}
+static int bwd_max_parts(int cols) {
+  int vpt, block;
+  norm_shape(cols, &vpt, &block);
+  return kNumSMs * bwd_ctas_per_sm(vpt, block);
 }
 
 template <typename T, int VPT, int BLOCK>
@@ -342,7 +356,7 @@ static int launch_bwd(const void* dy, const void* dsum_in, const void* xs, const
                       DropArgs d, cudaStream_t s) {
   const int rows_per_trip = bwd_rows_per_trip(cols);
   const int64_t trips = (rows + rows_per_trip - 1) / rows_per_trip;
-  const int cap = bwd_max_parts();
+  const int cap = kNumSMs * bwd_ctas_per_sm(VPT, BLOCK);
   const int grid = (int)(trips < cap ? trips : cap);
 #define DLION_NORM_BWD(RMS_, DROP_, ROWS_)                                                                        \
   norm_bwd_kernel<T, VPT, BLOCK, RMS_, ROWS_, DROP_><<<grid, BLOCK, 0, s>>>(                                        \
@@ -430,7 +444,7 @@ extern "C" int dlion_norm_bwd_partial_rows(void) { return kNumSMs * 16; }
 extern "C" int dlion_norm_bwd_parts(int64_t rows, int cols) {
   const int rows_per_trip = bwd_rows_per_trip(cols);        // must mirror launch_bwd
   const int64_t trips = (rows + rows_per_trip - 1) / rows_per_trip;
-  const int cap = bwd_max_parts();
+  const int cap = bwd_max_parts(cols);
   return (int)(trips < cap ? trips : cap);
 }
 
