@@ -258,6 +258,50 @@ class Lion(Optimizer):
             if stray:   # the checkpoint knows parameters we have not bucketed yet: re-plan at next step
                 self._buckets, self._bucket_sig = None, None
 
+    # ------------------------------------------------------------------ diagnostics
+    @torch.no_grad()
+    def vote_statistics(self, chunk_elems: int = 1 << 24) -> Dict[str, float]:
+        """Collective, off the hot path: what would the ballot of the CURRENT gradients look like?
+        Returns the fraction of coordinates that tie, that are unanimous, and the mean agreement
+        ``|2*cnt - L| / L`` (1 = every worker agrees, 0 = perfect split) — the observability the
+        reference lacks.  Uses the split path (pack → all_gather → count) on the
+        gradients currently held in ``p.grad``; does not modify parameters or momenta."""
+        self._resolve_backend()
+        self._ensure_buckets()
+        W = self.world_size
+        L = self.live_count()
+        live = self.live_mask
+        ties = unanimous = agree = total = 0.0
+        for b in self._buckets or []:
+            gather_grads(b, use_kernel=self._kernels_ok(b.device))
+            beta1 = float(self.param_groups[b.group_index]["betas"][0])
+            for off in range(0, b.numel, chunk_elems):
+                n = min(chunk_elems, b.numel - off)
+                bits = sem.local_bits(b.flat_m[off:off + n], b.flat_g[off:off + n], beta1)
+                mine = sem.pack_bits(bits)
+                if W > 1:
+                    gathered = torch.empty(W, mine.numel(), dtype=torch.uint8, device=mine.device)
+                    try:
+                        dist.all_gather_into_tensor(gathered.view(-1), mine, group=self.process_group)
+                    except (RuntimeError, NotImplementedError):
+                        dist.all_gather(list(gathered.unbind(0)), mine, group=self.process_group)
+                else:
+                    gathered = mine.unsqueeze(0)
+                cnt = sem.count_votes(gathered, n, live).to(torch.int32)
+                ties += float((cnt * 2 == L).sum())
+                unanimous += float(((cnt == 0) | (cnt == L)).sum())
+                agree += float((cnt * 2 - L).abs().sum()) / L
+                total += n
+            # alignment padding holds m = g = 0 on every rank: bit 0 everywhere, i.e. "unanimous" with
+            # agreement 1 and never a tie — take it out again so only real coordinates are reported
+            pad = b.numel - b.payload
+            unanimous -= pad
+            agree -= pad
+            total -= pad
+        total = max(total, 1.0)
+        return {"tie_fraction": ties / total, "unanimous_fraction": unanimous / total, "mean_agreement": agree / total,
+                "live_workers": float(L), "world_size": float(W)}
+
     # ------------------------------------------------------------------ helpers for backends
     def cpu_generator(self) -> torch.Generator:
         if self._cpu_gen is None:

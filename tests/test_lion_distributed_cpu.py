@@ -166,3 +166,25 @@ def test_functional_update_fn_distributed_matches_reference():
     assert all(o["same"] for o in outs)                                # bit-exact vs the reference, per tensor
     assert torch.equal(outs[0]["p_ref"], outs[1]["p_ref"])
     assert torch.equal(outs[0]["p_stoc"], outs[2]["p_stoc"])           # stochastic ballots still give one common update
+
+
+def _worker_vote_stats(rank, world):
+    from distributed_lion import Lion
+    p = torch.nn.Parameter(torch.zeros(1000))
+    opt = Lion([p], lr=1e-2)
+    # element i: ranks < (i % 5) vote +1, the others -1  ->  known counts
+    g = torch.where(torch.arange(1000) % 5 > rank, 1.0, -1.0)
+    p.grad = g.clone()
+    before = p.detach().clone()
+    st = opt.vote_statistics()
+    assert torch.equal(p.detach(), before)                      # a diagnostic: nothing moves
+    return st
+
+
+def test_vote_statistics_known_pattern():
+    outs = run_distributed(_worker_vote_stats, 4)
+    st = outs[0]
+    assert all(o == st for o in outs)
+    # counts cycle through 0,1,2,3,4 (of 4): ties at cnt=2 (1/5), unanimous at 0 and 4 (2/5)
+    assert abs(st["tie_fraction"] - 0.2) < 0.01 and abs(st["unanimous_fraction"] - 0.4) < 0.01
+    assert abs(st["mean_agreement"] - (1 + 0.5 + 0 + 0.5 + 1) / 5) < 0.01
