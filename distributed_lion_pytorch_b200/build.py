@@ -83,6 +83,26 @@ def build(force: bool = False, verbose: bool = False) -> Path:
     return LIB
 
 
+CPU_SRC = PKG / "csrc_cpu" / "cpu_ops.cpp"
+CPU_LIB = LIBDIR / "libdlion_cpu.so"
+
+
+def build_cpu(force: bool = False) -> Path:
+    """g++ -O3 -fopenmp build of the host-side codec/vote library (no CUDA involved)."""
+    if not force and CPU_LIB.exists() and CPU_LIB.stat().st_mtime >= CPU_SRC.stat().st_mtime:
+        return CPU_LIB
+    LIBDIR.mkdir(parents=True, exist_ok=True)
+    cxx = os.environ.get("CXX") or shutil.which("g++") or "g++"
+    base = [cxx, "-O3", "-std=c++17", "-fPIC", "-shared", str(CPU_SRC), "-o", str(CPU_LIB)]
+    r = subprocess.run(base[:5] + ["-fopenmp"] + base[5:], capture_output=True, text=True)
+    if r.returncode != 0:          # no libgomp on this image: the pragmas are then simply ignored
+        r = subprocess.run(base, capture_output=True, text=True)
+    if r.returncode != 0:
+        raise RuntimeError(f"g++ failed for cpu_ops.cpp:\n{r.stdout}\n{r.stderr}")
+    return CPU_LIB
+
+
 if __name__ == "__main__":
+    build_cpu(force="--force" in sys.argv)
     p = build(force="--force" in sys.argv, verbose="-v" in sys.argv)
     print(p)

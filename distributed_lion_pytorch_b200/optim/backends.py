@@ -88,15 +88,17 @@ class AllGatherBackend(_Backend):
                                seed=opt.seed, step=opt._steps_done, rank=opt.rank)
         else:
             gen = opt.cpu_generator() if opt.max_grad_norm is not None else None
+            from ..ops import cpu_ops
             bits = sem.local_bits(b.flat_m, b.flat_g, beta1, max_grad_norm=opt.max_grad_norm, generator=gen)
-            mine.copy_(sem.pack_bits(bits))
+            mine.copy_(cpu_ops.pack_bits(bits))
         self._all_gather(gathered, mine)
         L = opt.live_count()
         if kern:
             lion_ops.vote_update(b.flat_p, b.flat_g, b.flat_m, gathered, W, opt.live_mask, lr, wd, beta2,
                                  opt.vote, opt.tie)
         else:
-            cnt = sem.count_votes(gathered, b.numel, opt.live_mask)
+            from ..ops import cpu_ops
+            cnt = cpu_ops.count_votes(gathered, b.numel, opt.live_mask)
             sem.apply_vote_(b.flat_p, b.flat_g, b.flat_m, cnt, L, lr, wd, beta2, opt.vote, opt.tie)
 
 

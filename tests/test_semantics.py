@@ -111,3 +111,19 @@ def test_simulated_workers_stay_identical():
     for r in range(1, W):
         assert torch.equal(ps[0], ps[r])
     assert not torch.equal(ms[0], ms[1])     # momentum is per worker, never communicated
+
+
+@pytest.mark.parametrize("n", [1, 7, 8, 9, 63, 64, 65, 100003])
+def test_native_cpu_codec_matches_oracle(n):
+    from distributed_lion_pytorch_b200 import build
+    from distributed_lion_pytorch_b200.ops import cpu_ops
+    build.build_cpu()
+    assert cpu_ops.lib() is not None
+    g = torch.Generator().manual_seed(n)
+    for W, mask in ((1, None), (4, 0b1011), (8, None), (16, 0xF0F1)):
+        votes = [torch.rand(n, generator=g) > 0.5 for _ in range(W)]
+        packed = [cpu_ops.pack_bits(v) for v in votes]
+        for v, p in zip(votes, packed):
+            assert torch.equal(p, sem.pack_bits(v))
+        gathered = torch.stack(packed)
+        assert torch.equal(cpu_ops.count_votes(gathered, n, mask), sem.count_votes(gathered, n, mask))
