@@ -150,3 +150,55 @@ def test_bucket_ops():
         z = x.clone()
         bucket_ops.clip_scale_(z, ss, 1e9)                     # no clipping needed: untouched
         assert torch.equal(z, x)
+
+
+def _guarded(n, dtype, fill, guard=4096):
+    """A length-n view in the middle of a larger buffer whose margins hold a canary value."""
+    buf = torch.full((n + 2 * guard,), fill, dtype=dtype, device="cuda")
+    return buf, buf[guard:guard + n]
+
+
+def _canaries_intact(buf, n, fill, guard=4096):
+    return bool((buf[:guard] == fill).all()) and bool((buf[guard + n:] == fill).all())
+
+
+@pytest.mark.parametrize("dtype", DTYPES)
+def test_kernels_respect_buffer_bounds(dtype):
+    """compute-sanitizer is closed on this pool, so out-of-bounds writes are caught the slow way:
+    every output lives between canary margins that must survive the launch (ragged sizes included)."""
+    from distributed_lion_pytorch_b200.ops import bucket_ops, lion_ops
+    from distributed_lion_pytorch_b200.parallel.symm import EmulatedExchange
+    for n in (8, 1003, 4096 * 3 + 8 * 5):
+        pb, p = _guarded(n, dtype, 7.0)
+        mb, m = _guarded(n, dtype, 7.0)
+        g = torch.randn(n, device="cuda").to(dtype)
+        p.copy_(torch.randn(n, device="cuda"))
+        m.zero_()
+        lion_ops.local_step(p, g, m, 1e-3, 0.1, 0.9, 0.99)
+        wb, w = _guarded((n + 31) // 32 * 4, torch.uint8, 0x5A, guard=256)
+        lion_ops.sign_pack(m, g, 0.9, w)
+        gathered = torch.randint(0, 256, (4, (n + 31) // 32 * 4), dtype=torch.uint8, device="cuda")
+        lion_ops.vote_update(p, g, m, gathered, 4, None, 1e-3, 0.1, 0.99)
+        torch.cuda.synchronize()
+        assert _canaries_intact(pb, n, 7.0) and _canaries_intact(mb, n, 7.0)
+        assert bool((wb[:256] == 0x5A).all()) and bool((wb[256 + w.numel():] == 0x5A).all())
+    # fused kernel: stacked [W, n] buckets between canaries, arenas sized exactly
+    W = 4
+    n = lion_ops.fused_tile(dtype) * 37
+    Pb, Pf = _guarded(W * n, dtype, 7.0)
+    Mb, Mf = _guarded(W * n, dtype, 7.0)
+    P, M = Pf.view(W, n), Mf.view(W, n)
+    P.copy_(torch.randn(n, device="cuda").to(dtype).repeat(W, 1))
+    M.zero_()
+    G = torch.randn(W, n, device="cuda").to(dtype)
+    ex = EmulatedExchange(W, n, dtype, "cuda")
+    ex.step(P, G, M, 1e-3, 0.1, 0.9, 0.99, spin_limit=1 << 22)
+    torch.cuda.synchronize()
+    ex.check_status()
+    assert _canaries_intact(Pb, W * n, 7.0) and _canaries_intact(Mb, W * n, 7.0)
+    # clip / sumsq on a ragged tail
+    xb, x = _guarded(100003, dtype, 7.0)
+    x.copy_(torch.randn(100003, device="cuda"))
+    bucket_ops.clip_scale_(x, bucket_ops.sumsq(x), 0.5)
+    torch.cuda.synchronize()
+    assert _canaries_intact(xb, 100003, 7.0)
