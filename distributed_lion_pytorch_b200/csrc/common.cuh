@@ -63,8 +63,8 @@ struct DT<__half> {
   __device__ __forceinline__ static __half from_f(float x) { return __float2half_rn(x); }
 };
 
-// 8 consecutive elements <-> float[8].  Pointers must be 16-byte aligned for 2-byte types and
-// 32-byte... no: fp32 uses two 16-byte accesses, so 16-byte alignment suffices everywhere.
+// 8 consecutive elements <-> float[8].  Pointers must be 16-byte aligned (fp32 uses two 16-byte
+// accesses, the 2-byte types one).
 template <typename T>
 __device__ __forceinline__ void load8(const T* __restrict__ ptr, float (&v)[8]);
 template <typename T>
@@ -249,7 +249,7 @@ __device__ __forceinline__ uint32_t sign_byte(const float (&m)[8], const float (
 }
 
 // direction u for one element given the +1 count among L live workers
-__device__ __forceinline__ float vote_dir(int cnt, int L, float invL_unused, int vote) {
+__device__ __forceinline__ float vote_dir(int cnt, int L, int vote) {
   const int twice = 2 * cnt;
   if (vote == DLION_VOTE_AVERAGE) return __fdiv_rn((float)(twice - L), (float)L);
   if (vote == DLION_VOTE_MAJORITY_ZERO && twice == L) return 0.f;

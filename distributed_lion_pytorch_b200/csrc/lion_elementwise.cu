@@ -133,7 +133,7 @@ __global__ void __launch_bounds__(kThreads) vote_update_kernel(T* __restrict__ p
       for (int i = 0; i < 8; ++i) {
         const int cnt = ((c0 >> i) & 1) | (((c1 >> i) & 1) << 1) | (((c2 >> i) & 1) << 2) | (((c3 >> i) & 1) << 3) |
                         (((c4 >> i) & 1) << 4);
-        uf[i] = vote_dir(cnt, L, 0.f, vote);
+        uf[i] = vote_dir(cnt, L, vote);
       }
     } else {
       // bit-sliced comparison of the 8 counts with the (uniform) thresholds: one byte of

@@ -15,8 +15,6 @@
 
 namespace dlion {
 
-constexpr int kNormBwdParts = kNumSMs * 8;
-
 template <int BLOCK>
 __device__ __forceinline__ float block_allreduce_sum(float v, float* smem) {
 #pragma unroll

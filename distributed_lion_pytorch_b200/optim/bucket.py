@@ -54,9 +54,6 @@ class Bucket:
     def wire_bytes(self) -> int:
         return self.numel // 8
 
-    def signature(self):
-        return (self.group_index, self.dtype, str(self.device), tuple(id(p) for p in self.params))
-
 
 def plan_offsets(numels: List[int]) -> (List[int], int):
     offs, cur = [], 0
@@ -67,7 +64,7 @@ def plan_offsets(numels: List[int]) -> (List[int], int):
 
 
 def build_bucket(group_index: int, params: List[torch.nn.Parameter], state: dict, *,
-                 alias_params: bool = True, max_numel: Optional[int] = None) -> Bucket:
+                 alias_params: bool = True) -> Bucket:
     """Allocate flat storage for ``params`` (same dtype/device), move the live values in and
     re-point ``p.data`` (and the ``exp_avg`` state, if present) at the views."""
     assert params

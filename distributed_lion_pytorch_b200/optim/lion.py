@@ -75,6 +75,7 @@ class Lion(Optimizer):
         self.use_kernels = use_kernels
         self._buckets: Optional[List[Bucket]] = None
         self._bucket_sig = None
+        self._frozen_actives: List[list] = []
         self._backend = None            # resolved at first step
         self._steps_done = 0
         self._cpu_gen: Optional[torch.Generator] = None
