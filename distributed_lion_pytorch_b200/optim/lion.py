@@ -259,6 +259,18 @@ class Lion(Optimizer):
             if stray:   # the checkpoint knows parameters we have not bucketed yet: re-plan at next step
                 self._buckets, self._bucket_sig = None, None
 
+    @torch.no_grad()
+    def resync_replicas(self, src: int = 0) -> None:
+        """Collective: overwrite every replica's parameters with rank ``src``'s.  This is how a
+        worker that really missed steps rejoins (SURVEY §7.3: rejoin = parameter re-broadcast);
+        momenta stay per worker, as the algorithm prescribes."""
+        from ..parallel import runtime as rt
+        self._ensure_buckets()
+        if self._buckets:
+            rt.broadcast_parameters([b.flat_p for b in self._buckets], src)
+        else:
+            rt.broadcast_parameters([p for g in self.param_groups for p in g["params"]], src)
+
     # ------------------------------------------------------------------ diagnostics
     @torch.no_grad()
     def vote_statistics(self, chunk_elems: int = 1 << 24) -> Dict[str, float]:

@@ -33,7 +33,7 @@ def _check(P, M, rp, rm, dtype):
         assert torch.equal(P[0], P[r]), "replicas diverged"
 
 
-@pytest.mark.parametrize("dtype", [torch.bfloat16, torch.float32])
+@pytest.mark.parametrize("dtype", [torch.bfloat16, torch.float32, torch.float16])
 @pytest.mark.parametrize("W,grid", [(2, None), (4, 5), (8, None), (8, 3)])
 def test_fused_emulated_majority_multi_step(dtype, W, grid):
     from distributed_lion_pytorch_b200.ops import lion_ops

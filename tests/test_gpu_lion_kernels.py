@@ -30,7 +30,7 @@ def _close(a, b, dtype, what):
     assert torch.allclose(a.float(), b.float(), rtol=tol, atol=1e-6), what
 
 
-@pytest.mark.parametrize("dtype", DTYPES)
+@pytest.mark.parametrize("dtype", DTYPES + [torch.float16])
 @pytest.mark.parametrize("n", [8, 1000, 4099, (1 << 20) + 5])
 def test_local_step_matches_reference(dtype, n):
     from distributed_lion_pytorch_b200.ops import lion_ops

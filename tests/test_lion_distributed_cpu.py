@@ -188,3 +188,19 @@ def test_vote_statistics_known_pattern():
     # counts cycle through 0,1,2,3,4 (of 4): ties at cnt=2 (1/5), unanimous at 0 and 4 (2/5)
     assert abs(st["tie_fraction"] - 0.2) < 0.01 and abs(st["unanimous_fraction"] - 0.4) < 0.01
     assert abs(st["mean_agreement"] - (1 + 0.5 + 0 + 0.5 + 1) / 5) < 0.01
+
+
+def _worker_resync(rank, world):
+    from distributed_lion import Lion
+    torch.manual_seed(rank)                                   # replicas deliberately different
+    p = torch.nn.Parameter(torch.randn(300))
+    opt = Lion([p], lr=1e-2)
+    p.grad = torch.randn(300)
+    opt.step()
+    opt.resync_replicas(src=1)
+    return p.detach().clone()
+
+
+def test_resync_replicas_rebroadcasts_parameters():
+    outs = run_distributed(_worker_resync, 3)
+    assert torch.equal(outs[0], outs[1]) and torch.equal(outs[2], outs[1])
