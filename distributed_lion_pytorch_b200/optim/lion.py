@@ -259,6 +259,13 @@ class Lion(Optimizer):
             if stray:   # the checkpoint knows parameters we have not bucketed yet: re-plan at next step
                 self._buckets, self._bucket_sig = None, None
 
+    def check_health(self) -> None:
+        """Raise if the fused exchange kernel recorded a stalled flag wait since the last check
+        (synchronises the device; the trainer calls it whenever it logs).  No-op for other back-ends."""
+        ctx = getattr(self._backend, "_ctx", None)
+        if ctx is not None:
+            ctx.check_status()
+
     @torch.no_grad()
     def resync_replicas(self, src: int = 0) -> None:
         """Collective: overwrite every replica's parameters with rank ``src``'s.  This is how a

@@ -307,6 +307,8 @@ class Trainer:
                         logs["live_workers"] = self._dropout_schedule.live_count(step - 1)
                     logged_loss, logged_step = cur, step
                     logs.update(self.timer.summary())          # device-timed phase means (only with --profile_steps)
+                    if isinstance(self.optimizer, Lion):
+                        self.optimizer.check_health()          # a stalled sign exchange surfaces here, not as a hang
                     self.log(logs)
                 if a.evaluation_strategy == "steps" and a.eval_steps and step % a.eval_steps == 0 \
                         and self.eval_dataset is not None:

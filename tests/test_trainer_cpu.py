@@ -179,3 +179,30 @@ def test_run_clm_torchrun_gloo_world2(tmp_path):
         assert (ck / f).exists(), f
     res = json.loads((tmp_path / "o" / "all_results.json").read_text())
     assert res["lion_backend"] == "nccl_1bit" and "perplexity" in res
+
+
+def test_reference_readme_command_lines_parse():
+    """The three launch recipes of the reference README (README.md:19-72) parse unchanged."""
+    import dpo_llama2
+    import run_clm
+    import sft_llama2
+    from distributed_lion_pytorch_b200.train import AsyncTrainingArguments, TrainingArguments, parse_cli
+    gpt2 = ("--config_name gpt2 --tokenizer_name gpt2 --dataset_name openwebtext --per_device_train_batch_size 20 "
+            "--per_device_eval_batch_size 24 --do_train --do_eval --output_dir gpt2_lion_wd_0.1 --report_to wandb "
+            "--torch_dtype bfloat16 --gradient_accumulation_steps 8 --max_steps 100000 --warmup_steps 2000 --lion "
+            "--save_total_limit 2 --learning_rate 0.0001 --weight_decay 0.1 --async_grad").split()
+    m, d, t = parse_cli((run_clm.ModelArguments, run_clm.DataTrainingArguments, AsyncTrainingArguments), gpt2)
+    assert m.config_name == "gpt2" and m.torch_dtype == "bfloat16" and d.dataset_name == "openwebtext"
+    assert t.lion and t.async_grad and t.gradient_accumulation_steps == 8 and t.save_total_limit == 2
+    sft = ['--output_dir=./sft', '--max_steps=500', '--logging_steps=10', '--save_steps=10',
+           '--per_device_train_batch_size=4', '--per_device_eval_batch_size=1', '--gradient_accumulation_steps=2',
+           '--gradient_checkpointing=False', '--group_by_length=False', '--learning_rate=1e-4',
+           '--lr_scheduler_type=cosine', '--warmup_steps=100', '--weight_decay=0.05', '--optim=paged_adamw_32bit',
+           '--bf16=True', '--remove_unused_columns=False', '--run_name=sft_llama2', '--report_to=wandb', '--lion',
+           '--async_grad']
+    s, ta = parse_cli((sft_llama2.ScriptArguments, TrainingArguments), sft)
+    assert ta.lion and ta.async_grad and ta.bf16 and not ta.gradient_checkpointing and ta.weight_decay == 0.05
+    assert s.model_name == "meta-llama/Llama-2-7b-hf" and s.seq_length == 1024 and s.lora_r == 8
+    dpo = ['--model_name_or_path=sft/final_checkpoint', '--output_dir=dpo', '--lion', '--async_grad']
+    (ds,) = parse_cli((dpo_llama2.ScriptArguments,), dpo)
+    assert ds.lion and ds.async_grad and ds.beta == 0.1 and ds.max_length == 1024 and ds.max_prompt_length == 512
