@@ -17,6 +17,13 @@ namespace dlion {
 
 constexpr int kCEThreads = 512;
 
+// one MUFU.EX2; inputs here are <= 0 (x - max), flush-to-zero on underflow is exactly what softmax wants
+__device__ __forceinline__ float fast_exp2(float x) {
+  float y;
+  asm("ex2.approx.ftz.f32 %0, %1;" : "=f"(y) : "f"(x));
+  return y;
+}
+
 struct MaxSum {
   float m, s;
 };
@@ -75,9 +82,10 @@ __global__ void __launch_bounds__(kCEThreads) ce_kernel(T* __restrict__ logits, 
 #pragma unroll
       for (int i = 1; i < 8; ++i) mx = fmaxf(mx, f[i]);
       const float m = fmaxf(acc.m, mx);
-      float s = acc.s * __expf(acc.m - m);
+      const float ms = m * 1.4426950408889634f;
+      float s = acc.s * fast_exp2(fmaf(acc.m, 1.4426950408889634f, -ms));
 #pragma unroll
-      for (int i = 0; i < 8; ++i) s += __expf(f[i] - m);
+      for (int i = 0; i < 8; ++i) s += fast_exp2(fmaf(f[i], 1.4426950408889634f, -ms));   // one fma + one MUFU
       acc = {m, s};
     }
     if (threadIdx.x < vocab - tail0) {
@@ -90,16 +98,26 @@ __global__ void __launch_bounds__(kCEThreads) ce_kernel(T* __restrict__ logits, 
     if (MODE != 2 && threadIdx.x == 0 && loss != nullptr) loss[row] = lse - DT<T>::to_f(x[label]);
     if (MODE == 0) continue;
     __syncthreads();   // everyone (incl. thread 0's x[label] read) is done with the raw logits
-    const float inv = 1.0f / tot.s;
+    // p * scale = exp2(x*log2e - m*log2e) * (scale / sum): one fma + one MUFU + one mul per element;
+    // the label and the vocabulary boundary are handled per vector, not per element
+    constexpr float kLog2e = 1.4426950408889634f;
+    const float inv = scale / tot.s;
+    const float mxs = tot.m * kLog2e;
+    const int label_vec = (int)(label >> 3), label_lane = (int)(label & 7);
     for (int j = threadIdx.x; j < (padded >> 3); j += kCEThreads) {
       float f[8];
       load8<T>(x + j * 8, f);
 #pragma unroll
-      for (int i = 0; i < 8; ++i) {
-        const int col = j * 8 + i;
-        float p = col < vocab ? __expf(f[i] - tot.m) * inv : 0.f;
-        if (col == (int)label) p -= 1.f;
-        f[i] = p * scale;
+      for (int i = 0; i < 8; ++i) f[i] = fast_exp2(fmaf(f[i], kLog2e, -mxs)) * inv;
+      if (j >= nvec) {                      // the vector(s) straddling or beyond the real vocabulary
+#pragma unroll
+        for (int i = 0; i < 8; ++i)
+          if (j * 8 + i >= vocab) f[i] = 0.f;
+      }
+      if (j == label_vec) {
+#pragma unroll
+        for (int i = 0; i < 8; ++i)
+          if (i == label_lane) f[i] -= scale;
       }
       store8<T>(x + j * 8, f);
     }
