@@ -18,6 +18,7 @@ import torch.nn as nn
 import torch.nn.functional as F
 from torch.utils.checkpoint import checkpoint
 
+from ..ops.activation import gelu_tanh
 from ..ops.cross_entropy import linear_cross_entropy, linear_log_probs
 from ..ops.linear import fused_linear
 from ..ops.norm import add_layer_norm
@@ -113,7 +114,7 @@ class GPT2MLP(nn.Module):
 
     def forward(self, x):
         h = self.c_fc(x)
-        h = F.gelu(h, approximate="tanh") if self.act in ("gelu_new", "gelu_pytorch_tanh") else F.gelu(h)
+        h = gelu_tanh(h) if self.act in ("gelu_new", "gelu_pytorch_tanh") else F.gelu(h)
         return self.c_proj(h)
 
 

@@ -15,6 +15,7 @@ import torch.nn as nn
 import torch.nn.functional as F
 from torch.utils.checkpoint import checkpoint
 
+from ..ops.activation import swiglu
 from ..ops.cross_entropy import linear_cross_entropy, linear_log_probs
 from ..ops.linear import fused_linear
 from ..ops.norm import add_rms_norm
@@ -103,7 +104,7 @@ class LlamaMLP(nn.Module):
         self.down_proj = Linear(cfg.intermediate_size, cfg.hidden_size, bias=False)
 
     def forward(self, x):
-        return self.down_proj(F.silu(self.gate_proj(x)) * self.up_proj(x))
+        return self.down_proj(swiglu(self.gate_proj(x), self.up_proj(x)))
 
 
 class LlamaDecoderLayer(nn.Module):

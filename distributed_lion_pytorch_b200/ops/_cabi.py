@@ -76,6 +76,10 @@ def _declare(L: C.CDLL) -> None:
         "dlion_norm_bwd_finalize": [vp, vp, vp, vp, i32, i32, i32, vp],
         "dlion_colsum_parts": [i64, i32],
         "dlion_colsum": [vp, i64, i32, vp, i32, vp],
+        "dlion_gelu_tanh_fwd": [vp, vp, i64, i32, vp],
+        "dlion_gelu_tanh_bwd": [vp, vp, vp, i64, i32, vp],
+        "dlion_swiglu_fwd": [vp, vp, vp, i64, i32, vp],
+        "dlion_swiglu_bwd": [vp, vp, vp, vp, vp, i64, i32, vp],
         "dlion_rope": [vp, vp, vp, vp, i64, i32, i32, i32, i32, i64, i64, i32, i32, vp],
         "dlion_ce_fwd_bwd": [vp, vp, vp, i64, i32, i64, i64, f32, i32, i32, vp],
         "dlion_ce_bwd_rowscale": [vp, vp, vp, i64, i32, i64, i64, i32, vp],

@@ -187,6 +187,15 @@ int dlion_norm_bwd_finalize(const float* dw_partial, const float* db_partial, vo
 int dlion_colsum_parts(int64_t rows, int cols);
 int dlion_colsum(const void* x, int64_t rows, int cols, float* partial, int dtype, void* stream);
 
+/* MLP activations as single passes over n elements (n % 8 == 0): GPT-2's tanh-form GELU and
+ * Llama's silu(gate) * up, forward and backward.
+ * reference: HF GPT2MLP / LlamaMLP via Trainer.compute_loss (async_trainer.py:24). */
+int dlion_gelu_tanh_fwd(const void* x, void* y, int64_t n, int dtype, void* stream);
+int dlion_gelu_tanh_bwd(const void* x, const void* dy, void* dx, int64_t n, int dtype, void* stream);
+int dlion_swiglu_fwd(const void* gate, const void* up, void* y, int64_t n, int dtype, void* stream);
+int dlion_swiglu_bwd(const void* gate, const void* up, const void* dy, void* dgate, void* dup, int64_t n,
+                     int dtype, void* stream);
+
 /* N4 — rotary embedding applied in place to q [tokens, q_heads, head_dim] and k
  * [tokens, k_heads, head_dim] (HF "rotate_half" pairing: i <-> i + head_dim/2); cos/sin are
  * fp32 [seq, head_dim/2]; pos = token index % seq_len.  inverse != 0 applies the transpose

@@ -228,3 +228,29 @@ def test_add_norm_with_fused_dropout(dtype, rms, with_res, cols):
     assert (x.grad[~keep] == 0).all()                                                     # dropped inputs get no gradient
     if with_res:
         assert torch.allclose(r.grad.float(), rf.grad, **t)
+
+
+@pytest.mark.parametrize("dtype", [torch.float32, torch.bfloat16])
+def test_activation_kernels(dtype):
+    from distributed_lion_pytorch_b200.ops.activation import gelu_tanh, swiglu
+    torch.manual_seed(0)
+    x = (torch.randn(333, 3072, device="cuda") * 2).to(dtype).requires_grad_()
+    dy = torch.randn_like(x)
+    y = gelu_tanh(x)
+    y.backward(dy)
+    xf = x.detach().float().requires_grad_()
+    yf = F.gelu(xf, approximate="tanh")
+    yf.backward(dy.float())
+    t = dict(rtol=2e-2, atol=2e-2) if dtype == torch.bfloat16 else dict(rtol=1e-5, atol=1e-5)
+    assert torch.allclose(y.float(), yf, **t) and torch.allclose(x.grad.float(), xf.grad, **t)
+    g = (torch.randn(129, 11008, device="cuda") * 2).to(dtype).requires_grad_()
+    u = torch.randn(129, 11008, device="cuda").to(dtype).requires_grad_()
+    do = torch.randn_like(g)
+    o = swiglu(g, u)
+    o.backward(do)
+    gf, uf = g.detach().float().requires_grad_(), u.detach().float().requires_grad_()
+    of = F.silu(gf) * uf
+    of.backward(do.float())
+    t = dict(rtol=3e-2, atol=3e-2) if dtype == torch.bfloat16 else dict(rtol=1e-5, atol=1e-5)
+    assert torch.allclose(o.float(), of, **t)
+    assert torch.allclose(g.grad.float(), gf.grad, **t) and torch.allclose(u.grad.float(), uf.grad, **t)
