@@ -116,12 +116,35 @@ class FusedBackend(_Backend):
     def on_rebucket(self, opt) -> None:
         self._ctx = None
 
+    def _try_create(self, device) -> bool:
+        """Set the exchange up and agree collectively that it worked everywhere (a rank-local failure
+        must not leave the others spinning on flags that will never be written)."""
+        import logging
+        err = None
+        try:
+            self._ctx = self._symm.FusedExchange(self.opt.process_group, device)
+        except Exception as e:      # noqa: BLE001 — any failure means "no peer mapping here"
+            err = e
+            self._ctx = None
+        ok = torch.tensor([0 if err is not None else 1], dtype=torch.int32, device=device)
+        dist.all_reduce(ok, op=dist.ReduceOp.MIN, group=self.opt.process_group)
+        if int(ok.item()) == 1:
+            return True
+        self._ctx = None
+        if self.opt.comm == "fused":
+            raise RuntimeError(f"comm='fused' was requested but peer-mapped memory could not be set up: {err}")
+        logging.getLogger("dlion.lion").warning("fused NVLink exchange unavailable (%s); using nccl_1bit", err)
+        return False
+
     def step(self, b, lr, wd, beta1, beta2, missing):
         opt = self.opt
         if b.device.type != "cuda":
             raise RuntimeError("comm='fused' needs CUDA tensors; use comm='nccl_1bit' on CPU")
-        if self._ctx is None:
-            self._ctx = self._symm.FusedExchange(opt.process_group, b.device)
+        if self._ctx is None and not self._try_create(b.device):
+            # peer mapping is unavailable on at least one rank: every rank switches to the split path
+            fallback = AllGatherBackend(opt)
+            opt._backend = fallback
+            return fallback.step(b, lr, wd, beta1, beta2, missing)
         self._ctx.step(b, lr, wd, beta1, beta2, vote=opt.vote, tie=opt.tie, live_mask=opt.live_mask,
                        max_grad_norm=opt.max_grad_norm, seed=opt.seed, step_index=opt._steps_done)
 

@@ -5,12 +5,11 @@ Every rank owns one arena ``uint32[2 parities][W][arena_words]`` and one flag ta
 all other ranks' copies, so the kernel (csrc/lion_fused_sm100.cu) can store packed sign words
 and release progress counters straight into peer memory over NVLink / NVSwitch.
 
-Two ways to obtain the peer mappings, tried in this order (override with ``DLION_SYMM``):
-
-``symm``  ``torch.distributed._symmetric_memory`` (CUDA VMM + fabric/fd handles; also exposes an
-          NVLS multicast pointer where the fabric supports it);
-``ipc``   legacy CUDA IPC handles exchanged through ``all_gather_object`` — same-node only,
-          works wherever ``cudaIpcOpenMemHandle`` does.
+The peer mappings come from ``torch.distributed._symmetric_memory`` (CUDA VMM + fabric / fd
+handles; it also exposes an NVLS multicast pointer where the fabric supports it).  When that
+mechanism is unavailable on any rank, ``Lion`` falls back — collectively — to the ``nccl_1bit``
+back-end.  (A second mechanism over legacy ``cudaIpc*`` handles was tried and removed: it faulted
+on the B200 box and is not needed there.)
 
 reference: the only exchange upstream is ``dist.all_gather(all_updates, uint8_tensor)``
 (distributed_lion.py:80-81), one blocking NCCL collective per parameter tensor.
@@ -27,7 +26,6 @@ import torch.distributed as dist
 from ..ops import _cabi, lion_ops
 
 CHUNK_ELEMS = 1 << 28          # elements per fused launch (arena = 2*W*chunk/8 bytes: 512 MiB at W=8)
-_KEEPALIVE = []                # peer-mapped storages must outlive every kernel that targets them
 
 
 def _same_node(pg) -> bool:
@@ -56,23 +54,12 @@ class PeerBuffer:
     """A zero-initialised device buffer of ``nbytes`` on every rank + the addresses of all ranks'
     copies as seen from this process (``ptrs[r]``; ``ptrs[rank]`` is the local one)."""
 
-    def __init__(self, nbytes: int, device: torch.device, pg=None, how: Optional[str] = None):
+    def __init__(self, nbytes: int, device: torch.device, pg=None):
         self.pg, self.device, self.nbytes = pg, device, int(nbytes)
         self.rank, self.world = dist.get_rank(pg), dist.get_world_size(pg)
-        how = how or os.environ.get("DLION_SYMM", "auto")
-        self.how = None
         self.multicast_ptr = 0
-        errs = []
-        order = ("symm", "ipc") if how == "auto" else (how,)
-        for h in order:
-            try:
-                getattr(self, f"_alloc_{h}")()
-                self.how = h
-                break
-            except Exception as e:   # fall through to the next mechanism, keep the reason
-                errs.append(f"{h}: {type(e).__name__}: {e}")
-        if self.how is None:
-            raise RuntimeError("could not peer-map device memory: " + " | ".join(errs))
+        self._alloc_symm()
+        self.how = "symm"
         torch.cuda.synchronize(device)
         dist.barrier(group=pg)
 
@@ -95,22 +82,6 @@ class PeerBuffer:
             self.multicast_ptr = 0
         self._hdl = hdl
 
-    def _alloc_ipc(self):
-        t = torch.zeros(self.nbytes, dtype=torch.uint8, device=self.device)
-        torch.cuda.synchronize(self.device)
-        handle = t.untyped_storage()._share_cuda_()
-        handles = [None] * self.world
-        dist.all_gather_object(handles, (self.rank, handle, t.storage_offset()), group=self.pg)
-        ptrs = [0] * self.world
-        for r, h, off in handles:
-            if r == self.rank:
-                ptrs[r] = t.data_ptr()
-                continue
-            st = torch.UntypedStorage._new_shared_cuda(*h)
-            _KEEPALIVE.append(st)
-            ptrs[r] = st.data_ptr() + off
-        self.local, self.ptrs = t, ptrs
-
 
 class FusedExchange:
     """Owns the arenas/flags of one process group and launches the fused step bucket by bucket."""
@@ -131,7 +102,7 @@ class FusedExchange:
         if self.arena is not None and words <= self.arena_words:
             return
         # collective: every rank reaches this with the same bucket size
-        self.arena = PeerBuffer(2 * self.world * words * 4, self.device, self.pg, how=self.flags.how)
+        self.arena = PeerBuffer(2 * self.world * words * 4, self.device, self.pg)
         self.arena_words = words
 
     def grid_for(self, dtype: torch.dtype) -> int:

@@ -88,3 +88,4 @@ def test_fused_nvls_multicast_send_path():
         pytest.skip("no NVLS multicast pointer on this fabric")
     for o in outs:
         assert torch.equal(o["fused"], o["split"]) and torch.equal(o["fused"], outs[0]["fused"])
+
