@@ -280,26 +280,49 @@ __global__ void __launch_bounds__(BLOCK, bwd_ctas_per_sm(VPT, BLOCK)) norm_bwd_k
   }
 }
 
-// partials [parts, cols] -> dweight/dbias (T).  blockDim (32, 32): 32 columns x 32 row slices.
+// partials [parts, cols] -> dweight/dbias (T).  blockDim (8, 128): 8 threads x float4 = 32 columns,
+// 128 row lanes; every thread folds parts/128 rows with independent 16-byte loads, then the CTA
+// folds its 128 lanes through shared memory.  (The first version used 32 row lanes and scalar
+// loads: 46 dependent trips per thread, 10 us per call, 146 calls per micro-step.)
 template <typename T>
-__global__ void norm_bwd_finalize_kernel(const float* __restrict__ dw_part, const float* __restrict__ db_part,
-                                         T* __restrict__ dw, T* __restrict__ db, int parts, int cols) {
-  __shared__ float sw[32][33], sb[32][33];
-  const int c = blockIdx.x * 32 + threadIdx.x;
-  float aw = 0.f, ab = 0.f;
-  if (c < cols)
-    for (int r = threadIdx.y; r < parts; r += 32) {
-      aw += dw_part[(int64_t)r * cols + c];
-      if (db_part != nullptr) ab += db_part[(int64_t)r * cols + c];
+__global__ void __launch_bounds__(1024) norm_bwd_finalize_kernel(const float* __restrict__ dw_part,
+                                                                 const float* __restrict__ db_part,
+                                                                 T* __restrict__ dw, T* __restrict__ db, int parts,
+                                                                 int cols) {
+  __shared__ float4 sw[128][8], sb[128][8];
+  const int tx = threadIdx.x, ty = threadIdx.y;
+  const int c0 = blockIdx.x * 32 + tx * 4;
+  float4 aw = make_float4(0.f, 0.f, 0.f, 0.f), ab = aw;
+  if (c0 < cols) {
+    for (int r = ty; r < parts; r += 128) {
+      const float4 v = *reinterpret_cast<const float4*>(dw_part + (int64_t)r * cols + c0);
+      aw.x += v.x; aw.y += v.y; aw.z += v.z; aw.w += v.w;
+      if (db_part != nullptr) {
+        const float4 u = *reinterpret_cast<const float4*>(db_part + (int64_t)r * cols + c0);
+        ab.x += u.x; ab.y += u.y; ab.z += u.z; ab.w += u.w;
+      }
     }
-  sw[threadIdx.y][threadIdx.x] = aw;
-  sb[threadIdx.y][threadIdx.x] = ab;
+  }
+  sw[ty][tx] = aw;
+  sb[ty][tx] = ab;
   __syncthreads();
-  if (threadIdx.y == 0 && c < cols) {
-#pragma unroll
-    for (int r = 1; r < 32; ++r) aw += sw[r][threadIdx.x], ab += sb[r][threadIdx.x];
-    dw[c] = DT<T>::from_f(aw);
-    if (db != nullptr && db_part != nullptr) db[c] = DT<T>::from_f(ab);
+  for (int half = 64; half > 0; half >>= 1) {      // tree over the 128 row lanes
+    if (ty < half) {
+      float4 a = sw[ty][tx], b2 = sw[ty + half][tx];
+      sw[ty][tx] = make_float4(a.x + b2.x, a.y + b2.y, a.z + b2.z, a.w + b2.w);
+      a = sb[ty][tx]; b2 = sb[ty + half][tx];
+      sb[ty][tx] = make_float4(a.x + b2.x, a.y + b2.y, a.z + b2.z, a.w + b2.w);
+    }
+    __syncthreads();
+  }
+  if (ty == 0 && c0 < cols) {
+    const float4 a = sw[0][tx], b2 = sb[0][tx];
+    dw[c0] = DT<T>::from_f(a.x); dw[c0 + 1] = DT<T>::from_f(a.y);
+    dw[c0 + 2] = DT<T>::from_f(a.z); dw[c0 + 3] = DT<T>::from_f(a.w);
+    if (db != nullptr && db_part != nullptr) {
+      db[c0] = DT<T>::from_f(b2.x); db[c0 + 1] = DT<T>::from_f(b2.y);
+      db[c0 + 2] = DT<T>::from_f(b2.z); db[c0 + 3] = DT<T>::from_f(b2.w);
+    }
   }
 }
 
@@ -477,7 +500,7 @@ extern "C" int dlion_norm_bwd_finalize(const float* dw_partial, const float* db_
                                        int parts, int cols, int dtype, void* stream) {
   DLION_CHECK_ARG(parts > 0 && cols > 0 && dw_partial && dweight, "dlion_norm_bwd_finalize: bad arguments");
   cudaStream_t s = (cudaStream_t)stream;
-  const dim3 block(32, 32);
+  const dim3 block(8, 128);
   const int grid = (cols + 31) / 32;
   DISPATCH_DTYPE(dtype, norm_bwd_finalize_kernel<T><<<grid, block, 0, s>>>(dw_partial, db_partial, (T*)dweight,
                                                                              (T*)dbias, parts, cols));
