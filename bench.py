@@ -190,20 +190,12 @@ def run_ours(a, device, rank, world):
     dev = [{k: v.to(device) for k, v in b.items()} for b in host]
     last = {}
 
-    def step_device(i):
-        for j in range(a.ga):
-            trainer.training_step(model, dev[(i * a.ga + j) % len(dev)])
-        trainer._clip_gradients()
-        trainer._optimizer_step()
+    def step_device(i):      # batches already resident on the GPU, no read-back
+        trainer.train_step([dev[(i * a.ga + j) % len(dev)] for j in range(a.ga)])
 
-    def step_e2e(i):
-        tot = None
-        for j in range(a.ga):
-            l = trainer.training_step(model, host[(i * a.ga + j) % len(host)])      # H2D from pinned memory inside
-            tot = l if tot is None else tot + l
-        trainer._clip_gradients()
-        trainer._optimizer_step()
-        last["loss"] = float(tot.item())                                            # D2H read of the step's loss
+    def step_e2e(i):         # the public API as a user calls it: pinned host batches in, the step's loss out
+        loss = trainer.train_step([host[(i * a.ga + j) % len(host)] for j in range(a.ga)])   # H2D copies inside
+        last["loss"] = float(loss.item())                                                    # D2H read of the loss
 
     sampler = ClockSampler(torch.cuda.current_device())
     n0 = _cabi.LAUNCHES

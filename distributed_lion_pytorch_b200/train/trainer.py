@@ -129,6 +129,7 @@ class Trainer:
         self._dropout_schedule: Optional[DropoutSchedule] = None
         self.timer = StepTimer(enabled=bool(getattr(self.args, "profile_steps", False)))
         self._wandb = None
+        self._last_grad_norm = None
         if self.args.gradient_checkpointing and hasattr(self.model, "gradient_checkpointing_enable"):
             self.model.gradient_checkpointing_enable()
 
@@ -231,6 +232,27 @@ class Trainer:
         else:
             self.optimizer.zero_grad(set_to_none=True)
 
+    def train_step(self, micro_batches) -> torch.Tensor:
+        """One optimizer step from ``gradient_accumulation_steps`` micro-batches (host or device
+        tensors): forward/backward each, then gradient sync (baseline trainers only), local
+        clipping, optimizer, schedule, zero_grad.  Returns the step's mean loss as a device tensor
+        (no host sync).  ``train()`` is this in a loop plus logging/eval/checkpoints; it is public
+        so that custom loops and ``bench.py`` drive exactly the code path ``train()`` runs."""
+        if self.optimizer is None or self.lr_scheduler is None:
+            raise RuntimeError("call create_optimizer_and_scheduler(num_training_steps) or pass optimizers=(opt, sched)")
+        total = None
+        for inputs in micro_batches:
+            loss = self.training_step(self.model, inputs)
+            total = loss if total is None else total + loss
+        with self.timer.phase("grad_sync"):
+            self._sync_gradients()
+        with self.timer.phase("clip"):
+            self._last_grad_norm = self._clip_gradients()
+        with self.timer.phase("optimizer"):
+            self._optimizer_step()
+        self.state.global_step += 1
+        return total
+
     # ------------------------------------------------------------------ train
     def train(self, resume_from_checkpoint: Optional[str] = None, **_) -> TrainOutput:
         a = self.args
@@ -276,23 +298,20 @@ class Trainer:
             if sampler is not None:
                 sampler.set_epoch(epoch)
             micro = 0
+            pending = []
             for inputs in loader:
                 if skip_micro > 0:          # resume: drop the batches the checkpointed run consumed
                     skip_micro -= 1
                     continue
                 if tokens_per_micro is None and "input_ids" in inputs:
                     tokens_per_micro = inputs["input_ids"].numel()
-                tr_loss += self.training_step(self.model, inputs)
+                pending.append(inputs)
                 micro += 1
                 if micro % ga:
                     continue
-                with self.timer.phase("grad_sync"):
-                    self._sync_gradients()
-                with self.timer.phase("clip"):
-                    grad_norm = self._clip_gradients()
-                with self.timer.phase("optimizer"):
-                    self._optimizer_step()
-                self.state.global_step += 1
+                tr_loss += self.train_step(pending)
+                pending = []
+                grad_norm = self._last_grad_norm
                 self.state.epoch = epoch + (micro / ga) / steps_per_epoch if steps_per_epoch else 0.0
                 if tokens_per_micro:
                     self.state.num_input_tokens_seen += tokens_per_micro * ga * world
