@@ -11,7 +11,8 @@ import torch
 from .common import CausalLMOutput  # noqa: F401
 from .gpt2 import GPT2_PRESETS, GPT2Config, GPT2LMHeadModel  # noqa: F401
 from .llama import LLAMA_PRESETS, LlamaConfig, LlamaForCausalLM  # noqa: F401
-from .lora import LoraConfig, LoRALinear, apply_lora, merge_and_unload, lora_state_dict  # noqa: F401
+from .lora import (LoraConfig, LoRALinear, apply_lora, disable_adapters, lora_state_dict,  # noqa: F401
+                   merge_and_unload)
 
 _ALIASES = {
     "openai-community/gpt2": "gpt2", "gpt2": "gpt2", "gpt2-medium": "gpt2-medium", "gpt2-large": "gpt2-large",

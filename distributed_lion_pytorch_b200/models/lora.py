@@ -7,6 +7,7 @@ reference: ``LoraConfig(r=8, lora_alpha=16, lora_dropout=0.05, target_modules=["
 """
 from __future__ import annotations
 
+import contextlib
 import math
 from dataclasses import dataclass, field
 from typing import Dict, Iterable, List
@@ -35,12 +36,15 @@ class LoRALinear(nn.Module):
         self.lora_B = nn.Parameter(torch.zeros(base.out_features, r, dtype=base.weight.dtype, device=base.weight.device))
         nn.init.kaiming_uniform_(self.lora_A, a=math.sqrt(5))
         self.dropout = dropout
+        self.enabled = True
         base.weight.requires_grad_(False)
         if base.bias is not None:
             base.bias.requires_grad_(False)
 
     def forward(self, x):
         y = self.base(x)
+        if not self.enabled:
+            return y
         xd = F.dropout(x, self.dropout, self.training) if self.dropout > 0 else x
         return y + (xd @ self.lora_A.t()) @ self.lora_B.t() * self.scaling
 
@@ -65,6 +69,21 @@ def apply_lora(model: nn.Module, cfg: LoraConfig) -> nn.Module:
         raise ValueError(f"no module matched target_modules={cfg.target_modules}")
     model.peft_config = cfg
     return model
+
+
+@contextlib.contextmanager
+def disable_adapters(model: nn.Module):
+    """Run the wrapped model as its frozen base (what TRL's DPOTrainer uses as the implicit reference
+    model when only a PEFT policy is given)."""
+    mods = [m for m in model.modules() if isinstance(m, LoRALinear)]
+    old = [m.enabled for m in mods]
+    for m in mods:
+        m.enabled = False
+    try:
+        yield
+    finally:
+        for m, e in zip(mods, old):
+            m.enabled = e
 
 
 def merge_and_unload(model: nn.Module) -> nn.Module:

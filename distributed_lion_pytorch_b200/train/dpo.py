@@ -15,7 +15,7 @@ from typing import Dict, List, Optional
 import torch
 import torch.nn.functional as F
 
-from ..models.lora import LoraConfig, apply_lora
+from ..models.lora import LoraConfig, apply_lora, disable_adapters
 from .trainer import NoSyncMixin, Trainer
 
 IGNORE = -100
@@ -94,8 +94,11 @@ class DPOTrainer(Trainer):
         with torch.no_grad():
             if self.ref_model is not None:
                 ref = self._seq_logps(self.ref_model, ids, labels)
-            else:   # no explicit reference: the policy with adapters disabled would go here; use a detached copy
-                ref = pi.detach()
+            elif hasattr(model, "peft_config"):     # implicit reference = the policy with its adapters switched off
+                with disable_adapters(model):
+                    ref = self._seq_logps(model, ids, labels)
+            else:
+                raise ValueError("DPO needs a reference model (or a LoRA-wrapped policy whose base serves as one)")
         loss, cr, rr = dpo_loss(pi[:B], pi[B:], ref[:B], ref[B:], self.beta)
         self._last_metrics = {"rewards/chosen": cr.mean(), "rewards/rejected": rr.mean(),
                               "rewards/accuracies": (cr > rr).float().mean(), "rewards/margins": (cr - rr).mean()}

@@ -129,3 +129,20 @@ def test_schedules_match_hf_formulas():
         opt3.step()
         l.step()
     assert vals[:3] == [0.0, 0.5, 1.0] and abs(vals[7] - 0.5) < 1e-9
+
+
+def test_dpo_trainer_with_implicit_lora_reference(tmp_path):
+    """No ref_model: the LoRA-wrapped policy with adapters disabled is the reference (TRL behaviour)."""
+    from distributed_lion_pytorch_b200.models import LoraConfig, build_model
+    from distributed_lion_pytorch_b200.train import AsyncDPOTrainer, SyntheticPreferenceDataset, TrainingArguments
+    torch.manual_seed(0)
+    model = build_model("llama-tiny")
+    args = TrainingArguments(output_dir=str(tmp_path), per_device_train_batch_size=2, gradient_accumulation_steps=1,
+                             max_steps=3, learning_rate=1e-2, lion=True, async_grad=True, logging_steps=1, save_steps=100)
+    tr = AsyncDPOTrainer(model, None, args=args, beta=0.1, train_dataset=SyntheticPreferenceDataset(512, 8, 24, 16),
+                         peft_config=LoraConfig(r=4, lora_alpha=8, lora_dropout=0.0), max_prompt_length=8, max_length=24)
+    out = tr.train()
+    losses = [h["loss"] for h in tr.state.log_history if "loss" in h]
+    assert abs(losses[0] - 0.693147) < 1e-3            # adapters start at zero: policy == reference
+    assert out.global_step == 3 and losses[-1] != losses[0]
+    assert any("rewards/accuracies" in h for h in tr.state.log_history)
