@@ -103,11 +103,11 @@ def gather_grads(b: Bucket, *, use_kernel: bool = True):
         if g is None:
             gv.zero_()
             missing.append(i)
+        elif g.is_sparse:
+            raise RuntimeError("Lion does not support sparse gradients")
         elif g.data_ptr() == gv.data_ptr() and g.dtype == gv.dtype:
             continue
         else:
-            if g.is_sparse:
-                raise RuntimeError("Lion does not support sparse gradients")
             src.append(g)
             dst.append(gv)
     if src:

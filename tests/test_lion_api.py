@@ -178,3 +178,25 @@ def test_module_level_helpers_match_reference(ref_mod):
     ref_mod.update_fn(p1, gr, m1, 1e-3, 0.1, 0.9, 0.99)
     ours.update_fn(p2, gr, m2, 1e-3, 0.1, 0.9, 0.99)
     assert torch.equal(p1, p2) and torch.equal(m1, m2)
+
+
+def test_mixed_dtype_groups_make_separate_buckets_and_sparse_grads_are_rejected():
+    torch.manual_seed(0)
+    a = torch.nn.Parameter(torch.randn(40))
+    b = torch.nn.Parameter(torch.randn(24).bfloat16())
+    c = torch.nn.Parameter(torch.randn(8))
+    opt = Lion([{"params": [a, b]}, {"params": [c], "lr": 1e-2}], lr=1e-3, weight_decay=0.1)
+    for p in (a, b, c):
+        p.grad = torch.randn_like(p)
+    before = [p.detach().clone() for p in (a, b, c)]
+    opt.step()
+    assert len(opt.buckets) == 3                                     # (group 0, fp32), (group 0, bf16), (group 1, fp32)
+    assert {bk.dtype for bk in opt.buckets} == {torch.float32, torch.bfloat16}
+    for p, q in zip((a, b, c), before):
+        assert not torch.equal(p.detach(), q)
+    assert abs(float((c.detach() - before[2] * (1 - 1e-2 * 0.1)).abs().max()) - 1e-2) < 1e-6      # group lr honoured
+    emb = torch.nn.Embedding(10, 4, sparse=True)
+    o2 = Lion(emb.parameters(), lr=1e-3)
+    emb(torch.tensor([1, 2])).sum().backward()
+    with pytest.raises(RuntimeError, match="sparse"):
+        o2.step()

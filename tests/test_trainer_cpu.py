@@ -206,3 +206,35 @@ def test_reference_readme_command_lines_parse():
     dpo = ['--model_name_or_path=sft/final_checkpoint', '--output_dir=dpo', '--lion', '--async_grad']
     (ds,) = parse_cli((dpo_llama2.ScriptArguments,), dpo)
     assert ds.lion and ds.async_grad and ds.beta == 0.1 and ds.max_length == 1024 and ds.max_prompt_length == 512
+
+
+def _worker_per_rank_resume(rank, world, outdir):
+    from distributed_lion_pytorch_b200.models import build_model
+    from distributed_lion_pytorch_b200.train import AsyncTrainer, SyntheticTokenDataset, TrainingArguments
+
+    def mk(sub, **kw):
+        torch.manual_seed(0)
+        model = build_model("gpt2-tiny", config_overrides="resid_pdrop=0.0,embd_pdrop=0.0,attn_pdrop=0.0")
+        base = dict(output_dir=f"{outdir}/{sub}", per_device_train_batch_size=2, gradient_accumulation_steps=1,
+                    max_steps=4, learning_rate=1e-3, weight_decay=0.1, lion=True, async_grad=True, logging_steps=1,
+                    save_steps=2, lr_scheduler_type="cosine", warmup_steps=1, seed=11, per_rank_optimizer_state=True)
+        base.update(kw)
+        return AsyncTrainer(model=model, args=TrainingArguments(**base),
+                            train_dataset=SyntheticTokenDataset(512, 32, 64, seed=1))
+    a = mk("a")
+    a.train()
+    b = mk("a")                                       # resume from the mid-run checkpoint of the same directory
+    b.train(resume_from_checkpoint=f"{outdir}/a/checkpoint-2")
+    pa = torch.cat([p.detach().flatten() for p in a.model.parameters()])
+    pb = torch.cat([p.detach().flatten() for p in b.model.parameters()])
+    ma = torch.cat([a.optimizer.state[p]["exp_avg"].flatten() for p in a.model.parameters()])
+    mb = torch.cat([b.optimizer.state[p]["exp_avg"].flatten() for p in b.model.parameters()])
+    return dict(params_equal=torch.equal(pa, pb), mom_equal=torch.equal(ma, mb), mom=ma)
+
+
+def test_per_rank_momentum_survives_resume(tmp_path):
+    """--per_rank_optimizer_state: every worker gets ITS momentum back (upstream only rank 0's is
+    saved and all workers collapse onto it: SURVEY D14), so the resumed run is bit-identical."""
+    outs = run_distributed(_worker_per_rank_resume, 2, str(tmp_path))
+    assert all(o["params_equal"] and o["mom_equal"] for o in outs)
+    assert not torch.equal(outs[0]["mom"], outs[1]["mom"])
