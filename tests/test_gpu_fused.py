@@ -34,7 +34,7 @@ def _check(P, M, rp, rm, dtype):
 
 
 @pytest.mark.parametrize("dtype", [torch.bfloat16, torch.float32, torch.float16])
-@pytest.mark.parametrize("W,grid", [(2, None), (4, 5), (8, None), (8, 3)])
+@pytest.mark.parametrize("W,grid", [(2, None), (4, 5), (8, None), (8, 3), (16, 2)])
 def test_fused_emulated_majority_multi_step(dtype, W, grid):
     from distributed_lion_pytorch_b200.ops import lion_ops
     from distributed_lion_pytorch_b200.parallel.symm import EmulatedExchange
