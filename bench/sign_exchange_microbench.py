@@ -15,6 +15,7 @@ and prints each as time, achieved HBM GB/s on the 10 B/param algorithmic traffic
 fraction of the fused roofline max(HBM time, NVLink time).
 """
 import argparse
+import gc
 import importlib.util
 import json
 import sys
@@ -77,8 +78,8 @@ def main():
         for comm in ("fused", "fused_multicast", "nccl_1bit"):
             import os
             os.environ["DLION_MULTICAST"] = "1" if comm == "fused_multicast" else "0"
-            p = torch.nn.Parameter(torch.randn(n, device=device).bfloat16())
-            p.grad = torch.randn(n, device=device).bfloat16()
+            p = torch.nn.Parameter(torch.randn(n, device=device, dtype=torch.bfloat16))
+            p.grad = torch.randn(n, device=device, dtype=torch.bfloat16)
             opt = Lion([p], lr=1e-4, weight_decay=0.1, comm="fused" if comm.startswith("fused") else comm)
             t = timeit(lambda: opt.step(), a.iters, 3, device)
             if comm.startswith("fused"):
@@ -87,9 +88,10 @@ def main():
                     t = None                      # fabric exposes no multicast pointer
             res[comm] = t
             del opt, p
+            gc.collect()
             torch.cuda.empty_cache()
-        p = torch.randn(n, device=device).bfloat16()
-        g = torch.randn(n, device=device).bfloat16()
+        p = torch.randn(n, device=device, dtype=torch.bfloat16)
+        g = torch.randn(n, device=device, dtype=torch.bfloat16)
         m = torch.zeros_like(p)
 
         def ddp_step():
@@ -101,6 +103,7 @@ def main():
             res["reference"] = timeit(lambda: ref.update_fn_distributed(p, g, m, 1e-4, 0.1, 0.9, 0.99), max(a.iters // 2, 2),
                                       1, device)
         del p, g, m
+        gc.collect()
         torch.cuda.empty_cache()
         t_hbm = (10 * n + W * n / 8) / (hbm * 1e9) * 1e3
         t_nvl = ((W - 1) * n / 8) / (nvl * 1e9) * 1e3

@@ -7,6 +7,7 @@ strategy is pluggable per bucket; see ``optim/lion.py`` for the user-facing desc
 from __future__ import annotations
 
 import os
+import weakref
 from typing import List, Optional
 
 import torch
@@ -21,7 +22,16 @@ class _Backend:
 
     def __init__(self, opt):
         self.world_size = opt.world_size
-        self.opt = opt
+        # weak: the optimizer owns its back-end; a strong back-reference would form a cycle and keep
+        # tens of GB of flat buckets alive until the cyclic GC happens to run
+        self._opt_ref = weakref.ref(opt)
+
+    @property
+    def opt(self):
+        o = self._opt_ref()
+        if o is None:
+            raise ReferenceError("the Lion optimizer that owned this back-end is gone")
+        return o
 
     def on_rebucket(self, opt) -> None:
         pass
