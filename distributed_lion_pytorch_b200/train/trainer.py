@@ -289,6 +289,7 @@ class Trainer:
                         self.sync_gradients and world > 1)
         tr_loss = torch.zeros((), device=self.device)
         logged_loss, logged_step = 0.0, start_step
+        logged_time = time.time()
         t_start = time.time()
         epoch = start_step // steps_per_epoch if steps_per_epoch else 0
         skip_micro = (start_step % steps_per_epoch) * ga if steps_per_epoch else start_step * ga
@@ -324,6 +325,11 @@ class Trainer:
                         logs["grad_norm"] = float(grad_norm)
                     if isinstance(self.optimizer, Lion) and self._dropout_schedule is not None:
                         logs["live_workers"] = self._dropout_schedule.live_count(step - 1)
+                    now = time.time()                     # tr_loss.item() above synchronised the device
+                    if tokens_per_micro and step > logged_step:
+                        logs["tokens_per_second"] = round((step - logged_step) * tokens_per_micro * ga * world
+                                                          / max(now - logged_time, 1e-9), 1)
+                    logged_time = now
                     logged_loss, logged_step = cur, step
                     logs.update(self.timer.summary())          # device-timed phase means (only with --profile_steps)
                     if isinstance(self.optimizer, Lion):
