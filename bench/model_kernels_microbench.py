@@ -85,6 +85,16 @@ def main():
     k = torch.randn(4, 1024, 32 * 128, device="cuda").to(dt)
     us = timeit(lambda: rope_launch(q, k, cos, sin, 1024, 128, False))
     row("rope llama7b q,k [4x1024x32x128]", us, 2 * 2 * q.numel() * 2)
+    from distributed_lion_pytorch_b200.ops import quant4
+    for tag, shape in (("llama7b q_proj [4096x4096]", (4096, 4096)), ("llama7b up_proj [11008x4096]", (11008, 4096))):
+        wt = (torch.randn(shape, device="cuda") * 0.02).to(dt)
+        n = wt.numel()
+        us = timeit(lambda: quant4.quantize_4bit(wt))
+        row(f"q4_quantize nf4 {tag}", us, n * 2 + n // 2 + n // 16)
+        packed, absmax = quant4.quantize_4bit(wt)
+        buf = torch.empty(n, device="cuda", dtype=dt)
+        us = timeit(lambda: quant4.dequantize_4bit(packed, absmax, shape, dt, out=buf))
+        row(f"q4_dequantize nf4 {tag}", us, n // 2 + n // 16 + n * 2)
     if a.out:
         Path(a.out).write_text(json.dumps({"peak_gbs": peak, "rows": rows_out}, indent=1))
 

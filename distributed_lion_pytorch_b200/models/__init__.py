@@ -13,6 +13,7 @@ from .gpt2 import GPT2_PRESETS, GPT2Config, GPT2LMHeadModel  # noqa: F401
 from .llama import LLAMA_PRESETS, LlamaConfig, LlamaForCausalLM  # noqa: F401
 from .lora import (LoraConfig, LoRALinear, apply_lora, disable_adapters, lora_state_dict,  # noqa: F401
                    merge_and_unload)
+from .quant import Linear4bit, dequantize_base_, quantize_base_, quantized_bytes  # noqa: F401
 
 _ALIASES = {
     "openai-community/gpt2": "gpt2", "gpt2": "gpt2", "gpt2-medium": "gpt2-medium", "gpt2-large": "gpt2-large",
@@ -43,9 +44,19 @@ def model_class_for(config):
 
 
 def build_model(name_or_path: str, *, dtype: Optional[torch.dtype] = None, device=None, pretrained: bool = True,
-                config_overrides: Optional[str] = None):
+                config_overrides: Optional[str] = None, load_in_4bit: bool = False, quant_type: str = "nf4"):
     """``AutoModelForCausalLM`` stand-in: load weights when ``name_or_path`` is a checkpoint
-    directory, otherwise random-init the named architecture (there is no hub access here)."""
+    directory, otherwise random-init the named architecture (there is no hub access here).
+    ``load_in_4bit`` turns every linear layer but the LM head into a frozen 4-bit ``Linear4bit``
+    (reference: ``quantization_config=bnb_config`` at sft_llama2.py:147-150, dpo_llama2.py:137)."""
+    model = _build_model(name_or_path, dtype=dtype, device=device, pretrained=pretrained,
+                         config_overrides=config_overrides)
+    if load_in_4bit:
+        quantize_base_(model, quant_type=quant_type)
+    return model
+
+
+def _build_model(name_or_path: str, *, dtype, device, pretrained, config_overrides):
     cfg = config_for(name_or_path)
     if config_overrides:
         cfg.update_from_string(config_overrides)

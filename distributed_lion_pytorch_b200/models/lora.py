@@ -16,6 +16,8 @@ import torch
 import torch.nn as nn
 import torch.nn.functional as F
 
+from .quant import Linear4bit, dequantize_base_
+
 
 @dataclass
 class LoraConfig:
@@ -28,16 +30,23 @@ class LoraConfig:
 
 
 class LoRALinear(nn.Module):
-    def __init__(self, base: nn.Linear, r: int, alpha: int, dropout: float):
+    """``base`` is an ``nn.Linear`` or a 4-bit :class:`Linear4bit` (the QLoRA arrangement of
+    sft_llama2.py:141-154); the adapters are always 16/32-bit parameters."""
+
+    def __init__(self, base: nn.Module, r: int, alpha: int, dropout: float):
         super().__init__()
         self.base = base
         self.r, self.scaling = r, alpha / r
-        self.lora_A = nn.Parameter(torch.empty(r, base.in_features, dtype=base.weight.dtype, device=base.weight.device))
-        self.lora_B = nn.Parameter(torch.zeros(base.out_features, r, dtype=base.weight.dtype, device=base.weight.device))
+        if isinstance(base, Linear4bit):
+            dtype, device = base.compute_dtype, base.device
+        else:
+            dtype, device = base.weight.dtype, base.weight.device
+            base.weight.requires_grad_(False)
+        self.lora_A = nn.Parameter(torch.empty(r, base.in_features, dtype=dtype, device=device))
+        self.lora_B = nn.Parameter(torch.zeros(base.out_features, r, dtype=dtype, device=device))
         nn.init.kaiming_uniform_(self.lora_A, a=math.sqrt(5))
         self.dropout = dropout
         self.enabled = True
-        base.weight.requires_grad_(False)
         if base.bias is not None:
             base.bias.requires_grad_(False)
 
@@ -50,6 +59,10 @@ class LoRALinear(nn.Module):
 
     @torch.no_grad()
     def merged(self) -> nn.Linear:
+        if isinstance(self.base, Linear4bit):      # expand the 4-bit base and fold the adapters in, in fp32
+            lin = self.base.to_linear(self.lora_B.float() @ self.lora_A.float() * self.scaling)
+            lin.weight.requires_grad_(True)
+            return lin
         self.base.weight.add_((self.lora_B.float() @ self.lora_A.float() * self.scaling).to(self.base.weight.dtype))
         self.base.weight.requires_grad_(True)
         return self.base
@@ -62,7 +75,7 @@ def apply_lora(model: nn.Module, cfg: LoraConfig) -> nn.Module:
     hits = 0
     for parent in list(model.modules()):
         for name, child in list(parent.named_children()):
-            if isinstance(child, nn.Linear) and any(name == t or name.endswith(t) for t in cfg.target_modules):
+            if isinstance(child, (nn.Linear, Linear4bit)) and any(name == t or name.endswith(t) for t in cfg.target_modules):
                 setattr(parent, name, LoRALinear(child, cfg.r, cfg.lora_alpha, cfg.lora_dropout))
                 hits += 1
     if hits == 0:
@@ -86,11 +99,16 @@ def disable_adapters(model: nn.Module):
             m.enabled = e
 
 
-def merge_and_unload(model: nn.Module) -> nn.Module:
+def merge_and_unload(model: nn.Module, dequantize: bool = True) -> nn.Module:
+    """Fold every adapter into its base layer (reference: ``merge_and_unload`` at sft_llama2.py:195-196, done
+    there on a bf16 reload of the base).  With a 4-bit base the remaining 4-bit layers are expanded too, so
+    the result is a plain 16-bit model that ``save_pretrained`` writes in the ordinary HF layout."""
     for parent in list(model.modules()):
         for name, child in list(parent.named_children()):
             if isinstance(child, LoRALinear):
                 setattr(parent, name, child.merged())
+    if dequantize:
+        dequantize_base_(model)
     for p in model.parameters():
         p.requires_grad_(True)
     if hasattr(model, "peft_config"):

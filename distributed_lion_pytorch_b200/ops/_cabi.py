@@ -83,6 +83,8 @@ def _declare(L: C.CDLL) -> None:
         "dlion_rope": [vp, vp, vp, vp, i64, i32, i32, i32, i32, i64, i64, i32, i32, vp],
         "dlion_ce_fwd_bwd": [vp, vp, vp, i64, i32, i64, i64, f32, i32, i32, vp],
         "dlion_ce_bwd_rowscale": [vp, vp, vp, i64, i32, i64, i64, i32, vp],
+        "dlion_q4_quantize": [vp, vp, vp, i64, i32, C.POINTER(f32), i32, vp],
+        "dlion_q4_dequantize": [vp, vp, vp, i64, i32, C.POINTER(f32), i32, vp],
     }
     for name, argtypes in sigs.items():
         fn = getattr(L, name)          # a missing symbol is a broken build: fail loudly

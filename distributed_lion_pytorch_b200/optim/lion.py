@@ -112,6 +112,19 @@ class Lion(Optimizer):
     def buckets(self) -> List[Bucket]:
         return self._buckets or []
 
+    @property
+    def steps_done(self) -> int:
+        """Optimizer steps taken so far.  It indexes the Philox stream of the stochastic binarisation, and
+        ``optimizer.pt`` keeps the reference's schema (no room for it), so whoever resumes a run sets it
+        back (``Trainer`` does, from ``trainer_state.json``) — otherwise the noise sequence restarts."""
+        return self._steps_done
+
+    @steps_done.setter
+    def steps_done(self, n: int) -> None:
+        if int(n) < 0:
+            raise ValueError("steps_done must be non-negative")
+        self._steps_done = int(n)
+
     def wire_bytes_per_step(self) -> int:
         """Bytes this rank *sends* per optimizer step (true 1-bit payload × peers)."""
         W = self.world_size
@@ -166,6 +179,13 @@ class Lion(Optimizer):
         """Collective: re-derive which parameters participate (call on every rank)."""
         self._buckets = None
         self._bucket_sig = None
+
+    def add_param_group(self, param_group) -> None:
+        """Adding a group after the first step re-plans the buckets at the next step (with W > 1 that
+        step re-runs the one-off agreement on the active set, so add the group on every rank)."""
+        super().add_param_group(param_group)
+        if getattr(self, "_buckets", None) is not None:
+            self.refresh_active_set()
 
     # ------------------------------------------------------------------ backend choice
     def _kernels_ok(self, device: torch.device) -> bool:

@@ -539,6 +539,8 @@ class Trainer:
         ts = os.path.join(d, "trainer_state.json")
         if os.path.exists(ts):
             self.state = TrainerState.load_from_json(ts)
+            if isinstance(self.optimizer, Lion):     # continue the stochastic-sign noise stream where it stopped
+                self.optimizer.steps_done = self.state.global_step
         rf = self._rng_file(d)
         if os.path.exists(rf):
             rng = torch.load(rf, weights_only=False)

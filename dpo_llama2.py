@@ -24,7 +24,7 @@ import torch
 
 from async_trainer import AsyncDPOTrainer
 from distributed_lion import Lion
-from distributed_lion_pytorch_b200.models import LoraConfig, build_model
+from distributed_lion_pytorch_b200.models import LoraConfig, build_model, quantize_base_
 from distributed_lion_pytorch_b200.train import (DPOTrainer, SyntheticPreferenceDataset, TrainingArguments,
                                                  get_cosine_schedule_with_warmup, load_tokenizer, parse_cli, set_seed)
 
@@ -72,6 +72,8 @@ class ScriptArguments:
     synthetic_samples: Optional[int] = field(default=512)
     model_dtype: Optional[str] = field(default="bfloat16")
     config_overrides: Optional[str] = field(default=None)
+    load_in_4bit: Optional[bool] = field(default=False, metadata={"help": "4-bit policy base and reference model (reference: :137,:151)"})
+    bnb_4bit_quant_type: Optional[str] = field(default="nf4", metadata={"help": "nf4 | fp4"})
     seed: Optional[int] = field(default=42)
     max_eval_batches: Optional[int] = field(default=8)
 
@@ -121,6 +123,11 @@ def main(argv=None):
     model_ref = build_model(script_args.model_name_or_path, dtype=dtype, device=device,
                             config_overrides=script_args.config_overrides)
     model_ref.load_state_dict(model.state_dict())        # identical start even when randomly initialised
+    if script_args.load_in_4bit:
+        if not script_args.use_lora:
+            raise ValueError("--load_in_4bit freezes the base weights; it needs --use_lora True")
+        quantize_base_(model, quant_type=script_args.bnb_4bit_quant_type)
+        quantize_base_(model_ref, quant_type=script_args.bnb_4bit_quant_type)
     vocab = model.config.vocab_size
 
     tokenizer = None

@@ -10,7 +10,8 @@ and merged weights are written under ``output_dir``.
 Deliberate differences: a ``main()`` instead of import-time execution; the optimizer is built
 AFTER the adapters exist (upstream optimises nothing with --lion); full-parameter
 bf16 training (``--use_lora False``, the BASELINE "Llama-2-7B SFT bf16" config) is supported
-next to LoRA; bitsandbytes nf4 is not available on the box and is not emulated; with
+next to LoRA; the nf4 4-bit base of upstream (:141-145, bitsandbytes there) is ``--load_in_4bit``
+here (``models/quant.py`` + ``csrc/quant4.cu``; off by default because the BASELINE config is bf16); with
 ``--synthetic_data`` (no network here) packed random-token blocks of the same shape are used.
 """
 from __future__ import annotations
@@ -25,7 +26,7 @@ import torch
 
 from async_trainer import AsyncSFTTrainer
 from distributed_lion import Lion
-from distributed_lion_pytorch_b200.models import LoraConfig, build_model, merge_and_unload
+from distributed_lion_pytorch_b200.models import LoraConfig, build_model, merge_and_unload, quantize_base_
 from distributed_lion_pytorch_b200.models.lora import print_trainable_parameters  # noqa: F401  (reference: :78-90)
 from distributed_lion_pytorch_b200.train import (ConstantLengthDataset, SFTTrainer, SyntheticTokenDataset,
                                                  TrainingArguments, get_cosine_schedule_with_warmup, load_tokenizer,
@@ -54,6 +55,8 @@ class ScriptArguments:
     use_lora: Optional[bool] = field(default=True, metadata={"help": "False = full-parameter bf16 SFT"})
     model_dtype: Optional[str] = field(default="bfloat16")
     config_overrides: Optional[str] = field(default=None)
+    load_in_4bit: Optional[bool] = field(default=False, metadata={"help": "frozen 4-bit base under LoRA (reference: :141-145)"})
+    bnb_4bit_quant_type: Optional[str] = field(default="nf4", metadata={"help": "nf4 | fp4"})
 
 
 def create_datasets(tokenizer, args: ScriptArguments, training_args: TrainingArguments, vocab_size: int):
@@ -97,6 +100,10 @@ def main(argv=None):
         if script_args.use_lora else None
     base_model = build_model(script_args.model_name, dtype=getattr(torch, script_args.model_dtype), device=device,
                              config_overrides=script_args.config_overrides)
+    if script_args.load_in_4bit:
+        if not script_args.use_lora:
+            raise ValueError("--load_in_4bit freezes the base weights; it needs --use_lora True")
+        quantize_base_(base_model, quant_type=script_args.bnb_4bit_quant_type)
     tokenizer = None
     if not training_args.synthetic_data:
         tokenizer = load_tokenizer(script_args.model_name)

@@ -200,3 +200,41 @@ def test_mixed_dtype_groups_make_separate_buckets_and_sparse_grads_are_rejected(
     emb(torch.tensor([1, 2])).sum().backward()
     with pytest.raises(RuntimeError, match="sparse"):
         o2.step()
+
+
+def test_step_counter_is_settable_and_state_dict_keeps_reference_schema():
+    m = _model(5)
+    o = Lion(m.parameters(), lr=1e-3, max_grad_norm=1.0)
+    _run(o, m, steps=3)
+    assert o.steps_done == 3
+    assert set(o.state_dict().keys()) == {"state", "param_groups"}
+    o.steps_done = 10
+    _run(o, m, steps=1)
+    assert o.steps_done == 11
+    with pytest.raises(ValueError):
+        o.steps_done = -1
+
+
+def test_add_param_group_after_first_step_is_picked_up(ref_mod):
+    torch.manual_seed(0)
+    a_ref, b_ref = torch.nn.Linear(6, 4), torch.nn.Linear(4, 2)
+    a_new, b_new = copy.deepcopy(a_ref), copy.deepcopy(b_ref)
+
+    def run(opt, a, b, late):
+        torch.manual_seed(3)
+        for s in range(4):
+            if s == 2:
+                opt.add_param_group({"params": list(b.parameters()), "lr": 5e-3, "weight_decay": 0.2})
+            x = torch.randn(3, 6)
+            opt.zero_grad()
+            b(a(x)).pow(2).mean().backward()
+            opt.step()
+
+    o_ref = ref_mod.Lion(a_ref.parameters(), lr=1e-3)
+    o_new = Lion(a_new.parameters(), lr=1e-3)
+    run(o_ref, a_ref, b_ref, True)
+    run(o_new, a_new, b_new, True)
+    for x, y in zip(list(a_ref.parameters()) + list(b_ref.parameters()),
+                    list(a_new.parameters()) + list(b_new.parameters())):
+        assert torch.equal(x, y)
+    assert len(o_new.buckets) == 2
