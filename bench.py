@@ -46,6 +46,8 @@ def parse():
     ap.add_argument("--ga", type=int, default=8)
     ap.add_argument("--comm", default="auto")
     ap.add_argument("--no-e2e", action="store_true")
+    ap.add_argument("--lora", action="store_true", help="non-default: LoRA on q_proj/v_proj (the sft_llama2 arrangement)")
+    ap.add_argument("--load-in-4bit", action="store_true", help="non-default: NF4 frozen base under --lora")
     return ap.parse_args()
 
 
@@ -168,12 +170,18 @@ def build_ours(a, device):
     from distributed_lion_pytorch_b200.train import TrainingArguments, get_cosine_schedule_with_warmup
     torch.manual_seed(1234)
     model = build_model(a.model, dtype=torch.bfloat16, device=device, pretrained=False)
+    if a.load_in_4bit:
+        from distributed_lion_pytorch_b200.models import quantize_base_
+        quantize_base_(model)
+    if a.lora:
+        from distributed_lion_pytorch_b200.models import LoraConfig, apply_lora
+        apply_lora(model, LoraConfig(target_modules=["q_proj", "v_proj"]))
     targs = TrainingArguments(output_dir="/tmp/dlion_bench", per_device_train_batch_size=a.batch,
                               gradient_accumulation_steps=a.ga, learning_rate=1e-4, weight_decay=0.1,
                               max_grad_norm=1.0, lion=True, async_grad=True, comm=a.comm, max_steps=100000,
                               warmup_steps=2000)
     comm = a.comm if a.comm in ("auto", "fused", "nccl_1bit", "local") else "auto"
-    opt = Lion(model.parameters(), lr=1e-4, weight_decay=0.1, comm=comm)
+    opt = Lion([p for p in model.parameters() if p.requires_grad], lr=1e-4, weight_decay=0.1, comm=comm)
     sched = get_cosine_schedule_with_warmup(opt, 2000, 100000)
     trainer = AsyncTrainer(model=model, args=targs, optimizers=(opt, sched))
     rt.broadcast_parameters(list(model.parameters()) + list(model.buffers()))
@@ -209,7 +217,8 @@ def run_ours(a, device, rank, world):
     tokens_per_step = a.batch * a.seq * a.ga * world
     total = max_over_ranks(total, device)
     res = {"ms_per_step": total / a.steps * 1e3, "value": tokens_per_step * a.steps / total,
-           "gpu_launches": launches, "clocks": clocks, "backend": opt.backend_name, "loss": last.get("loss")}
+           "gpu_launches": launches, "clocks": clocks, "backend": opt.backend_name, "loss": last.get("loss"),
+           "peak_mem_gb": round(torch.cuda.max_memory_allocated(device) / 2 ** 30, 2)}
     if e2e_total is not None:
         e2e_total = max_over_ranks(e2e_total, device)
         h2d = a.ga * 2 * a.batch * a.seq * 8
@@ -331,8 +340,11 @@ def main():
                                "global_batch": a.batch * world * a.ga, "per_device_batch": a.batch, "seq_len": a.seq,
                                "grad_accum": a.ga, "parallelism": f"dp{world}", "optimizer": "lion-majority-vote",
                                "sign_exchange": res["backend"], "named_config": default_cfg,
+                               "lora": bool(a.lora), "load_in_4bit": bool(a.load_in_4bit),
                                "l2": "working set >> 126 MB L2 and a 256 MB scratch write between timed steps"},
                     "clocks": res["clocks"], "gpu_launches": res["gpu_launches"], "loss": res.get("loss")}
+            if "peak_mem_gb" in res:
+                line["peak_mem_gb"] = res["peak_mem_gb"]
             if "e2e" in res:
                 line["e2e"] = res["e2e"]
             print(json.dumps(line))

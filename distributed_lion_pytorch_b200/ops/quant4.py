@@ -34,13 +34,19 @@ def code_book(quant_type: str) -> Tuple[float, ...]:
         raise ValueError(f"quant_type must be one of {sorted(CODE_BOOKS)}, got {quant_type!r}") from None
 
 
+_CODE_PTRS = {}
+
+
 def _code_ptr(quant_type: str):
-    return (C.c_float * 16)(*code_book(quant_type))
+    p = _CODE_PTRS.get(quant_type)
+    if p is None:
+        p = _CODE_PTRS[quant_type] = (C.c_float * 16)(*code_book(quant_type))
+    return p
 
 
 def _check(n: int, blocksize: int) -> None:
-    if blocksize < 64 or blocksize % 64:
-        raise ValueError(f"blocksize must be a positive multiple of 64, got {blocksize}")
+    if blocksize < 64 or blocksize & (blocksize - 1):
+        raise ValueError(f"blocksize must be a power of two >= 64 (64 ... 4096 upstream), got {blocksize}")
     if n % blocksize:
         raise ValueError(f"tensor size {n} is not a multiple of blocksize {blocksize}")
 

@@ -78,6 +78,12 @@ class ScriptArguments:
     max_eval_batches: Optional[int] = field(default=8)
 
 
+def paired_batch_to_prompts(samples) -> Dict[str, list]:
+    """Column mapping of one batch of ``lvwerra/stack-exchange-paired`` rows (reference: dpo_llama2.py:115-121)."""
+    return {"prompt": ["Question: " + q + "\n\nAnswer: " for q in samples["question"]],
+            "chosen": samples["response_j"], "rejected": samples["response_k"]}
+
+
 def get_stack_exchange_paired(data_dir: str = "data/rl", sanity_check: bool = False, cache_dir: Optional[str] = None,
                               num_proc=24):
     """{'prompt': "Question: ...\\n\\nAnswer: ", 'chosen': response_j, 'rejected': response_k}
@@ -87,11 +93,7 @@ def get_stack_exchange_paired(data_dir: str = "data/rl", sanity_check: bool = Fa
     original_columns = dataset.column_names
     if sanity_check:
         dataset = dataset.select(range(min(len(dataset), 1000)))
-
-    def return_prompt_and_responses(samples) -> Dict[str, str]:
-        return {"prompt": ["Question: " + q + "\n\nAnswer: " for q in samples["question"]],
-                "chosen": samples["response_j"], "rejected": samples["response_k"]}
-    return dataset.map(return_prompt_and_responses, batched=True, num_proc=num_proc, remove_columns=original_columns)
+    return dataset.map(paired_batch_to_prompts, batched=True, num_proc=num_proc, remove_columns=original_columns)
 
 
 def main(argv=None):

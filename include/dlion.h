@@ -218,7 +218,7 @@ int dlion_ce_bwd_rowscale(void* logits, const int64_t* labels, const float* row_
 /* Blockwise 4-bit weight codec for frozen LoRA base weights (bitsandbytes layout: element 2i in
  * the high nibble of byte i, one fp32 absmax per `blocksize` elements, 16-entry code book given
  * as a HOST pointer — NF4 or FP4).  n must be a multiple of blocksize; quantize needs
- * blocksize % 64 == 0, dequantize blocksize % 32 == 0; `packed` holds n/2 bytes and `absmax`
+ * blocksize % 64 == 0, dequantize a power of two >= 8; `packed` holds n/2 bytes and `absmax`
  * n/blocksize floats.  dtype is the type of w / out.
  * reference: BitsAndBytesConfig(load_in_4bit, nf4) at sft_llama2.py:141-145, dpo_llama2.py:137,151. */
 int dlion_q4_quantize(const void* w, void* packed, float* absmax, int64_t n, int blocksize,

@@ -146,3 +146,33 @@ def test_dpo_trainer_with_implicit_lora_reference(tmp_path):
     assert abs(losses[0] - 0.693147) < 1e-3            # adapters start at zero: policy == reference
     assert out.global_step == 3 and losses[-1] != losses[0]
     assert any("rewards/accuracies" in h for h in tr.state.log_history)
+
+
+def test_print_trainable_parameters_and_paired_dataset_mapping(monkeypatch, capsys):
+    """C19 (sft_llama2.py:78-90) and C24 (dpo_llama2.py:84-125), the latter on an in-memory stand-in for the hub set."""
+    from distributed_lion_pytorch_b200.models import LoraConfig, apply_lora, build_model
+    from distributed_lion_pytorch_b200.models.lora import print_trainable_parameters
+    m = apply_lora(build_model("llama-tiny"), LoraConfig(r=4))
+    msg = print_trainable_parameters(m)
+    trainable = sum(p.numel() for p in m.parameters() if p.requires_grad)
+    total = sum(p.numel() for p in m.parameters())
+    assert capsys.readouterr().out.strip() == msg
+    assert f"trainable params: {trainable} || all params: {total}" in msg and 0 < trainable < total
+
+    import dpo_llama2
+    rows = {"qid": [1, 2, 3], "question": ["a?", "b?", "c?"], "date": ["x"] * 3, "metadata": [["m"]] * 3,
+            "response_j": ["good a", "good b", "good c"], "response_k": ["bad a", "bad b", "bad c"]}
+    assert dpo_llama2.paired_batch_to_prompts(rows) == {
+        "prompt": ["Question: a?\n\nAnswer: ", "Question: b?\n\nAnswer: ", "Question: c?\n\nAnswer: "],
+        "chosen": rows["response_j"], "rejected": rows["response_k"]}
+    datasets = pytest.importorskip("datasets")
+    seen = {}
+
+    def fake_load(name, split=None, cache_dir=None, data_dir=None, **kw):
+        seen.update(name=name, split=split, data_dir=data_dir)
+        return datasets.Dataset.from_dict(rows)
+    monkeypatch.setattr(datasets, "load_dataset", fake_load)
+    ds = dpo_llama2.get_stack_exchange_paired("data/rl", sanity_check=True, num_proc=None)
+    assert seen == {"name": "lvwerra/stack-exchange-paired", "split": "train", "data_dir": "data/rl"}
+    assert sorted(ds.column_names) == ["chosen", "prompt", "rejected"] and len(ds) == 3
+    assert ds[1] == {"prompt": "Question: b?\n\nAnswer: ", "chosen": "good b", "rejected": "bad b"}
