@@ -124,3 +124,15 @@ def test_sft_entry_point_with_4bit_base(tmp_path):
     with pytest.raises(ValueError):
         sft_llama2.main(["--model_name", "llama-tiny", "--synthetic_data", "--max_steps", "1", "--load_in_4bit",
                          "--use_lora", "False", "--output_dir", str(out)])
+
+
+def test_dpo_entry_point_with_4bit_policy_and_reference(tmp_path):
+    """reference: dpo_llama2.py:133-152 loads BOTH the policy and the frozen reference model in 4 bit."""
+    import dpo_llama2
+    out = tmp_path / "dpo4"
+    dpo_llama2.main([
+        "--model_name_or_path", "llama-tiny", "--synthetic_data", "--synthetic_samples", "16", "--max_prompt_length", "8",
+        "--max_length", "24", "--max_steps", "2", "--per_device_train_batch_size", "2", "--learning_rate", "1e-3",
+        "--lion", "--async_grad", "--load_in_4bit", "--logging_steps", "1", "--eval_steps", "100", "--save_steps", "100",
+        "--model_dtype", "float32", "--output_dir", str(out)])
+    assert (out / "final_checkpoint").is_dir()
