@@ -72,7 +72,7 @@ def build(force: bool = False, verbose: bool = False) -> Path:
     objs = [str(o) for o, _ in results]
     for (o, err), s in zip(results, srcs):
         log_lines.append(f"==== {s.name}\n{err}")
-    link = [nvcc, *ARCH_FLAGS, "-shared", "-o", str(LIB), *objs, "-cudart", "static"]
+    link = [nvcc, *ARCH_FLAGS, "-shared", "-o", str(LIB), *objs, "-cudart", "static", "-ldl"]
     r = subprocess.run(link, capture_output=True, text=True)
     if r.returncode != 0:
         raise RuntimeError(f"link failed:\n{r.stdout}\n{r.stderr}")

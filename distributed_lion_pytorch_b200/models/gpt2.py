@@ -21,6 +21,7 @@ from torch.utils.checkpoint import checkpoint
 from ..ops.activation import gelu_tanh
 from ..ops.cross_entropy import linear_cross_entropy, linear_log_probs
 from ..ops.linear import fused_linear
+from ..ops.lt_gemm import linear_gelu
 from ..ops.norm import add_layer_norm
 from .common import CausalLMOutput, ConfigBase, PreTrainedMixin, shift_labels
 
@@ -113,8 +114,12 @@ class GPT2MLP(nn.Module):
         self.act = cfg.activation_function
 
     def forward(self, x):
-        h = self.c_fc(x)
-        h = gelu_tanh(h) if self.act in ("gelu_new", "gelu_pytorch_tanh") else F.gelu(h)
+        if self.act in ("gelu_new", "gelu_pytorch_tanh"):
+            h = linear_gelu(x, self.c_fc.weight, self.c_fc.bias)        # GEMM with the GELU in its epilogue
+            if h is None:
+                h = gelu_tanh(self.c_fc(x))
+        else:
+            h = F.gelu(self.c_fc(x))
         return self.c_proj(h)
 
 

@@ -38,6 +38,17 @@ class FusedArgs(C.Structure):
     ]
 
 
+class LtArgs(C.Structure):
+    """``dlion_lt_args`` (include/dlion.h): one cuBLASLt GEMM with a training epilogue."""
+    _fields_ = [("a", C.c_void_p), ("b", C.c_void_p), ("d", C.c_void_p),
+                ("m", C.c_int64), ("n", C.c_int64), ("k", C.c_int64),
+                ("lda", C.c_int64), ("ldb", C.c_int64), ("ldd", C.c_int64),
+                ("trans_a", C.c_int), ("trans_b", C.c_int), ("alpha", C.c_float), ("beta", C.c_float),
+                ("epilogue", C.c_int), ("bias", C.c_void_p), ("bias_grad", C.c_void_p), ("aux", C.c_void_p),
+                ("ld_aux", C.c_int64), ("workspace", C.c_void_p), ("workspace_bytes", C.c_int64), ("dtype", C.c_int),
+                ("algo_rank", C.c_int)]
+
+
 def dtype_code(dt: torch.dtype) -> int:
     try:
         return _DTYPES[dt]
@@ -83,6 +94,8 @@ def _declare(L: C.CDLL) -> None:
         "dlion_rope": [vp, vp, vp, vp, i64, i32, i32, i32, i32, i64, i64, i32, i32, vp],
         "dlion_ce_fwd_bwd": [vp, vp, vp, i64, i32, i64, i64, f32, i32, i32, vp],
         "dlion_ce_bwd_rowscale": [vp, vp, vp, i64, i32, i64, i64, i32, vp],
+        "dlion_lt_available": [],
+        "dlion_lt_gemm": [C.POINTER(LtArgs), vp],
         "dlion_q4_quantize": [vp, vp, vp, i64, i32, C.POINTER(f32), i32, vp],
         "dlion_q4_dequantize": [vp, vp, vp, i64, i32, C.POINTER(f32), i32, vp],
     }

@@ -226,6 +226,42 @@ int dlion_q4_quantize(const void* w, void* packed, float* absmax, int64_t n, int
 int dlion_q4_dequantize(const void* packed, const float* absmax, void* out, int64_t n, int blocksize,
                         const float* code16, int dtype, void* stream);
 
+/* Library GEMMs with cuBLASLt's training epilogues (the ones PyTorch does not expose).  Row-major:
+ * d[m,n] (ld ldd) = alpha * op(a) @ op(b) + beta * d, a stored [m,k] (trans_a = 0) or [k,m], b stored
+ * [k,n] (trans_b = 0) or [n,k].  Epilogues:
+ *   DLION_LT_BIAS           d = a@b + bias[n]
+ *   DLION_LT_GELU_AUX_BIAS  aux[m,n] = a@b + bias;  d = gelu_tanh(aux)
+ *   DLION_LT_DGELU_BGRAD    d = gelu_tanh'(aux) * (a@b);  bias_grad[n] = sum_m d[m,n]
+ *   DLION_LT_BGRAD_B        d = a@b (+ beta*d);  bias_grad[n] = sum_k b[k,n]   (weight + bias gradient in one pass)
+ *   DLION_LT_DGELU          d = gelu_tanh'(aux) * (a@b)
+ * `algo_rank` picks the r-th candidate of the library's heuristic (0 = its first choice); callers that tune time
+ * a few ranks on scratch buffers and keep the fastest.
+ * cuBLASLt is looked up at run time (dlopen), not linked: dlion_lt_available() says whether it was found;
+ * without it, or when the library has no kernel for the request, dlion_lt_gemm returns DLION_E_UNSUPPORTED
+ * and the caller keeps its unfused path.  `workspace` is caller-owned scratch (32 MiB is plenty).
+ * reference: HF GPT-2 MLP forward/backward under autograd (run_clm.py:588-639). */
+enum { DLION_LT_NONE = 0, DLION_LT_BIAS = 1, DLION_LT_GELU_AUX_BIAS = 2, DLION_LT_DGELU_BGRAD = 3, DLION_LT_BGRAD_B = 4,
+       DLION_LT_DGELU = 5 };
+typedef struct {
+  const void* a;
+  const void* b;
+  void* d;
+  int64_t m, n, k, lda, ldb, ldd;
+  int trans_a, trans_b;
+  float alpha, beta;
+  int epilogue;
+  const void* bias;
+  void* bias_grad;
+  void* aux;
+  int64_t ld_aux;
+  void* workspace;
+  int64_t workspace_bytes;
+  int dtype;
+  int algo_rank;
+} dlion_lt_args;
+int dlion_lt_available(void);
+int dlion_lt_gemm(const dlion_lt_args* args, void* stream);
+
 #ifdef __cplusplus
 }
 #endif
