@@ -8,7 +8,7 @@ from typing import Optional
 
 import torch
 
-from .common import CausalLMOutput  # noqa: F401
+from .common import CausalLMOutput, checkpoint_files, has_weights, load_checkpoint_into  # noqa: F401
 from .gpt2 import GPT2_PRESETS, GPT2Config, GPT2LMHeadModel  # noqa: F401
 from .llama import LLAMA_PRESETS, LlamaConfig, LlamaForCausalLM  # noqa: F401
 from .lora import (LoraConfig, LoRALinear, apply_lora, disable_adapters, lora_state_dict,  # noqa: F401
@@ -61,8 +61,7 @@ def _build_model(name_or_path: str, *, dtype, device, pretrained, config_overrid
     if config_overrides:
         cfg.update_from_string(config_overrides)
     cls = model_class_for(cfg)
-    is_ckpt = os.path.isdir(name_or_path) and any(
-        os.path.exists(os.path.join(name_or_path, f)) for f in ("model.safetensors", "pytorch_model.bin"))
+    is_ckpt = has_weights(name_or_path)
     if pretrained and is_ckpt:
         return cls.from_pretrained(name_or_path, dtype=dtype, device=device)
     ctx = torch.device(device) if device is not None else contextlib.nullcontext()

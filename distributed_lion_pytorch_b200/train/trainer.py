@@ -520,13 +520,8 @@ class Trainer:
     def _load_checkpoint(self, d: str) -> None:
         if not os.path.isdir(d):
             raise FileNotFoundError(d)
-        st = os.path.join(d, "model.safetensors")
-        if os.path.exists(st):
-            from safetensors.torch import load_file
-            sd = load_file(st)
-        else:
-            sd = torch.load(os.path.join(d, "pytorch_model.bin"), map_location="cpu")
-        self.model.load_state_dict(sd, strict=False)
+        from ..models.common import load_checkpoint_into
+        load_checkpoint_into(self.model, d)          # single-file or sharded, safetensors or .bin
         if hasattr(self.model, "tie_weights"):
             self.model.tie_weights()
         mine = os.path.join(d, f"optimizer_rank{rt.rank()}.pt")

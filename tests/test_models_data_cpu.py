@@ -176,3 +176,64 @@ def test_print_trainable_parameters_and_paired_dataset_mapping(monkeypatch, caps
     assert seen == {"name": "lvwerra/stack-exchange-paired", "split": "train", "data_dir": "data/rl"}
     assert sorted(ds.column_names) == ["chosen", "prompt", "rejected"] and len(ds) == 3
     assert ds[1] == {"prompt": "Question: b?\n\nAnswer: ", "chosen": "good b", "rejected": "bad b"}
+
+
+@pytest.mark.parametrize("family", ["gpt2-tiny", "llama-tiny"])
+@pytest.mark.parametrize("safe", [True, False])
+def test_sharded_checkpoints_round_trip_and_interchange_with_transformers(tmp_path, family, safe):
+    """A real Llama-2-7b-hf directory is sharded (model-0000i-of-0000n.safetensors + index); both directions."""
+    import os
+    from distributed_lion_pytorch_b200.models import build_model, checkpoint_files
+    torch.manual_seed(0)
+    m = build_model(family).eval()
+    ids = torch.randint(0, 512, (2, 16))
+    with torch.no_grad():
+        ref = m(ids).logits
+    d = str(tmp_path / "ours")
+    m.save_pretrained(d, safe_serialization=safe, max_shard_size="64KB")
+    files = checkpoint_files(d)
+    assert len(files) > 2 and all(("-of-" in os.path.basename(f)) for f in files)
+    back = build_model(d).eval()
+    with torch.no_grad():
+        assert torch.equal(back(ids).logits, ref)
+    if family == "gpt2-tiny":
+        assert back.lm_head.weight is back.transformer.wte.weight           # tying survives the meta-device build
+    # bf16 on load: built directly in the target dtype
+    assert next(build_model(d, dtype=torch.bfloat16).parameters()).dtype == torch.bfloat16
+    # saving again as a single file removes the stale shards and index
+    m.save_pretrained(d, safe_serialization=safe)
+    assert sorted(os.listdir(d)) == ["config.json", "model.safetensors" if safe else "pytorch_model.bin"]
+    if not safe:
+        return
+    transformers = pytest.importorskip("transformers")
+    m.save_pretrained(d, max_shard_size="64KB")
+    hf = transformers.AutoModelForCausalLM.from_pretrained(d).eval()       # ours (sharded) -> transformers
+    with torch.no_grad():
+        assert torch.allclose(hf(ids).logits, ref, atol=1e-5)
+    d2 = str(tmp_path / "theirs")
+    hf.save_pretrained(d2, max_shard_size="64KB")                          # transformers (sharded) -> ours
+    assert len(checkpoint_files(d2)) > 2
+    with torch.no_grad():
+        assert torch.allclose(build_model(d2).eval()(ids).logits, ref, atol=1e-5)
+
+
+def test_checkpoint_loader_reports_problems(tmp_path):
+    import json
+    from distributed_lion_pytorch_b200.models import build_model, checkpoint_files, load_checkpoint_into
+    m = build_model("llama-tiny")
+    d = str(tmp_path / "ck")
+    m.save_pretrained(d, max_shard_size="64KB")
+    files = checkpoint_files(d)
+    import os
+    os.remove(files[1])
+    with pytest.raises(FileNotFoundError, match="shards that are not there"):
+        checkpoint_files(d)
+    with pytest.raises(FileNotFoundError, match="no model weights"):
+        checkpoint_files(str(tmp_path))
+    m.save_pretrained(d)
+    other = build_model("llama-tiny", config_overrides="num_hidden_layers=1")
+    missing, unexpected = load_checkpoint_into(other, d)
+    assert not missing and unexpected and all(".layers.1." in k for k in unexpected)
+    wide = build_model("llama-tiny", config_overrides="intermediate_size=192")
+    with pytest.raises(RuntimeError, match="shape"):
+        load_checkpoint_into(wide, d)
