@@ -238,3 +238,24 @@ def test_per_rank_momentum_survives_resume(tmp_path):
     outs = run_distributed(_worker_per_rank_resume, 2, str(tmp_path))
     assert all(o["params_equal"] and o["mom_equal"] for o in outs)
     assert not torch.equal(outs[0]["mom"], outs[1]["mom"])
+
+
+def test_run_clm_on_text_files_with_eval_metrics(tmp_path):
+    """reference: run_clm.py:352-381 (text files), :562-577 (accuracy), :628-639 (perplexity)."""
+    import json
+    import run_clm
+    text = "\n".join(f"the quick brown fox number {i} jumps over the lazy dog" for i in range(400))
+    (tmp_path / "train.txt").write_text(text)
+    (tmp_path / "valid.txt").write_text(text[:4000])
+    out = tmp_path / "out"
+    res = run_clm.main([
+        "--model_type", "gpt2-tiny", "--train_file", str(tmp_path / "train.txt"), "--validation_file",
+        str(tmp_path / "valid.txt"), "--block_size", "64", "--do_train", "--do_eval", "--max_steps", "12",
+        "--per_device_train_batch_size", "4", "--per_device_eval_batch_size", "4", "--learning_rate", "3e-3", "--lion",
+        "--async_grad", "--logging_steps", "4", "--save_strategy", "no", "--output_dir", str(out)])
+    assert res["train_samples"] > 0 and 0.0 <= res["eval_accuracy"] <= 1.0
+    assert abs(res["perplexity"] - __import__("math").exp(res["eval_loss"])) < 1e-6
+    hist = json.loads((out / "trainer_state.json").read_text())["log_history"]
+    losses = [h["loss"] for h in hist if "loss" in h]
+    assert losses[-1] < losses[0]                              # byte-level LM on repetitive text learns quickly
+    assert {"all_results.json", "train_results.json", "eval_results.json", "README.md"} <= set(p.name for p in out.iterdir())
