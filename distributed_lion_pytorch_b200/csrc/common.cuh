@@ -124,6 +124,51 @@ __device__ __forceinline__ void store8<__half>(__half* __restrict__ ptr, const f
   *reinterpret_cast<uint4*>(ptr) = make_uint4(w[0], w[1], w[2], w[3]);
 }
 
+// Raw (unconverted) 8-element vectors: lets a kernel issue the loads of a later iteration early and pay
+// the conversion only when the values are consumed.
+template <typename T>
+struct Raw8 {
+  uint4 q[sizeof(T) * 8 / 16];
+};
+template <typename T>
+__device__ __forceinline__ Raw8<T> load_raw8(const T* __restrict__ ptr) {
+  Raw8<T> r;
+#pragma unroll
+  for (int i = 0; i < (int)(sizeof(T) * 8 / 16); ++i) r.q[i] = reinterpret_cast<const uint4*>(ptr)[i];
+  return r;
+}
+template <typename T>
+__device__ __forceinline__ void unpack_raw8(const Raw8<T>& r, float (&v)[8]);
+template <>
+__device__ __forceinline__ void unpack_raw8<float>(const Raw8<float>& r, float (&v)[8]) {
+#pragma unroll
+  for (int i = 0; i < 2; ++i) {
+    v[4 * i] = __uint_as_float(r.q[i].x);
+    v[4 * i + 1] = __uint_as_float(r.q[i].y);
+    v[4 * i + 2] = __uint_as_float(r.q[i].z);
+    v[4 * i + 3] = __uint_as_float(r.q[i].w);
+  }
+}
+template <>
+__device__ __forceinline__ void unpack_raw8<__nv_bfloat16>(const Raw8<__nv_bfloat16>& r, float (&v)[8]) {
+  const uint32_t w[4] = {r.q[0].x, r.q[0].y, r.q[0].z, r.q[0].w};
+#pragma unroll
+  for (int i = 0; i < 4; ++i) {
+    v[2 * i] = __uint_as_float(w[i] << 16);
+    v[2 * i + 1] = __uint_as_float(w[i] & 0xffff0000u);
+  }
+}
+template <>
+__device__ __forceinline__ void unpack_raw8<__half>(const Raw8<__half>& r, float (&v)[8]) {
+  const uint32_t w[4] = {r.q[0].x, r.q[0].y, r.q[0].z, r.q[0].w};
+#pragma unroll
+  for (int i = 0; i < 4; ++i) {
+    const float2 f = __half22float2(*reinterpret_cast<const __half2*>(&w[i]));
+    v[2 * i] = f.x;
+    v[2 * i + 1] = f.y;
+  }
+}
+
 // ------------------------------------------------------------------ rounding through the storage type
 // round8: v[i] <- float(T(v[i])).  Packed converts (F2FP.*.PACK_AB, two values per ALU-pipe
 // instruction) instead of eight scalar F2F on the slow conversion pipe: with six roundings per
