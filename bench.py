@@ -331,8 +331,11 @@ def main():
         if "unavailable" in res:
             print(json.dumps({"impl": "reference", "unavailable": res["unavailable"]}))
         else:
-            default_cfg = (a.model, a.batch, a.seq, a.ga) == ("gpt2", 20, 1024, 8)
-            line = {"metric": METRIC, "value": res["value"], "unit": "tokens/s", "n_gpus": world, "steps": a.steps,
+            default_cfg = (a.model, a.batch, a.seq, a.ga, a.lora, a.load_in_4bit) == ("gpt2", 20, 1024, 8, False, False)
+            metric = METRIC if default_cfg else (
+                f"tokens/sec/box {a.model} Lion training (per-device batch {a.batch}x{a.seq}, grad-accum {a.ga}, bf16"
+                + (", LoRA" if a.lora else "") + (", NF4 base" if a.load_in_4bit else "") + ")")
+            line = {"metric": metric, "value": res["value"], "unit": "tokens/s", "n_gpus": world, "steps": a.steps,
                     "warmup": a.warmup, "ms_per_step": res["ms_per_step"], "higher_is_better": True,
                     "scaling": "weak", "vs_baseline": None, "dtype": "bf16", "data": "synthetic",
                     "impl": a.impl,

@@ -254,3 +254,36 @@ def test_activation_kernels(dtype):
     t = dict(rtol=3e-2, atol=3e-2) if dtype == torch.bfloat16 else dict(rtol=1e-5, atol=1e-5)
     assert torch.allclose(o.float(), of, **t)
     assert torch.allclose(g.grad.float(), gf.grad, **t) and torch.allclose(u.grad.float(), uf.grad, **t)
+
+
+@pytest.mark.parametrize("dtype", [torch.float32, torch.bfloat16])
+@pytest.mark.parametrize("cols,rows,rms", [(768, 2 * 3108 + 17, False), (4096, 3 * 1184 + 5, True), (64, 3 * 9472 + 1, False)])
+def test_add_norm_many_rows_per_cta(dtype, cols, rows, rms):
+    """More rows than resident CTAs: every CTA walks several rows, which is the software-pipelined path of the
+    forward (next row's loads in flight while this one is reduced) and the partial-row accumulation of the backward."""
+    from distributed_lion_pytorch_b200.ops.norm import add_layer_norm, add_rms_norm
+    torch.manual_seed(rows)
+    x = torch.randn(rows, cols, device="cuda").to(dtype).requires_grad_()
+    r = torch.randn(rows, cols, device="cuda").to(dtype).requires_grad_()
+    w = (1 + 0.1 * torch.randn(cols, device="cuda")).to(dtype).requires_grad_()
+    b = (0.1 * torch.randn(cols, device="cuda")).to(dtype).requires_grad_() if not rms else None
+    y, s = add_rms_norm(x, r, w, 1e-5) if rms else add_layer_norm(x, r, w, b, 1e-5)
+    dy = torch.randn_like(y)
+    y.backward(dy)
+    xf, rf, wf = (t.detach().float().requires_grad_() for t in (x, r, w))
+    sf = xf + rf
+    if dtype == torch.bfloat16:
+        sf = sf + (sf.detach().to(dtype).float() - sf.detach())
+    if rms:
+        yf = wf * (sf * torch.rsqrt(sf.pow(2).mean(-1, keepdim=True) + 1e-5))
+    else:
+        bf = b.detach().float().requires_grad_()
+        yf = F.layer_norm(sf, (cols,), wf, bf, 1e-5)
+    yf.backward(dy.float())
+    t = _tol(dtype)
+    assert torch.allclose(y.float(), yf, **t)
+    assert torch.equal(s.float(), sf.detach()) or torch.allclose(s.float(), sf.detach(), **t)
+    assert torch.allclose(x.grad.float(), xf.grad, **t)
+    assert torch.allclose(r.grad.float(), rf.grad, **t)
+    scale = float(wf.grad.abs().max())
+    assert float((w.grad.float() - wf.grad).abs().max()) < (3e-2 if dtype == torch.bfloat16 else 1e-3) * scale
