@@ -187,14 +187,15 @@ def test_fused_linear_accumulates_into_existing_grads(dtype, in_out, with_bias):
 
 
 @pytest.mark.parametrize("dtype", [torch.float32, torch.bfloat16])
-@pytest.mark.parametrize("rms,with_res,cols", [(False, True, 768), (False, False, 768), (True, True, 4096)])
-def test_add_norm_with_fused_dropout(dtype, rms, with_res, cols):
+@pytest.mark.parametrize("rms,with_res,cols,rows", [(False, True, 768, 512), (False, False, 768, 512), (True, True, 4096, 512),
+                                                    (False, True, 768, 2 * 3108 + 5)])      # last: several rows per CTA
+def test_add_norm_with_fused_dropout(dtype, rms, with_res, cols, rows):
     """dropout(x) + residual + norm in one kernel: the keep-mask is regenerated from the seed in
     the backward.  The mask is recovered from the kernel's own output and the op is then compared
     with plain autograd using that fixed mask."""
     from distributed_lion_pytorch_b200.ops.norm import _FusedNorm
     torch.manual_seed(1)
-    rows, p, seed = 512, 0.3, 12345
+    p, seed = 0.3, 12345
     x = (torch.randn(rows, cols, device="cuda") + 8.0).to(dtype).requires_grad_()       # kept values stay far from zero
     r = torch.randn(rows, cols, device="cuda").to(dtype).requires_grad_() if with_res else None
     w = (1 + 0.1 * torch.randn(cols, device="cuda")).to(dtype).requires_grad_()
