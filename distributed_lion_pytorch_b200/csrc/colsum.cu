@@ -14,10 +14,15 @@ namespace dlion {
 
 constexpr int kColsumParts = kNumSMs * 4;
 
-template <typename T>
+// FUSED: the CTA that finishes last on a 256-column tile (ticket per tile, self-resetting) folds the
+// tile's partial rows and writes — or accumulates into — the final [cols] vector, so the bias gradient
+// needs one launch instead of three (partials, fold, add into .grad).
+template <typename T, bool FUSED>
 __global__ void __launch_bounds__(256) colsum_kernel(const T* __restrict__ x, float* __restrict__ partial,
-                                                     int64_t rows, int cols) {
+                                                     int64_t rows, int cols, unsigned int* __restrict__ tickets,
+                                                     T* __restrict__ out, int accumulate) {
   __shared__ float sm[8][32][9];
+  __shared__ bool is_last;
   const int lane = threadIdx.x & 31, rl = threadIdx.x >> 5;
   const int cg = blockIdx.x * 32 + lane;          // 8-column group
   const bool live = cg * 8 < cols;
@@ -51,6 +56,38 @@ __global__ void __launch_bounds__(256) colsum_kernel(const T* __restrict__ x, fl
     for (int q = 0; q < 8; ++q) s += sm[q][c >> 3][c & 7];
     partial[(int64_t)blockIdx.y * cols + col] = s;
   }
+  if constexpr (FUSED) {
+    __threadfence();                               // this CTA's partial row is visible before its ticket
+    __syncthreads();
+    if (threadIdx.x == 0) {
+      const unsigned int t = atomicAdd(&tickets[blockIdx.x], 1u);
+      is_last = (t == gridDim.y - 1);
+      if (is_last) tickets[blockIdx.x] = 0u;       // ready for the next call on this stream
+    }
+    __syncthreads();
+    if (!is_last) return;
+    __threadfence();                               // acquire: the other CTAs' partial rows
+    float tot[8] = {0.f, 0.f, 0.f, 0.f, 0.f, 0.f, 0.f, 0.f};
+    if (live) {
+      for (int p = rl; p < (int)gridDim.y; p += 8) {
+        const float4* src = reinterpret_cast<const float4*>(partial + (int64_t)p * cols + cg * 8);
+        const float4 u = __ldcg(src), v = __ldcg(src + 1);          // L2: written by other SMs
+        tot[0] += u.x; tot[1] += u.y; tot[2] += u.z; tot[3] += u.w;
+        tot[4] += v.x; tot[5] += v.y; tot[6] += v.z; tot[7] += v.w;
+      }
+    }
+    __syncthreads();                               // sm is reused
+#pragma unroll
+    for (int i = 0; i < 8; ++i) sm[rl][lane][i] = tot[i];
+    __syncthreads();
+    if (col < cols) {
+      float s = 0.f;
+#pragma unroll
+      for (int q = 0; q < 8; ++q) s += sm[q][c >> 3][c & 7];
+      if (accumulate) s += DT<T>::to_f(out[col]);
+      out[col] = DT<T>::from_f(s);
+    }
+  }
 }
 
 }  // namespace dlion
@@ -71,6 +108,20 @@ extern "C" int dlion_colsum(const void* x, int64_t rows, int cols, float* partia
   if (rows == 0) return 0;
   const dim3 grid((cols + 255) / 256, dlion_colsum_parts(rows, cols));
   cudaStream_t s = (cudaStream_t)stream;
-  DISPATCH_DTYPE(dtype, colsum_kernel<T><<<grid, 256, 0, s>>>((const T*)x, partial, rows, cols));
+  DISPATCH_DTYPE(dtype, (colsum_kernel<T, false><<<grid, 256, 0, s>>>((const T*)x, partial, rows, cols, nullptr, nullptr, 0)));
   return DLION_LAUNCH_CHECK("dlion_colsum");
+}
+
+extern "C" int dlion_colsum_tiles(int cols) { return (cols + 255) / 256; }
+
+extern "C" int dlion_colsum_fused(const void* x, int64_t rows, int cols, float* partial, unsigned int* tickets,
+                                  void* out, int accumulate, int dtype, void* stream) {
+  DLION_CHECK_ARG(rows > 0 && cols > 0 && (cols & 7) == 0, "dlion_colsum_fused: cols (%d) must be a positive multiple of 8", cols);
+  DLION_CHECK_ARG(aligned16(x) && partial != nullptr && tickets != nullptr && out != nullptr,
+                  "dlion_colsum_fused: bad pointers");
+  const dim3 grid((cols + 255) / 256, dlion_colsum_parts(rows, cols));
+  cudaStream_t s = (cudaStream_t)stream;
+  DISPATCH_DTYPE(dtype, (colsum_kernel<T, true><<<grid, 256, 0, s>>>((const T*)x, partial, rows, cols, tickets, (T*)out,
+                                                                     accumulate)));
+  return DLION_LAUNCH_CHECK("dlion_colsum_fused");
 }

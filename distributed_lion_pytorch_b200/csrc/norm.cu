@@ -308,7 +308,7 @@ template <typename T>
 __global__ void __launch_bounds__(1024) norm_bwd_finalize_kernel(const float* __restrict__ dw_part,
                                                                  const float* __restrict__ db_part,
                                                                  T* __restrict__ dw, T* __restrict__ db, int parts,
-                                                                 int cols) {
+                                                                 int cols, int acc_mask) {
   __shared__ float4 sw[128][8], sb[128][8];
   const int tx = threadIdx.x, ty = threadIdx.y;
   const int c0 = blockIdx.x * 32 + tx * 4;
@@ -336,10 +336,18 @@ __global__ void __launch_bounds__(1024) norm_bwd_finalize_kernel(const float* __
     __syncthreads();
   }
   if (ty == 0 && c0 < cols) {
-    const float4 a = sw[0][tx], b2 = sb[0][tx];
+    float4 a = sw[0][tx], b2 = sb[0][tx];
+    if (acc_mask & 1) {     // accumulate into the existing gradient: one fp32 add, one rounding (no add kernel later)
+      a.x += DT<T>::to_f(dw[c0]); a.y += DT<T>::to_f(dw[c0 + 1]);
+      a.z += DT<T>::to_f(dw[c0 + 2]); a.w += DT<T>::to_f(dw[c0 + 3]);
+    }
     dw[c0] = DT<T>::from_f(a.x); dw[c0 + 1] = DT<T>::from_f(a.y);
     dw[c0 + 2] = DT<T>::from_f(a.z); dw[c0 + 3] = DT<T>::from_f(a.w);
     if (db != nullptr && db_part != nullptr) {
+      if (acc_mask & 2) {
+        b2.x += DT<T>::to_f(db[c0]); b2.y += DT<T>::to_f(db[c0 + 1]);
+        b2.z += DT<T>::to_f(db[c0 + 2]); b2.w += DT<T>::to_f(db[c0 + 3]);
+      }
       db[c0] = DT<T>::from_f(b2.x); db[c0 + 1] = DT<T>::from_f(b2.y);
       db[c0 + 2] = DT<T>::from_f(b2.z); db[c0 + 3] = DT<T>::from_f(b2.w);
     }
@@ -516,13 +524,19 @@ extern "C" int dlion_norm_bwd(const void* dy, const void* dsum_in, const void* x
   return DLION_E_UNSUPPORTED;
 }
 
-extern "C" int dlion_norm_bwd_finalize(const float* dw_partial, const float* db_partial, void* dweight, void* dbias,
-                                       int parts, int cols, int dtype, void* stream) {
-  DLION_CHECK_ARG(parts > 0 && cols > 0 && dw_partial && dweight, "dlion_norm_bwd_finalize: bad arguments");
+extern "C" int dlion_norm_bwd_finalize_acc(const float* dw_partial, const float* db_partial, void* dweight,
+                                           void* dbias, int parts, int cols, int acc_mask, int dtype, void* stream) {
+  DLION_CHECK_ARG(parts > 0 && cols > 0 && (cols & 3) == 0 && dw_partial && dweight,
+                  "dlion_norm_bwd_finalize: bad arguments");
   cudaStream_t s = (cudaStream_t)stream;
   const dim3 block(8, 128);
   const int grid = (cols + 31) / 32;
   DISPATCH_DTYPE(dtype, norm_bwd_finalize_kernel<T><<<grid, block, 0, s>>>(dw_partial, db_partial, (T*)dweight,
-                                                                             (T*)dbias, parts, cols));
+                                                                             (T*)dbias, parts, cols, acc_mask));
   return DLION_LAUNCH_CHECK("dlion_norm_bwd_finalize");
+}
+
+extern "C" int dlion_norm_bwd_finalize(const float* dw_partial, const float* db_partial, void* dweight, void* dbias,
+                                       int parts, int cols, int dtype, void* stream) {
+  return dlion_norm_bwd_finalize_acc(dw_partial, db_partial, dweight, dbias, parts, cols, 0, dtype, stream);
 }

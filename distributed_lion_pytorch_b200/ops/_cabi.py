@@ -87,6 +87,9 @@ def _declare(L: C.CDLL) -> None:
         "dlion_norm_bwd_finalize": [vp, vp, vp, vp, i32, i32, i32, vp],
         "dlion_colsum_parts": [i64, i32],
         "dlion_colsum": [vp, i64, i32, vp, i32, vp],
+        "dlion_colsum_tiles": [i32],
+        "dlion_colsum_fused": [vp, i64, i32, vp, vp, vp, i32, i32, vp],
+        "dlion_norm_bwd_finalize_acc": [vp, vp, vp, vp, i32, i32, i32, i32, vp],
         "dlion_gelu_tanh_fwd": [vp, vp, i64, i32, vp],
         "dlion_gelu_tanh_bwd": [vp, vp, vp, i64, i32, vp],
         "dlion_swiglu_fwd": [vp, vp, vp, i64, i32, vp],

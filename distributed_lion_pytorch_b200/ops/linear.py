@@ -18,25 +18,65 @@ import torch
 from . import _cabi, require_library
 
 _FUSE_WGRAD = os.environ.get("DLION_FUSE_WGRAD", "1") == "1"
+_FUSE_COLSUM = os.environ.get("DLION_FUSE_COLSUM", "1") == "1"
 
 
-def column_sum(dy2: torch.Tensor, out_dtype: torch.dtype) -> torch.Tensor:
-    """[rows, cols] -> [cols] (fp32 accumulation)."""
+_TICKETS: dict = {}
+_MAX_TILES = 64
+
+
+def _tickets(device: torch.device) -> torch.Tensor:
+    """Zeroed uint32 counters for the one-launch column sum; the kernel leaves them zeroed, and every call on a
+    device goes through the one stream autograd uses there, so a single cached buffer is enough."""
+    t = _TICKETS.get(device)
+    if t is None:
+        t = _TICKETS[device] = torch.zeros(_MAX_TILES, dtype=torch.int32, device=device)
+    return t
+
+
+def _kernel_ok(dy2: torch.Tensor) -> bool:
+    return dy2.is_cuda and require_library() and dy2.shape[1] % 8 == 0 and dy2.is_contiguous() \
+        and dy2.data_ptr() % 16 == 0 and dy2.dtype in (torch.float32, torch.bfloat16, torch.float16) and dy2.shape[0] > 0
+
+
+def column_sum(dy2: torch.Tensor, out_dtype: torch.dtype, accumulate_into: Optional[torch.Tensor] = None):
+    """[rows, cols] -> [cols] (fp32 accumulation).  With ``accumulate_into`` (a [cols] gradient buffer) the sums are
+    added to it — inside the same kernel when dtypes allow — and ``None`` is returned."""
     rows, cols = dy2.shape
-    if dy2.is_cuda and require_library() and cols % 8 == 0 and dy2.is_contiguous() and dy2.data_ptr() % 16 == 0 \
-            and dy2.dtype in (torch.float32, torch.bfloat16, torch.float16):
+    if _kernel_ok(dy2):
         L = _cabi.lib()
         parts = int(L.dlion_colsum_parts(rows, cols))
         partial = torch.empty(parts, cols, dtype=torch.float32, device=dy2.device)
-        out = torch.empty(cols, dtype=out_dtype, device=dy2.device)
+        acc = accumulate_into
+        one_launch = out_dtype == dy2.dtype and int(L.dlion_colsum_tiles(cols)) <= _MAX_TILES and _FUSE_COLSUM \
+            and (acc is None or (acc.dtype == out_dtype and acc.is_contiguous() and acc.shape == (cols,)))
         with torch.cuda.device(dy2.device):
             st = _cabi.stream_ptr(dy2.device)
+            if one_launch:
+                out = acc if acc is not None else torch.empty(cols, dtype=out_dtype, device=dy2.device)
+                _cabi.check(L.dlion_colsum_fused(dy2.data_ptr(), rows, cols, partial.data_ptr(),
+                                                 _tickets(dy2.device).data_ptr(), out.data_ptr(), int(acc is not None),
+                                                 _cabi.dtype_code(dy2.dtype), st), "colsum_fused")
+                return None if acc is not None else out
+            out = torch.empty(cols, dtype=out_dtype, device=dy2.device)
             _cabi.check(L.dlion_colsum(dy2.data_ptr(), rows, cols, partial.data_ptr(), _cabi.dtype_code(dy2.dtype), st),
                         "colsum")
             _cabi.check(L.dlion_norm_bwd_finalize(partial.data_ptr(), None, out.data_ptr(), None, parts, cols,
                                                   _cabi.dtype_code(out_dtype), st), "colsum_finalize")
-        return out
-    return dy2.sum(0).to(out_dtype)
+    else:
+        out = dy2.sum(0).to(out_dtype)
+    if accumulate_into is not None:
+        accumulate_into.add_(out)
+        return None
+    return out
+
+
+def bias_grad(dy2: torch.Tensor, bias: torch.Tensor):
+    """Gradient of a bias added to every row of the tensor whose gradient is ``dy2``: accumulated straight into
+    ``bias.grad`` when that buffer exists (returns ``None``), returned otherwise."""
+    if _can_accumulate(bias, dy2) and bias.grad.shape == (dy2.shape[1],):
+        return column_sum(dy2, bias.dtype, accumulate_into=bias.grad)
+    return column_sum(dy2, bias.dtype)
 
 
 def _can_accumulate(param: torch.Tensor, like: torch.Tensor) -> bool:
@@ -83,10 +123,7 @@ class _FusedLinear(torch.autograd.Function):
             else:
                 dw = x2.t() @ dy2 if ctx.in_out else dy2.t() @ x2
         if bias is not None and ctx.needs_input_grad[2]:
-            db = column_sum(dy2, bias.dtype)
-            if _can_accumulate(bias, db):
-                bias.grad.add_(db)
-                db = None
+            db = bias_grad(dy2, bias)                        # one launch: column sums folded and added into bias.grad
         return dx, dw, db, None
 
 

@@ -100,7 +100,7 @@ class _LinearGelu(torch.autograd.Function):
 
     @staticmethod
     def backward(ctx, dact):
-        from .linear import _can_accumulate, column_sum
+        from .linear import _can_accumulate, bias_grad
         x2, pre, weight, bias = ctx.saved_tensors
         d2 = dact.reshape(-1, dact.shape[-1])
         if not d2.is_contiguous():
@@ -118,10 +118,7 @@ class _LinearGelu(torch.autograd.Function):
             else:
                 dw = x2.t() @ dpre
         if ctx.needs_input_grad[2]:
-            db = column_sum(dpre, bias.dtype)
-            if _can_accumulate(bias, db):
-                bias.grad.add_(db)
-                db = None
+            db = bias_grad(dpre, bias)
         return dx, dw, db
 
 

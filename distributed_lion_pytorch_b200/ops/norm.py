@@ -37,7 +37,7 @@ class _FusedNorm(torch.autograd.Function):
                 summed.data_ptr() if summed is not xc else None, _cabi.ptr(mean), rstd.data_ptr(), rows, cols,
                 float(eps), int(rms), float(drop_p), int(seed), _cabi.dtype_code(x.dtype),
                 _cabi.stream_ptr(x.device)), "norm_fwd")
-        ctx.save_for_backward(summed, weight, mean, rstd)
+        ctx.save_for_backward(summed, weight, mean, rstd, bias)
         ctx.rms, ctx.has_res, ctx.has_bias = rms, residual is not None, bias is not None
         ctx.drop_p, ctx.seed = float(drop_p), int(seed)
         ctx.set_materialize_grads(False)      # an unused residual output costs nothing in backward
@@ -45,7 +45,7 @@ class _FusedNorm(torch.autograd.Function):
 
     @staticmethod
     def backward(ctx, dy, dsum):
-        summed, weight, mean, rstd = ctx.saved_tensors
+        summed, weight, mean, rstd, bias = ctx.saved_tensors
         cols = summed.shape[-1]
         rows = summed.numel() // cols
         if dy is None:      # only the residual stream was consumed downstream
@@ -59,21 +59,27 @@ class _FusedNorm(torch.autograd.Function):
         dres = torch.empty_like(summed) if (drop and ctx.has_res) else None
         dwp = torch.empty(parts, cols, dtype=torch.float32, device=dy.device)
         dbp = torch.empty(parts, cols, dtype=torch.float32, device=dy.device) if ctx.has_bias else None
-        dw = torch.empty_like(weight)
-        db = torch.empty_like(weight) if ctx.has_bias else None
+        # weight / bias gradients go straight into existing .grad buffers (the flat-bucket views once Lion has
+        # aliased them): the fold kernel adds in fp32 and rounds once, and autograd has no add kernel left to run
+        from .linear import _can_accumulate
+        acc_w = ctx.needs_input_grad[2] and _can_accumulate(weight, weight)
+        acc_b = ctx.has_bias and ctx.needs_input_grad[3] and _can_accumulate(bias, bias)
+        dw = weight.grad if acc_w else torch.empty_like(weight)
+        db = (bias.grad if acc_b else torch.empty_like(weight)) if ctx.has_bias else None
         with torch.cuda.device(dy.device):
             st = _cabi.stream_ptr(dy.device)
             _cabi.check(L.dlion_norm_bwd(dyc.data_ptr(), _cabi.ptr(dsc), summed.data_ptr(), weight.data_ptr(),
                                          _cabi.ptr(mean), rstd.data_ptr(), dx.data_ptr(), _cabi.ptr(dres),
                                          dwp.data_ptr(), _cabi.ptr(dbp), rows, cols, int(ctx.rms), ctx.drop_p, ctx.seed,
                                          _cabi.dtype_code(dy.dtype), st), "norm_bwd")
-            _cabi.check(L.dlion_norm_bwd_finalize(dwp.data_ptr(), _cabi.ptr(dbp), dw.data_ptr(), _cabi.ptr(db),
-                                                  parts, cols, _cabi.dtype_code(weight.dtype), st), "norm_bwd_finalize")
+            _cabi.check(L.dlion_norm_bwd_finalize_acc(dwp.data_ptr(), _cabi.ptr(dbp), dw.data_ptr(), _cabi.ptr(db),
+                                                      parts, cols, int(acc_w) | (int(acc_b) << 1),
+                                                      _cabi.dtype_code(weight.dtype), st), "norm_bwd_finalize")
         if ctx.has_res:
             g_res = dres if drop else dx
         else:
             g_res = None
-        return dx, g_res, dw, db, None, None, None, None
+        return dx, g_res, (None if acc_w else dw), (None if acc_b else db), None, None, None, None
 
 
 def _draw_seed() -> int:

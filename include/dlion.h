@@ -179,6 +179,10 @@ int dlion_norm_bwd(const void* dy, const void* dsum_in, const void* xsum, const 
                    int dtype, void* stream);
 int dlion_norm_bwd_finalize(const float* dw_partial, const float* db_partial, void* dweight, void* dbias,
                             int parts, int cols, int dtype, void* stream);
+/* same, but bit 0 / bit 1 of acc_mask make dweight / dbias ACCUMULATE (out = T(float(out) + sum)): the
+ * gradient lands in an existing .grad buffer with one rounding and no separate add kernel */
+int dlion_norm_bwd_finalize_acc(const float* dw_partial, const float* db_partial, void* dweight, void* dbias,
+                                int parts, int cols, int acc_mask, int dtype, void* stream);
 
 /* Bias gradient: fp32 partial column sums of x [rows, cols] (cols % 8 == 0) into
  * partial[dlion_colsum_parts(rows, cols)][cols]; fold them with dlion_norm_bwd_finalize
@@ -186,6 +190,13 @@ int dlion_norm_bwd_finalize(const float* dw_partial, const float* db_partial, vo
  * backward, reached from accelerator.backward (async_trainer.py:33). */
 int dlion_colsum_parts(int64_t rows, int cols);
 int dlion_colsum(const void* x, int64_t rows, int cols, float* partial, int dtype, void* stream);
+/* One-launch form: the last CTA to finish on each 256-column tile folds the tile's partial rows and writes
+ * (accumulate = 0) or adds into (accumulate = 1) out[cols] (same dtype as x).  `tickets` is
+ * uint32[dlion_colsum_tiles(cols)], zero-initialised once by the caller; the kernel leaves it zeroed, so one
+ * buffer serves every call ISSUED ON ONE STREAM (calls that overlap on the GPU must not share it). */
+int dlion_colsum_tiles(int cols);
+int dlion_colsum_fused(const void* x, int64_t rows, int cols, float* partial, unsigned int* tickets, void* out,
+                       int accumulate, int dtype, void* stream);
 
 /* MLP activations as single passes over n elements (n % 8 == 0): GPT-2's tanh-form GELU and
  * Llama's silu(gate) * up, forward and backward.

@@ -288,3 +288,83 @@ def test_add_norm_many_rows_per_cta(dtype, cols, rows, rms):
     assert torch.allclose(r.grad.float(), rf.grad, **t)
     scale = float(wf.grad.abs().max())
     assert float((w.grad.float() - wf.grad).abs().max()) < (3e-2 if dtype == torch.bfloat16 else 1e-3) * scale
+
+
+@pytest.mark.parametrize("family", ["gpt2-tiny", "llama-tiny"])
+def test_gradient_checkpointing_replays_fused_dropout_on_gpu(family):
+    """Activation checkpointing recomputes the block: the in-kernel dropout masks (seed drawn from the CPU generator)
+    and cuDNN's attention dropout (CUDA generator) must replay, so gradients match the uncheckpointed run."""
+    from distributed_lion_pytorch_b200.models import build_model
+    torch.manual_seed(0)
+    m = build_model(family, dtype=torch.bfloat16, device="cuda").train()
+    ids = torch.randint(0, 512, (4, 64), device="cuda")
+    runs = []
+    for ckpt in (False, True):
+        m.zero_grad()
+        (m.gradient_checkpointing_enable if ckpt else m.gradient_checkpointing_disable)()
+        torch.manual_seed(7)
+        loss = m(ids, labels=ids).loss
+        loss.backward()
+        runs.append((float(loss), {n: p.grad.float().clone() for n, p in m.named_parameters()}))
+    assert runs[0][0] == runs[1][0]
+    for n, g in runs[0][1].items():
+        assert float((g - runs[1][1][n]).abs().max()) <= 1e-2 * float(g.abs().max()) + 1e-6, n
+
+
+@pytest.mark.parametrize("dtype", [torch.float32, torch.bfloat16])
+def test_one_launch_column_sum_repeated_calls_and_accumulation(dtype):
+    """The fused column sum keeps its tile tickets zeroed between calls: many calls of different shapes in a row,
+    writing and accumulating, all agree with torch."""
+    from distributed_lion_pytorch_b200.ops import _cabi
+    from distributed_lion_pytorch_b200.ops.linear import column_sum
+    torch.manual_seed(0)
+    tol = dict(rtol=2e-2, atol=0.5) if dtype == torch.bfloat16 else dict(rtol=1e-4, atol=1e-3)
+    for rep in range(3):
+        for rows, cols in [(20480, 768), (4096, 3072), (1000, 2304), (7, 8), (20480, 768), (333, 16384)]:
+            x = torch.randn(rows, cols, device="cuda").to(dtype)
+            n0 = _cabi.LAUNCHES
+            out = column_sum(x, dtype)
+            assert _cabi.LAUNCHES == n0 + 1                     # one kernel, no separate fold
+            assert torch.allclose(out.float(), x.float().sum(0), **tol)
+            g0 = torch.randn(cols, device="cuda").to(dtype)
+            g = g0.clone()
+            n0 = _cabi.LAUNCHES
+            assert column_sum(x, dtype, accumulate_into=g) is None
+            assert _cabi.LAUNCHES == n0 + 1
+            assert torch.allclose(g.float(), g0.float() + x.float().sum(0), **tol)
+    # a different output dtype takes the two-launch path and still agrees
+    x = torch.randn(512, 256, device="cuda").to(dtype)
+    other = torch.float32 if dtype == torch.bfloat16 else torch.bfloat16
+    assert torch.allclose(column_sum(x, other).float(), x.float().sum(0), rtol=2e-2, atol=0.5)
+
+
+@pytest.mark.parametrize("dtype", [torch.float32, torch.bfloat16])
+@pytest.mark.parametrize("rms", [False, True])
+def test_add_norm_accumulates_into_existing_grads(dtype, rms):
+    from distributed_lion_pytorch_b200.ops.norm import add_layer_norm, add_rms_norm
+    torch.manual_seed(3)
+    rows, cols = 4000, 768
+    x = torch.randn(rows, cols, device="cuda").to(dtype).requires_grad_()
+    w = (1 + 0.1 * torch.randn(cols, device="cuda")).to(dtype).requires_grad_()
+    b = None if rms else (0.1 * torch.randn(cols, device="cuda")).to(dtype).requires_grad_()
+    w0 = torch.randn(cols, device="cuda").to(dtype)
+    b0 = torch.randn(cols, device="cuda").to(dtype)
+    w.grad = w0.clone()
+    if b is not None:
+        b.grad = b0.clone()
+    wg_ptr = w.grad.data_ptr()
+    y, _ = add_rms_norm(x, None, w, 1e-5) if rms else add_layer_norm(x, None, w, b, 1e-5)
+    dy = torch.randn_like(y)
+    y.backward(dy)
+    assert w.grad.data_ptr() == wg_ptr                           # written in place, not replaced
+    xf, wf = x.detach().float().requires_grad_(), w.detach().float().requires_grad_()
+    if rms:
+        yf = wf * (xf * torch.rsqrt(xf.pow(2).mean(-1, keepdim=True) + 1e-5))
+    else:
+        bf = b.detach().float().requires_grad_()
+        yf = F.layer_norm(xf, (cols,), wf, bf, 1e-5)
+    yf.backward(dy.float())
+    tol = dict(rtol=3e-2, atol=0.5) if dtype == torch.bfloat16 else dict(rtol=1e-3, atol=1e-2)
+    assert torch.allclose(w.grad.float(), w0.float() + wf.grad, **tol)
+    if b is not None:
+        assert torch.allclose(b.grad.float(), b0.float() + bf.grad, **tol)

@@ -237,3 +237,23 @@ def test_checkpoint_loader_reports_problems(tmp_path):
     wide = build_model("llama-tiny", config_overrides="intermediate_size=192")
     with pytest.raises(RuntimeError, match="shape"):
         load_checkpoint_into(wide, d)
+
+
+@pytest.mark.parametrize("family", ["gpt2-tiny", "llama-tiny"])
+def test_gradient_checkpointing_gives_the_same_gradients(family):
+    """reference: ``--gradient_checkpointing`` of the HF TrainingArguments (README.md:52, dpo_llama2.py:46)."""
+    from distributed_lion_pytorch_b200.models import build_model
+    torch.manual_seed(0)
+    m = build_model(family).train()
+    ids = torch.randint(0, 512, (2, 24))
+    grads = []
+    for ckpt in (False, True):
+        m.zero_grad()
+        (m.gradient_checkpointing_enable if ckpt else m.gradient_checkpointing_disable)()
+        torch.manual_seed(123)                      # same dropout draws in both runs (and in the recomputation)
+        loss = m(ids, labels=ids).loss
+        loss.backward()
+        grads.append((float(loss), {n: p.grad.clone() for n, p in m.named_parameters()}))
+    assert grads[0][0] == grads[1][0]
+    for n in grads[0][1]:
+        assert torch.allclose(grads[0][1][n], grads[1][1][n], atol=1e-6), n
