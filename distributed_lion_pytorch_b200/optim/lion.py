@@ -300,6 +300,32 @@ class Lion(Optimizer):
 
     # ------------------------------------------------------------------ diagnostics
     @torch.no_grad()
+    def replica_checksum(self) -> torch.Tensor:
+        """One int64 per bucket: the wrap-around sum of the parameter bits.  Bit-identical replicas — the
+        invariant the whole algorithm rests on (every worker applies the same voted update to the same
+        parameters) — have identical checksums."""
+        self._ensure_buckets()
+        sums = []
+        for b in self._buckets or []:
+            bits = b.flat_p.view({1: torch.int8, 2: torch.int16, 4: torch.int32, 8: torch.int64}[b.flat_p.element_size()])
+            sums.append(bits.sum(dtype=torch.int64))
+        dev = self._buckets[0].device if self._buckets else torch.device("cpu")
+        return torch.stack(sums) if sums else torch.zeros(0, dtype=torch.int64, device=dev)
+
+    @torch.no_grad()
+    def replicas_identical(self) -> bool:
+        """Collective (call on every rank): do all replicas hold bit-identical parameters?  One small reduction
+        per bucket plus two all-reduces of a few integers; cheap enough for every logging step.  The reference
+        has no such check: a diverged replica there trains on silently."""
+        cs = self.replica_checksum()
+        if self.world_size == 1 or cs.numel() == 0:
+            return True
+        lo, hi = cs.clone(), cs.clone()
+        dist.all_reduce(lo, op=dist.ReduceOp.MIN, group=self.process_group)
+        dist.all_reduce(hi, op=dist.ReduceOp.MAX, group=self.process_group)
+        return bool(torch.equal(lo, hi))
+
+    @torch.no_grad()
     def vote_statistics(self, chunk_elems: int = 1 << 24) -> Dict[str, float]:
         """Collective, off the hot path: what would the ballot of the CURRENT gradients look like?
         Returns the fraction of coordinates that tie, that are unanimous, and the mean agreement

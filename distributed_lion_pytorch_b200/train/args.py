@@ -69,6 +69,8 @@ class TrainingArguments:
     lion_bucket_mb: Optional[int] = field(default=None, metadata={"help": "MiB of bf16 parameters per fused launch"})
     profile_steps: bool = field(default=False, metadata={"help": "log device-timed forward/backward/optimizer ms"})
     per_rank_optimizer_state: bool = field(default=False, metadata={"help": "also save optimizer_rank<r>.pt"})
+    check_replicas: str = field(default="raise", metadata={
+        "help": "at every logging step compare parameter checksums across ranks: raise | resync | off"})
     synthetic_data: bool = field(default=False, metadata={"help": "random tokens of the right shape"})
     synthetic_samples: int = 4096
     device: Optional[str] = None

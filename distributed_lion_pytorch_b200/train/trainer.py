@@ -232,6 +232,24 @@ class Trainer:
         else:
             self.optimizer.zero_grad(set_to_none=True)
 
+    def _check_replicas(self, logs: Dict[str, float]) -> None:
+        """Distributed Lion only works while every replica holds the same parameters; verify it whenever we log
+        (collective; one checksum per bucket).  ``--check_replicas resync`` repairs a divergence by re-broadcasting
+        rank 0's parameters instead of stopping."""
+        mode = getattr(self.args, "check_replicas", "off")
+        if mode == "off" or rt.world_size() == 1 or self.sync_gradients:
+            return
+        same = self.optimizer.replicas_identical()
+        logs["replicas_identical"] = int(same)
+        if same:
+            return
+        if mode == "resync":
+            logger.warning("replicas diverged at step %d: re-broadcasting rank 0's parameters", self.state.global_step)
+            self.optimizer.resync_replicas(0)
+            return
+        raise RuntimeError(f"parameter replicas diverged by step {self.state.global_step} (checksums differ across "
+                           "ranks); rerun with --check_replicas resync to repair in place, or off to ignore")
+
     def train_step(self, micro_batches) -> torch.Tensor:
         """One optimizer step from ``gradient_accumulation_steps`` micro-batches (host or device
         tensors): forward/backward each, then gradient sync (baseline trainers only), local
@@ -334,6 +352,7 @@ class Trainer:
                     logs.update(self.timer.summary())          # device-timed phase means (only with --profile_steps)
                     if isinstance(self.optimizer, Lion):
                         self.optimizer.check_health()          # a stalled sign exchange surfaces here, not as a hang
+                        self._check_replicas(logs)
                     self.log(logs)
                 if a.evaluation_strategy == "steps" and a.eval_steps and step % a.eval_steps == 0 \
                         and self.eval_dataset is not None:

@@ -204,3 +204,29 @@ def _worker_resync(rank, world):
 def test_resync_replicas_rebroadcasts_parameters():
     outs = run_distributed(_worker_resync, 3)
     assert torch.equal(outs[0], outs[1]) and torch.equal(outs[2], outs[1])
+
+
+def _worker_replica_check(rank, world):
+    from distributed_lion import Lion
+    torch.manual_seed(0)                                      # identical replicas, different gradients
+    ps = [torch.nn.Parameter(torch.randn(300)), torch.nn.Parameter(torch.randn(40, 7).bfloat16())]
+    opt = Lion(ps, lr=1e-2)
+    g = torch.Generator().manual_seed(100 + rank)
+    for _ in range(3):
+        for p in ps:
+            p.grad = torch.randn(p.shape, generator=g).to(p.dtype)
+        opt.step()
+    same_before = opt.replicas_identical()
+    cs = opt.replica_checksum().tolist()
+    if rank == 1:                                             # one worker silently corrupts one element
+        with torch.no_grad():
+            ps[1].view(-1)[5] += 0.5
+    same_after = opt.replicas_identical()
+    opt.resync_replicas(0)
+    return same_before, same_after, opt.replicas_identical(), cs
+
+
+def test_replica_checksums_detect_a_diverged_worker():
+    outs = run_distributed(_worker_replica_check, 3)
+    assert all(o[0] is True and o[1] is False and o[2] is True for o in outs)
+    assert outs[0][3] == outs[1][3] == outs[2][3] and len(outs[0][3]) == 2      # one checksum per bucket

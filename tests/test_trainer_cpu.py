@@ -179,6 +179,9 @@ def test_run_clm_torchrun_gloo_world2(tmp_path):
         assert (ck / f).exists(), f
     res = json.loads((tmp_path / "o" / "all_results.json").read_text())
     assert res["lion_backend"] == "nccl_1bit" and "perplexity" in res
+    hist = json.loads((ck / "trainer_state.json").read_text())["log_history"]
+    checked = [h["replicas_identical"] for h in hist if "replicas_identical" in h]
+    assert checked and all(v == 1 for v in checked)              # the per-log-step replica checksum ran and agreed
 
 
 def test_reference_readme_command_lines_parse():
