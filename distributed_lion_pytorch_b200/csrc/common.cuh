@@ -237,6 +237,62 @@ __device__ __forceinline__ void apply8(float (&p)[8], const float (&u)[8], float
 #pragma unroll
   for (int i = 0; i < 8; ++i) p[i] = fmaf(-lr, u[i], p[i]);
 }
+// ------------------------------------------------------------------ stochastic rounding of the parameter write
+// Opt-in (Lion(stochastic_rounding=True)); bf16 only.  At lr ~ 1e-4 a Lion update is below half a bf16 ulp
+// of a typical weight, so round-to-nearest leaves most weights unchanged step after step; rounding up with
+// probability (discarded bits / 2^16) makes the expected stored value equal the fp32 result.  The random
+// bits are a counter hash of (key, element index): every rank draws the same bits for the same element, so
+// replicas stay bit-identical, and the split and fused paths agree bit for bit.
+__device__ __forceinline__ uint32_t mix32(uint32_t x) {   // "lowbias32" integer hash: full avalanche in 5 ops
+  x ^= x >> 16; x *= 0x7feb352du; x ^= x >> 15; x *= 0x846ca68bu; x ^= x >> 16;
+  return x;
+}
+// four 32-bit hashes = eight 16-bit uniforms for 8-element vector number `vec` of the bucket
+__device__ __forceinline__ void hash_bits8(uint64_t key, int64_t vec, uint32_t (&r)[4]) {
+  const uint32_t lo = (uint32_t)key, hi = (uint32_t)(key >> 32);
+  const uint32_t base = mix32((uint32_t)vec * 0x9E3779B9u + lo) ^ mix32((uint32_t)(vec >> 32) + hi);
+#pragma unroll
+  for (int i = 0; i < 4; ++i) r[i] = mix32(base + (uint32_t)i * 0x85EBCA6Bu + hi);
+}
+template <typename T>
+struct SrCapable { static constexpr bool value = false; };
+template <>
+struct SrCapable<__nv_bfloat16> { static constexpr bool value = true; };
+// p' = p*decay - lr*u in fp32, no intermediate rounding (the stochastic store is the only rounding)
+__device__ __forceinline__ void apply8_fp32(float (&p)[8], const float (&u)[8], float lr, float decay) {
+#pragma unroll
+  for (int i = 0; i < 8; ++i) p[i] = fmaf(-lr, u[i], p[i] * decay);
+}
+__device__ __forceinline__ uint32_t sr_add(uint32_t bits, uint32_t r16) {
+  return (bits & 0x7f800000u) == 0x7f800000u ? bits : bits + r16;       // leave inf / nan alone
+}
+__device__ __forceinline__ void store8_sr(__nv_bfloat16* __restrict__ ptr, const float (&v)[8], uint64_t key,
+                                          int64_t vec) {
+  uint32_t r[4], w[4];
+  hash_bits8(key, vec, r);
+#pragma unroll
+  for (int i = 0; i < 4; ++i) {
+    const uint32_t a = sr_add(__float_as_uint(v[2 * i]), r[i] & 0xffffu);
+    const uint32_t b = sr_add(__float_as_uint(v[2 * i + 1]), r[i] >> 16);
+    w[i] = (a >> 16) | (b & 0xffff0000u);
+  }
+  *reinterpret_cast<uint4*>(ptr) = make_uint4(w[0], w[1], w[2], w[3]);
+}
+// Parameter update + store in either mode; SR falls back to the reference rounding for types without it.
+template <typename T>
+__device__ __forceinline__ void apply_store8(T* __restrict__ ptr, float (&p)[8], const float (&u)[8], float lr,
+                                             float decay, uint64_t sr_key, int64_t vec) {
+  if constexpr (SrCapable<T>::value) {
+    if (sr_key != 0) {
+      apply8_fp32(p, u, lr, decay);
+      store8_sr(ptr, p, sr_key, vec);
+      return;
+    }
+  }
+  apply8<T>(p, u, lr, decay);
+  store8<T>(ptr, p);
+}
+
 // scalar forms for ragged tails
 template <typename T>
 __device__ __forceinline__ float lion_blend(float m, float g, float beta1, float omb1) {

@@ -21,7 +21,8 @@ static inline int grid_for(int64_t nvec) {
 template <typename T>
 __global__ void __launch_bounds__(kThreads) lion_local_kernel(T* __restrict__ p, const T* __restrict__ g,
                                                               T* __restrict__ m, int64_t n, float lr, float decay,
-                                                              float beta1, float omb1, float beta2, float omb2) {
+                                                              float beta1, float omb1, float beta2, float omb2,
+                                                              uint64_t sr_key, int64_t vec_base) {
   const int64_t nvec = n >> 3;
   const int64_t stride = (int64_t)gridDim.x * blockDim.x;
   for (int64_t v = (int64_t)blockIdx.x * blockDim.x + threadIdx.x; v < nvec; v += stride) {
@@ -34,12 +35,11 @@ __global__ void __launch_bounds__(kThreads) lion_local_kernel(T* __restrict__ p,
     const float thr = tie_to_zero<T>();
 #pragma unroll
     for (int i = 0; i < 8; ++i) u[i] = c[i] > thr ? 1.f : (c[i] < -thr ? -1.f : 0.f);   // torch.sign: sign(0) = 0
-    apply8<T>(pf, u, lr, decay);
+    apply_store8<T>(p + v * 8, pf, u, lr, decay, sr_key, vec_base + v);
     momentum8<T>(mf, gf, beta2, omb2);
-    store8<T>(p + v * 8, pf);
     store8<T>(m + v * 8, mf);
   }
-  // ragged tail (< 8 elements): one thread
+  // ragged tail (< 8 elements): one thread (always round-to-nearest)
   if (blockIdx.x == 0 && threadIdx.x == 0) {
     for (int64_t e = nvec << 3; e < n; ++e) {
       const float gf = DT<T>::to_f(g[e]), mf = DT<T>::to_f(m[e]), pf = DT<T>::to_f(p[e]);
@@ -95,7 +95,7 @@ __global__ void __launch_bounds__(kThreads) vote_update_kernel(T* __restrict__ p
                                                                T* __restrict__ m, const uint8_t* __restrict__ gathered,
                                                                int64_t row_bytes, int world, uint32_t live_mask,
                                                                int L, int64_t n, float lr, float decay, float beta2,
-                                                               float omb2, int vote) {
+                                                               float omb2, int vote, uint64_t sr_key) {
   const int64_t nvec = (n + 7) >> 3;
   const int64_t stride = (int64_t)gridDim.x * blockDim.x;
   for (int64_t v = (int64_t)blockIdx.x * blockDim.x + threadIdx.x; v < nvec; v += stride) {
@@ -154,12 +154,13 @@ __global__ void __launch_bounds__(kThreads) vote_update_kernel(T* __restrict__ p
 #pragma unroll
       for (int i = 0; i < 8; ++i) uf[i] = ((tie >> i) & 1u) ? 0.f : (((maj >> i) & 1u) ? 1.f : -1.f);
     }
-    apply8<T>(pf, uf, lr, decay);
-    momentum8<T>(mf, gf, beta2, omb2);
     if (full) {
-      store8<T>(p + e0, pf);
+      apply_store8<T>(p + e0, pf, uf, lr, decay, sr_key, v);
+      momentum8<T>(mf, gf, beta2, omb2);
       store8<T>(m + e0, mf);
     } else {
+      apply8<T>(pf, uf, lr, decay);
+      momentum8<T>(mf, gf, beta2, omb2);
       for (int i = 0; i < 8 && e0 + i < n; ++i) {
         p[e0 + i] = DT<T>::from_f(pf[i]);
         m[e0 + i] = DT<T>::from_f(mf[i]);
@@ -172,16 +173,24 @@ __global__ void __launch_bounds__(kThreads) vote_update_kernel(T* __restrict__ p
 
 using namespace dlion;
 
-extern "C" int dlion_lion_local(void* p, const void* g, void* m, int64_t n, int dtype, float lr, float decay,
-                                float beta1, float omb1, float beta2, float omb2, void* stream) {
+extern "C" int dlion_lion_local_sr(void* p, const void* g, void* m, int64_t n, int dtype, float lr, float decay,
+                                   float beta1, float omb1, float beta2, float omb2, uint64_t sr_key,
+                                   int64_t elem_base, void* stream) {
   DLION_CHECK_ARG(n >= 0, "dlion_lion_local: negative n");
+  DLION_CHECK_ARG(elem_base >= 0 && (elem_base & 7) == 0, "dlion_lion_local: elem_base must be a multiple of 8");
   if (n == 0) return 0;
   DLION_CHECK_ARG(aligned16(p) && aligned16(g) && aligned16(m), "dlion_lion_local: pointers must be 16-byte aligned");
   cudaStream_t s = (cudaStream_t)stream;
   const int grid = grid_for(n >> 3);
   DISPATCH_DTYPE(dtype, lion_local_kernel<T><<<grid, kThreads, 0, s>>>((T*)p, (const T*)g, (T*)m, n, lr, decay,
-                                                                         beta1, omb1, beta2, omb2));
+                                                                         beta1, omb1, beta2, omb2, sr_key,
+                                                                         elem_base >> 3));
   return DLION_LAUNCH_CHECK("dlion_lion_local");
+}
+
+extern "C" int dlion_lion_local(void* p, const void* g, void* m, int64_t n, int dtype, float lr, float decay,
+                                float beta1, float omb1, float beta2, float omb2, void* stream) {
+  return dlion_lion_local_sr(p, g, m, n, dtype, lr, decay, beta1, omb1, beta2, omb2, 0, 0, stream);
 }
 
 extern "C" int dlion_sign_pack(const void* m, const void* g, uint32_t* words, int64_t n, int dtype, float beta1,
@@ -196,9 +205,9 @@ extern "C" int dlion_sign_pack(const void* m, const void* g, uint32_t* words, in
   return DLION_LAUNCH_CHECK("dlion_sign_pack");
 }
 
-extern "C" int dlion_vote_update(void* p, const void* g, void* m, const uint32_t* gathered, int64_t row_words,
-                                 int world, uint32_t live_mask, int64_t n, int dtype, float lr, float decay,
-                                 float beta2, float omb2, int vote, void* stream) {
+extern "C" int dlion_vote_update_sr(void* p, const void* g, void* m, const uint32_t* gathered, int64_t row_words,
+                                    int world, uint32_t live_mask, int64_t n, int dtype, float lr, float decay,
+                                    float beta2, float omb2, int vote, uint64_t sr_key, void* stream) {
   DLION_CHECK_ARG(n >= 0, "dlion_vote_update: negative n");
   DLION_CHECK_ARG(world >= 1 && world <= DLION_MAX_RANKS, "dlion_vote_update: world %d outside [1, %d]", world,
                   DLION_MAX_RANKS);
@@ -215,6 +224,13 @@ extern "C" int dlion_vote_update(void* p, const void* g, void* m, const uint32_t
   const int grid = grid_for((n + 7) >> 3);
   DISPATCH_DTYPE(dtype, vote_update_kernel<T><<<grid, kThreads, 0, s>>>(
                             (T*)p, (const T*)g, (T*)m, (const uint8_t*)gathered, row_words * 4, world, live_mask, L, n,
-                            lr, decay, beta2, omb2, vote));
+                            lr, decay, beta2, omb2, vote, sr_key));
   return DLION_LAUNCH_CHECK("dlion_vote_update");
+}
+
+extern "C" int dlion_vote_update(void* p, const void* g, void* m, const uint32_t* gathered, int64_t row_words,
+                                 int world, uint32_t live_mask, int64_t n, int dtype, float lr, float decay,
+                                 float beta2, float omb2, int vote, void* stream) {
+  return dlion_vote_update_sr(p, g, m, gathered, row_words, world, live_mask, n, dtype, lr, decay, beta2, omb2, vote, 0,
+                              stream);
 }

@@ -85,6 +85,7 @@ struct FusedParams {
   int64_t emu_stride;
   int32_t* status;
   int64_t spin_limit;
+  uint64_t sr_key;
 };
 
 // ------------------------------------------------------------------ PTX helpers
@@ -480,8 +481,7 @@ __global__ void __launch_bounds__(kFusedThreads, 1) lion_fused_kernel(const __gr
 #pragma unroll
           for (int e = 0; e < 8; ++e) uf[e] = ((z >> e) & 1u) ? 0.f : (((a >> e) & 1u) ? 1.f : -1.f);
         }
-        apply8<T>(pf, uf, P.lr, P.decay);
-        store8<T>(p + off + unit * 8, pf);
+        apply_store8<T>(p + off + unit * 8, pf, uf, P.lr, P.decay, P.sr_key, (P.elem_base + off + unit * 8) >> 3);
       }
       __syncwarp();
       if (lane == 0) mbar_arrive(smem_u32(emptyC + slot));
@@ -552,7 +552,7 @@ static int launch_fused(const dlion_fused_args* a, cudaStream_t s) {
                     "dlion_fused_step: arena/flags pointer of rank %d is null or unaligned", r);
   P.mc_arena = a->emulate_ranks > 0 ? nullptr : a->mc_arena;
   P.arena_words = a->arena_words; P.grid = a->grid; P.emulate_ranks = a->emulate_ranks; P.emu_stride = a->emu_stride;
-  P.status = a->status; P.spin_limit = a->spin_limit;
+  P.status = a->status; P.spin_limit = a->spin_limit; P.sr_key = a->sr_key;
   void* kargs[] = {(void*)&P};
   return check_cuda(cudaLaunchCooperativeKernel((void*)lion_fused_kernel<T>, dim3(a->grid * vr), dim3(kFusedThreads),
                                                 kargs, (size_t)C::SMEM_TOTAL, s),

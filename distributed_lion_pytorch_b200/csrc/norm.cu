@@ -34,10 +34,7 @@ __device__ __forceinline__ float block_allreduce_sum(float v, float* smem) {
 // Dropout fused into the residual add: keep-mask bits for the 8 elements of vector `vec` of the
 // whole [rows, cols] tensor, regenerated (not stored) in the backward from (seed, vec): keep iff a
 // 16-bit uniform >= p * 65536.
-__device__ __forceinline__ uint32_t mix32(uint32_t x) {   // "lowbias32" integer hash: full avalanche in 5 ops
-  x ^= x >> 16; x *= 0x7feb352du; x ^= x >> 15; x *= 0x846ca68bu; x ^= x >> 16;
-  return x;
-}
+// mix32 (the counter hash) lives in common.cuh
 __device__ __forceinline__ uint32_t keep_mask8(uint64_t seed, int64_t vec, uint32_t thr16) {
   // four counter-based 32-bit hashes -> eight 16-bit uniforms (Philox4x32-10 here made the norm
   // kernels issue-bound: ~70 instructions per 8 elements against ~25 for this)

@@ -34,7 +34,7 @@ class FusedArgs(C.Structure):
         ("epoch", C.c_uint64),
         ("arena", C.c_void_p * MAX_RANKS), ("flags", C.c_void_p * MAX_RANKS), ("mc_arena", C.c_void_p),
         ("arena_words", C.c_int64), ("grid", C.c_int), ("emulate_ranks", C.c_int),
-        ("emu_stride", C.c_int64), ("status", C.c_void_p), ("spin_limit", C.c_int64),
+        ("emu_stride", C.c_int64), ("status", C.c_void_p), ("spin_limit", C.c_int64), ("sr_key", C.c_uint64),
     ]
 
 
@@ -73,8 +73,10 @@ def _declare(L: C.CDLL) -> None:
     sigs = {
         "dlion_device_sm_count": [C.POINTER(i32)],
         "dlion_lion_local": [vp, vp, vp, i64, i32, f32, f32, f32, f32, f32, f32, vp],
+        "dlion_lion_local_sr": [vp, vp, vp, i64, i32, f32, f32, f32, f32, f32, f32, u64, i64, vp],
         "dlion_sign_pack": [vp, vp, vp, i64, i32, f32, f32, f32, u64, u32, u32, vp],
         "dlion_vote_update": [vp, vp, vp, vp, i64, i32, u32, i64, i32, f32, f32, f32, f32, i32, vp],
+        "dlion_vote_update_sr": [vp, vp, vp, vp, i64, i32, u32, i64, i32, f32, f32, f32, f32, i32, u64, vp],
         "dlion_fused_step": [C.POINTER(FusedArgs), vp],
         "dlion_fused_tile": [i32],
         "dlion_fused_max_grid": [i32, C.POINTER(i32)],

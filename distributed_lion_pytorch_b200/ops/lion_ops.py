@@ -20,13 +20,16 @@ def _check_triplet(p, g, m):
 
 
 def local_step(p: torch.Tensor, g: torch.Tensor, m: torch.Tensor, lr: float, wd: float, beta1: float,
-               beta2: float) -> None:
+               beta2: float, sr_key: int = 0, elem_base: int = 0) -> None:
+    """``sr_key != 0``: stochastic rounding of the bf16 parameter write (``optim.semantics.sr_key``);
+    ``elem_base`` = index of ``p[0]`` within its bucket (keeps the random stream layout-invariant)."""
     _check_triplet(p, g, m)
     lr_, decay, b1, omb1, b2, omb2 = _scalars(lr, wd, beta1, beta2)
     with torch.cuda.device(p.device):
-        _cabi.check(_cabi.lib().dlion_lion_local(p.data_ptr(), g.data_ptr(), m.data_ptr(), p.numel(),
-                                                 _cabi.dtype_code(p.dtype), lr_, decay, b1, omb1, b2, omb2,
-                                                 _cabi.stream_ptr(p.device)), "lion_local")
+        _cabi.check(_cabi.lib().dlion_lion_local_sr(p.data_ptr(), g.data_ptr(), m.data_ptr(), p.numel(),
+                                                    _cabi.dtype_code(p.dtype), lr_, decay, b1, omb1, b2, omb2,
+                                                    int(sr_key) & (2 ** 64 - 1), int(elem_base),
+                                                    _cabi.stream_ptr(p.device)), "lion_local")
 
 
 def stoch_radius(beta1: float, max_grad_norm: Optional[float]) -> float:
@@ -53,7 +56,7 @@ def sign_pack(m: torch.Tensor, g: torch.Tensor, beta1: float, out: torch.Tensor,
 
 def vote_update(p: torch.Tensor, g: torch.Tensor, m: torch.Tensor, gathered: torch.Tensor, world: int,
                 live_mask: Optional[int], lr: float, wd: float, beta2: float, vote: str = "majority",
-                tie: str = "neg") -> None:
+                tie: str = "neg", sr_key: int = 0) -> None:
     """gathered: [world, row_bytes] uint8 (row_bytes % 4 == 0), row r = rank r's packed signs."""
     _check_triplet(p, g, m)
     assert gathered.is_contiguous() and gathered.dim() == 2 and gathered.shape[0] == world
@@ -62,10 +65,11 @@ def vote_update(p: torch.Tensor, g: torch.Tensor, m: torch.Tensor, gathered: tor
     mask = (1 << world) - 1 if live_mask is None else int(live_mask) & ((1 << world) - 1)
     lr_, decay, _, _, b2, omb2 = _scalars(lr, wd, 0.0, beta2)
     with torch.cuda.device(p.device):
-        _cabi.check(_cabi.lib().dlion_vote_update(p.data_ptr(), g.data_ptr(), m.data_ptr(), gathered.data_ptr(),
-                                                  row_bytes // 4, world, mask, p.numel(), _cabi.dtype_code(p.dtype),
-                                                  lr_, decay, b2, omb2, _cabi.VOTE_CODES[(vote, tie)],
-                                                  _cabi.stream_ptr(p.device)), "vote_update")
+        _cabi.check(_cabi.lib().dlion_vote_update_sr(p.data_ptr(), g.data_ptr(), m.data_ptr(), gathered.data_ptr(),
+                                                     row_bytes // 4, world, mask, p.numel(), _cabi.dtype_code(p.dtype),
+                                                     lr_, decay, b2, omb2, _cabi.VOTE_CODES[(vote, tie)],
+                                                     int(sr_key) & (2 ** 64 - 1), _cabi.stream_ptr(p.device)),
+                    "vote_update")
 
 
 # --------------------------------------------------------------------------- N1 fused step
@@ -86,7 +90,7 @@ def fused_step(p: torch.Tensor, g: torch.Tensor, m: torch.Tensor, *, world: int,
                vote: str = "majority", tie: str = "neg", live_mask: Optional[int] = None,
                wait_mask: Optional[int] = None, max_grad_norm: Optional[float] = None, seed: int = 0, step: int = 0,
                elem_base: int = 0, emulate_ranks: int = 0, emu_stride: int = 0, status: Optional[torch.Tensor] = None,
-               spin_limit: int = 0, n: Optional[int] = None, mc_arena_ptr: int = 0) -> None:
+               spin_limit: int = 0, n: Optional[int] = None, mc_arena_ptr: int = 0, sr_key: int = 0) -> None:
     """Launch the fused sign-pack-exchange-vote-update kernel on ``n`` elements of p/g/m.
 
     ``arena_ptrs[r]`` / ``flag_ptrs[r]`` are device addresses of rank r's receive arena and
@@ -113,6 +117,7 @@ def fused_step(p: torch.Tensor, g: torch.Tensor, m: torch.Tensor, *, world: int,
     a.emulate_ranks, a.emu_stride = int(emulate_ranks), int(emu_stride)
     a.status = status.data_ptr() if status is not None else None
     a.spin_limit = int(spin_limit)
+    a.sr_key = int(sr_key) & (2 ** 64 - 1)
     import ctypes as C
     with torch.cuda.device(p.device):
         _cabi.check(_cabi.lib().dlion_fused_step(C.byref(a), _cabi.stream_ptr(p.device)), "fused_step")

@@ -51,17 +51,18 @@ class LocalBackend(_Backend):
         if missing:
             # reference semantics: a parameter without a gradient is left untouched this step
             skip = set(missing)
-            spans = [(pv, gv, mv) for i, (pv, gv, mv) in enumerate(zip(b.p_views, b.g_views, b.m_views))
-                     if i not in skip]
+            spans = [(pv, gv, mv, off) for i, (pv, gv, mv, off) in
+                     enumerate(zip(b.p_views, b.g_views, b.m_views, b.offsets)) if i not in skip]
         else:
-            spans = [(b.flat_p, b.flat_g, b.flat_m)]
+            spans = [(b.flat_p, b.flat_g, b.flat_m, 0)]
+        key = self.opt.sr_key()
         if self._use_kernels(b):
             from ..ops import lion_ops
-            for p, g, m in spans:
-                lion_ops.local_step(p, g, m, lr, wd, beta1, beta2)
+            for p, g, m, off in spans:
+                lion_ops.local_step(p, g, m, lr, wd, beta1, beta2, sr_key=key, elem_base=off)
         else:
-            for p, g, m in spans:
-                sem.local_lion_step_(p, g, m, lr, wd, beta1, beta2)
+            for p, g, m, off in spans:
+                sem.local_lion_step_(p.view(-1), g.view(-1), m.view(-1), lr, wd, beta1, beta2, sr_key=key, elem_base=off)
 
 
 class AllGatherBackend(_Backend):
@@ -105,11 +106,11 @@ class AllGatherBackend(_Backend):
         L = opt.live_count()
         if kern:
             lion_ops.vote_update(b.flat_p, b.flat_g, b.flat_m, gathered, W, opt.live_mask, lr, wd, beta2,
-                                 opt.vote, opt.tie)
+                                 opt.vote, opt.tie, sr_key=opt.sr_key())
         else:
             from ..ops import cpu_ops
             cnt = cpu_ops.count_votes(gathered, b.numel, opt.live_mask)
-            sem.apply_vote_(b.flat_p, b.flat_g, b.flat_m, cnt, L, lr, wd, beta2, opt.vote, opt.tie)
+            sem.apply_vote_(b.flat_p, b.flat_g, b.flat_m, cnt, L, lr, wd, beta2, opt.vote, opt.tie, sr_key=opt.sr_key())
 
 
 class FusedBackend(_Backend):
@@ -156,7 +157,7 @@ class FusedBackend(_Backend):
             opt._backend = fallback
             return fallback.step(b, lr, wd, beta1, beta2, missing)
         self._ctx.step(b, lr, wd, beta1, beta2, vote=opt.vote, tie=opt.tie, live_mask=opt.live_mask,
-                       max_grad_norm=opt.max_grad_norm, seed=opt.seed, step_index=opt._steps_done)
+                       max_grad_norm=opt.max_grad_norm, seed=opt.seed, step_index=opt._steps_done, sr_key=opt.sr_key())
 
 
 def pick_auto(opt) -> _Backend:

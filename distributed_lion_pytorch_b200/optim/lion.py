@@ -17,7 +17,8 @@ What is different from the reference (on purpose):
 * a parameter with ``grad is None`` on *this* rank but active elsewhere contributes a zero
   gradient instead of desynchronising the collective sequence (D6);
 * new keyword-only options: ``vote`` (majority | average), ``tie`` (neg | zero), ``comm``
-  (auto | fused | nccl_1bit | local), ``live_mask`` / :meth:`set_live_mask`, ``seed``.
+  (auto | fused | nccl_1bit | local), ``live_mask`` / :meth:`set_live_mask`, ``seed``,
+  ``stochastic_rounding`` (bf16 parameter writes; off by default = the reference's arithmetic).
 
 Communication back-ends (``comm``):
 
@@ -52,7 +53,7 @@ class Lion(Optimizer):
                  weight_decay: float = 0.0, max_grad_norm: Optional[float] = None, *,
                  vote: str = "majority", tie: str = "neg", comm: str = "auto",
                  process_group=None, live_mask: Optional[int] = None, seed: int = 0,
-                 flat_grads: bool = True, use_kernels: Optional[bool] = None):
+                 flat_grads: bool = True, use_kernels: Optional[bool] = None, stochastic_rounding: bool = False):
         if not lr > 0.0:
             raise ValueError(f"lr must be positive, got {lr}")
         if not all(0.0 <= b <= 1.0 for b in betas):
@@ -73,6 +74,10 @@ class Lion(Optimizer):
         self.seed = int(seed)
         self.flat_grads = flat_grads
         self.use_kernels = use_kernels
+        # opt-in: bf16 parameters are written with stochastic instead of nearest rounding (not in the reference;
+        # SURVEY §7.3 — at lr ~ 1e-4 a sign update is below half a bf16 ulp of a typical weight).  The noise is a
+        # counter hash of (seed, step, element), identical on every rank, so replicas stay bit-identical.
+        self.stochastic_rounding = bool(stochastic_rounding)
         self._buckets: Optional[List[Bucket]] = None
         self._bucket_sig = None
         self._frozen_actives: List[list] = []
@@ -377,3 +382,7 @@ class Lion(Optimizer):
 
     def live_count(self) -> int:
         return len(sem.live_ranks(self.world_size, self.live_mask))
+
+    def sr_key(self) -> int:
+        """Key of this step's rounding noise (0 = round to nearest)."""
+        return sem.sr_key(self.seed, self._steps_done) if self.stochastic_rounding else 0

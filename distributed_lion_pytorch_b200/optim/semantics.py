@@ -119,9 +119,59 @@ def momentum_update_(m: torch.Tensor, g: torch.Tensor, beta2: float) -> None:
     m.mul_(beta2).add_(g, alpha=1 - beta2)
 
 
+# ----------------------------------------------------------------------------- stochastic rounding (opt-in)
+_M32 = 0xFFFFFFFF
+
+
+def sr_key(seed: int, step: int) -> int:
+    """Non-zero 64-bit key of one optimizer step's rounding noise; identical on every rank."""
+    return ((int(seed) * 0x9E3779B97F4A7C15 + (int(step) + 1) * 0xD1B54A32D192ED03) & (2 ** 64 - 1)) | 1
+
+
+def _mix32(x: torch.Tensor) -> torch.Tensor:
+    """The kernels' counter hash ("lowbias32") on int64 tensors holding 32-bit values."""
+    x = x ^ (x >> 16)
+    x = (x * 0x7FEB352D) & _M32
+    x = x ^ (x >> 15)
+    x = (x * 0x846CA68B) & _M32
+    return x ^ (x >> 16)
+
+
+def stochastic_round_bf16(x: torch.Tensor, key: int, elem_base: int = 0) -> torch.Tensor:
+    """fp32 ``x`` (flat) → bf16, rounding up in magnitude with probability (discarded bits) / 2^16; the random bits
+    are the kernels' hash of ``(key, elem_base + index)`` — same bits on CPU, in the split kernels and in the
+    fused kernel (``csrc/common.cuh: store8_sr``)."""
+    assert x.dtype == torch.float32 and x.dim() == 1
+    idx = torch.arange(x.numel(), dtype=torch.int64, device=x.device) + int(elem_base)
+    vec, lane = idx >> 3, idx & 7
+    lo, hi = key & _M32, (key >> 32) & _M32
+    base = _mix32(((vec & _M32) * 0x9E3779B9 + lo) & _M32) ^ _mix32(((vec >> 32) + hi) & _M32)
+    word = _mix32((base + (lane >> 1) * 0x85EBCA6B + hi) & _M32)
+    r16 = torch.where((lane & 1) == 0, word & 0xFFFF, word >> 16)
+    bits = x.view(torch.int32).to(torch.int64) & _M32
+    finite = (bits & 0x7F800000) != 0x7F800000
+    bits = torch.where(finite, (bits + r16) & _M32, bits)
+    out16 = (bits >> 16).to(torch.int32)
+    out16 = torch.where(out16 >= 0x8000, out16 - 0x10000, out16).to(torch.int16)      # reinterpret as signed
+    return out16.view(torch.bfloat16)
+
+
+def _apply_sr_(p: torch.Tensor, u: torch.Tensor, lr: float, wd: float, key: int, elem_base: int) -> None:
+    """p ← SR(p·(1−lr·wd) − lr·u), all in fp32 with one stochastic rounding (csrc/common.cuh: apply8_fp32)."""
+    decay = torch.tensor(1 - lr * wd, dtype=torch.float32, device=p.device)
+    neg_lr = torch.tensor(-lr, dtype=torch.float32, device=p.device)
+    x = p.float().reshape(-1) * decay
+    x = torch.addcmul(x, u.float().reshape(-1), neg_lr)
+    p.copy_(stochastic_round_bf16(x, key, elem_base).view_as(p))
+
+
 def local_lion_step_(p: torch.Tensor, g: torch.Tensor, m: torch.Tensor, lr: float, wd: float,
-                     beta1: float, beta2: float) -> None:
+                     beta1: float, beta2: float, sr_key: int = 0, elem_base: int = 0) -> None:
     """Single-worker Lion (reference: distributed_lion.py:47-59); ``sign(0) == 0``."""
+    if sr_key and p.dtype == torch.bfloat16:
+        _apply_sr_(p, lion_blend(m, g, beta1).sign_(), lr, wd, sr_key, elem_base)
+        momentum_update_(m, g, beta2)
+        return
     p.mul_(1 - lr * wd)
     u = lion_blend(m, g, beta1).sign_()
     p.add_(u, alpha=-lr)
@@ -129,8 +179,12 @@ def local_lion_step_(p: torch.Tensor, g: torch.Tensor, m: torch.Tensor, lr: floa
 
 
 def apply_vote_(p: torch.Tensor, g: torch.Tensor, m: torch.Tensor, cnt: torch.Tensor, L: int, lr: float,
-                wd: float, beta2: float, vote: str = "majority", tie: str = "neg") -> None:
+                wd: float, beta2: float, vote: str = "majority", tie: str = "neg", sr_key: int = 0) -> None:
     """Decay, voted update, momentum write-back (reference: distributed_lion.py:64,91-96)."""
+    if sr_key and p.dtype == torch.bfloat16:
+        _apply_sr_(p, vote_direction(cnt.view_as(p), L, vote, tie, dtype=torch.float32), lr, wd, sr_key, 0)
+        momentum_update_(m, g, beta2)
+        return
     p.mul_(1 - lr * wd)
     u = vote_direction(cnt.view_as(p), L, vote, tie, dtype=torch.float32)
     if vote == "majority":

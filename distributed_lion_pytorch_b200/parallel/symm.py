@@ -115,7 +115,8 @@ class FusedExchange:
             self._grid[dtype] = g
         return g
 
-    def step(self, b, lr, wd, beta1, beta2, *, vote, tie, live_mask, max_grad_norm, seed, step_index) -> None:
+    def step(self, b, lr, wd, beta1, beta2, *, vote, tie, live_mask, max_grad_norm, seed, step_index,
+             sr_key: int = 0) -> None:
         tile = lion_ops.fused_tile(b.dtype)
         assert b.numel % tile == 0, "bucket length must be a multiple of the fused tile"
         chunk = self.chunk_elems - self.chunk_elems % tile
@@ -129,7 +130,7 @@ class FusedExchange:
                                 flag_ptrs=self.flags.ptrs, arena_words=self.arena_words, epoch=self.epoch,
                                 grid=grid, lr=lr, wd=wd, beta1=beta1, beta2=beta2, vote=vote, tie=tie,
                                 live_mask=live_mask, max_grad_norm=max_grad_norm, seed=seed, step=step_index,
-                                elem_base=off, status=self.status, mc_arena_ptr=self._mc_ptr())
+                                elem_base=off, status=self.status, mc_arena_ptr=self._mc_ptr(), sr_key=sr_key)
 
     def _mc_ptr(self) -> int:
         """NVLS multicast alias of the arena, when the fabric exposes one and DLION_MULTICAST allows it

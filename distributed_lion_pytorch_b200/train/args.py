@@ -62,6 +62,8 @@ class TrainingArguments:
     async_grad: bool = field(default=False, metadata={"help": "never synchronise gradients; exchange signs"})
     lion_vote: str = field(default="majority", metadata={"help": "majority | average | stochastic"})
     lion_tie: str = field(default="neg", metadata={"help": "neg (reference) | zero (paper)"})
+    lion_stochastic_rounding: bool = field(default=False, metadata={
+        "help": "write bf16 parameters with stochastic rounding (same noise on every rank; not in the reference)"})
     lion_max_grad_norm: Optional[float] = field(default=None, metadata={"help": "range for stochastic binarisation"})
     lion_drop_prob: float = field(default=0.0, metadata={"help": "simulated per-step worker drop-out probability"})
     lion_live_mask: Optional[str] = field(default=None, metadata={"help": "fixed live-worker mask, e.g. 0b1011"})

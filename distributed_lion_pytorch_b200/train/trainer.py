@@ -143,7 +143,8 @@ class Trainer:
                 mgn = a.lion_max_grad_norm if a.lion_vote != "stochastic" else (a.lion_max_grad_norm or 1.0)
                 comm = lion_comm_for(a, self.sync_gradients)
                 self.optimizer = Lion(params, lr=a.learning_rate, weight_decay=a.weight_decay, max_grad_norm=mgn,
-                                      vote=vote, tie=a.lion_tie, comm=comm, seed=a.seed)
+                                      vote=vote, tie=a.lion_tie, comm=comm, seed=a.seed,
+                                      stochastic_rounding=a.lion_stochastic_rounding)
             else:   # reference: run_clm.py:584 (hard-codes weight_decay=0.1 there — D13; we honour the flag)
                 self.optimizer = torch.optim.AdamW(params, lr=a.learning_rate, weight_decay=a.weight_decay)
         if self.lr_scheduler is None:

@@ -65,6 +65,7 @@ class ScriptArguments:
     # ---- additions
     lion_vote: Optional[str] = field(default="majority", metadata={"help": "majority | average | stochastic"})
     lion_tie: Optional[str] = field(default="neg")
+    lion_stochastic_rounding: Optional[bool] = field(default=False)
     lion_drop_prob: Optional[float] = field(default=0.0)
     lion_live_mask: Optional[str] = field(default=None)
     comm: Optional[str] = field(default="auto")
@@ -161,7 +162,8 @@ def main(argv=None):
         vote = "majority" if script_args.lion_vote == "stochastic" else script_args.lion_vote
         optimizer = Lion(params, lr=script_args.learning_rate, weight_decay=script_args.weight_decay, vote=vote,
                          tie=script_args.lion_tie, comm=comm, seed=script_args.seed,
-                         max_grad_norm=1.0 if script_args.lion_vote == "stochastic" else None)
+                         max_grad_norm=1.0 if script_args.lion_vote == "stochastic" else None,
+                         stochastic_rounding=script_args.lion_stochastic_rounding)
         dpo_trainer.optimizer = optimizer
         dpo_trainer.lr_scheduler = get_cosine_schedule_with_warmup(optimizer, script_args.warmup_steps,
                                                                    script_args.max_steps)

@@ -55,6 +55,12 @@ int dlion_device_sm_count(int* out);
  * reference: distributed_lion.py:47-59 (update_fn: 7 ATen kernels, 2 temporaries). */
 int dlion_lion_local(void* p, const void* g, void* m, int64_t n, int dtype, float lr, float decay,
                      float beta1, float omb1, float beta2, float omb2, void* stream);
+/* Same with opt-in stochastic rounding of the parameter write (bf16 only; other dtypes ignore it): sr_key != 0
+ * selects it, the random bits are a counter hash of (sr_key, elem_base + index), so every rank and every
+ * back-end draws the same bits for the same bucket element.  Not in the reference (at lr ~ 1e-4
+ * a Lion update is below half a bf16 ulp of a typical weight). */
+int dlion_lion_local_sr(void* p, const void* g, void* m, int64_t n, int dtype, float lr, float decay, float beta1,
+                        float omb1, float beta2, float omb2, uint64_t sr_key, int64_t elem_base, void* stream);
 
 /* Sign + pack: words[e/32] bit e%32 = (b1*m + (1-b1)*g)[e] > 0; tail bits of the last word are 0.
  * stoch_r > 0 selects stochastic binarisation, bit ~ Bernoulli((c + r) / 2r) with a Philox
@@ -69,6 +75,9 @@ int dlion_sign_pack(const void* m, const void* g, uint32_t* words, int64_t n, in
 int dlion_vote_update(void* p, const void* g, void* m, const uint32_t* gathered, int64_t row_words,
                       int world, uint32_t live_mask, int64_t n, int dtype, float lr, float decay,
                       float beta2, float omb2, int vote, void* stream);
+int dlion_vote_update_sr(void* p, const void* g, void* m, const uint32_t* gathered, int64_t row_words, int world,
+                         uint32_t live_mask, int64_t n, int dtype, float lr, float decay, float beta2, float omb2,
+                         int vote, uint64_t sr_key, void* stream);
 
 /* N1 — the fused sign-pack-exchange-vote-update kernel (one persistent cooperative launch).
  *
@@ -116,6 +125,8 @@ typedef struct {
   int64_t emu_stride;
   int32_t* status;
   int64_t spin_limit;  /* flag polls before giving up (0 = default) */
+  uint64_t sr_key;     /* != 0: stochastic rounding of the bf16 parameter write, keyed by (sr_key, element index) —
+                          identical on every rank; 0 = round to nearest (the reference's arithmetic) */
 } dlion_fused_args;
 
 #define DLION_FUSED_MAX_CTAS 1024

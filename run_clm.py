@@ -175,7 +175,8 @@ def main(argv=None):
         sync = (not training_args.async_grad) or training_args.comm == "nccl_allreduce"
         comm = lion_comm_for(training_args, sync)
         optimizer = Lion(model.parameters(), lr=training_args.learning_rate, weight_decay=training_args.weight_decay,
-                         max_grad_norm=mgn, vote=vote, tie=training_args.lion_tie, comm=comm, seed=training_args.seed)
+                         max_grad_norm=mgn, vote=vote, tie=training_args.lion_tie, comm=comm, seed=training_args.seed,
+                         stochastic_rounding=training_args.lion_stochastic_rounding)
         optimizers = (optimizer, get_cosine_schedule_with_warmup(optimizer, training_args.warmup_steps,
                                                                  training_args.max_steps))
     # reference: run_clm.py:587; --comm nccl_allreduce forces the synchronous-gradient baseline

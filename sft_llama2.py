@@ -124,7 +124,8 @@ def main(argv=None):
         vote = "majority" if training_args.lion_vote == "stochastic" else training_args.lion_vote
         optimizer = Lion(params, lr=training_args.learning_rate, weight_decay=training_args.weight_decay, vote=vote,
                          tie=training_args.lion_tie, comm=comm, seed=training_args.seed,
-                         max_grad_norm=training_args.lion_max_grad_norm)
+                         max_grad_norm=training_args.lion_max_grad_norm,
+                         stochastic_rounding=training_args.lion_stochastic_rounding)
         trainer.optimizer = optimizer
         trainer.lr_scheduler = get_cosine_schedule_with_warmup(optimizer, training_args.warmup_steps,
                                                                training_args.max_steps)

@@ -230,3 +230,26 @@ def test_replica_checksums_detect_a_diverged_worker():
     outs = run_distributed(_worker_replica_check, 3)
     assert all(o[0] is True and o[1] is False and o[2] is True for o in outs)
     assert outs[0][3] == outs[1][3] == outs[2][3] and len(outs[0][3]) == 2      # one checksum per bucket
+
+
+def _worker_sr(rank, world, comm):
+    from distributed_lion import Lion
+    torch.manual_seed(0)
+    ps = [torch.nn.Parameter((torch.randn(1000) * 0.5).bfloat16()), torch.nn.Parameter(torch.randn(64, 9).bfloat16())]
+    ref = [p.detach().clone() for p in ps]
+    opt = Lion(ps, lr=1e-4, weight_decay=0.1, stochastic_rounding=True, seed=5, comm=comm)
+    g = torch.Generator().manual_seed(100 + rank)
+    for _ in range(4):
+        for p in ps:
+            p.grad = torch.randn(p.shape, generator=g).to(p.dtype)
+        opt.step()
+    moved = sum(int((p.detach() != r).sum()) for p, r in zip(ps, ref))
+    return [p.detach().clone() for p in ps], opt.replicas_identical(), moved
+
+
+@pytest.mark.parametrize("comm", ["nccl_1bit"])
+def test_stochastic_rounding_keeps_replicas_bit_identical(comm):
+    outs = run_distributed(_worker_sr, 3, comm)
+    for o in outs[1:]:
+        assert all(torch.equal(a, b) for a, b in zip(o[0], outs[0][0]))      # same noise on every rank
+    assert all(o[1] for o in outs) and outs[0][2] > 0

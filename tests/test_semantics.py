@@ -127,3 +127,44 @@ def test_native_cpu_codec_matches_oracle(n):
             assert torch.equal(p, sem.pack_bits(v))
         gathered = torch.stack(packed)
         assert torch.equal(cpu_ops.count_votes(gathered, n, mask), sem.count_votes(gathered, n, mask))
+
+
+def test_stochastic_rounding_is_unbiased_exact_on_representables_and_deterministic():
+    from distributed_lion_pytorch_b200.optim import semantics as sem
+    key = sem.sr_key(seed=11, step=4)
+    assert key != 0 and key == sem.sr_key(11, 4) and key != sem.sr_key(11, 5) and key != sem.sr_key(12, 4)
+    n = 1 << 18
+    for frac in (1 / 8, 1 / 2, 15 / 16):
+        for sign in (1.0, -1.0):
+            x = torch.full((n,), sign * (1.0 + frac * 2.0 ** -7))          # between the bf16 neighbours 1 and 1 + 2^-7
+            y = sem.stochastic_round_bf16(x, key).float()
+            assert set(y.abs().unique().tolist()) <= {1.0, 1.0 + 2.0 ** -7}
+            up = float((y.abs() > 1.0).float().mean())
+            assert abs(up - frac) < 0.01, (frac, up)                        # P(round away from zero) = discarded fraction
+            assert abs(float(y.mean()) - float(x.mean())) < 2.0 ** -7 * 0.01
+    exact = torch.tensor([0.0, 1.0, -2.5, 2.0 ** 127, float("inf"), float("-inf")]).repeat(100)
+    assert torch.equal(sem.stochastic_round_bf16(exact, key).float(), exact.bfloat16().float())
+    assert torch.isnan(sem.stochastic_round_bf16(torch.tensor([float("nan")]), key)).all()
+    # layout invariance: element e of the bucket gets the same noise whether it is rounded in one call or in pieces
+    x = torch.randn(4096) * 0.02
+    whole = sem.stochastic_round_bf16(x, key)
+    parts = torch.cat([sem.stochastic_round_bf16(x[:1024], key, 0), sem.stochastic_round_bf16(x[1024:], key, 1024)])
+    assert torch.equal(whole, parts)
+
+
+def test_stochastic_rounding_lets_sub_ulp_updates_accumulate():
+    """lr = 1e-4 on weights of magnitude 1: round-to-nearest never moves them, stochastic rounding moves their mean by
+    lr per step — the reason the option exists."""
+    from distributed_lion_pytorch_b200.optim import semantics as sem
+    n, steps, lr = 1 << 14, 64, 1e-4
+    g = torch.ones(n).bfloat16()
+    for sr in (False, True):
+        p = torch.ones(n).bfloat16()
+        m = torch.zeros(n).bfloat16()
+        for s in range(steps):
+            sem.local_lion_step_(p, g, m, lr, 0.0, 0.9, 0.99, sr_key=sem.sr_key(0, s) if sr else 0)
+        drift = 1.0 - float(p.float().mean())
+        if sr:
+            assert abs(drift - steps * lr) < 0.15 * steps * lr, drift
+        else:
+            assert drift == 0.0
