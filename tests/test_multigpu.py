@@ -16,7 +16,7 @@ def _net(seed, dtype):
     return m.to(dtype)
 
 
-def _worker(rank, world, dtype_name, vote, tie, mask, steps, skew, multicast=False):
+def _worker(rank, world, dtype_name, vote, tie, mask, steps, skew, multicast=False, sr=False):
     import os
     import time
     os.environ["DLION_MULTICAST"] = "1" if multicast else "0"
@@ -27,7 +27,7 @@ def _worker(rank, world, dtype_name, vote, tie, mask, steps, skew, multicast=Fal
     for comm in ("fused", "nccl_1bit"):
         nets[comm] = _net(0, dtype).to(dev)
         opts[comm] = Lion(nets[comm].parameters(), lr=1e-3, weight_decay=0.1, vote=vote, tie=tie, comm=comm,
-                          live_mask=mask)
+                          live_mask=mask, stochastic_rounding=sr, seed=9)
     g = torch.Generator(device=dev).manual_seed(100 + rank)
     for s in range(steps):
         x = torch.randn(64, 256, device=dev, generator=g).to(dtype)
@@ -42,7 +42,8 @@ def _worker(rank, world, dtype_name, vote, tie, mask, steps, skew, multicast=Fal
     opts["fused"]._backend._ctx.check_status()
     flat = {c: torch.cat([p.detach().float().flatten() for p in nets[c].parameters()]).cpu() for c in nets}
     mom = torch.cat([opts["fused"].state[p]["exp_avg"].float().flatten() for p in nets["fused"].parameters()]).cpu()
-    return dict(fused=flat["fused"], split=flat["nccl_1bit"], mom=mom, backend=opts["fused"].backend_name,
+    same = opts["fused"].replicas_identical()
+    return dict(fused=flat["fused"], split=flat["nccl_1bit"], mom=mom, backend=opts["fused"].backend_name, same=same,
                 how=opts["fused"]._backend._ctx.flags.how, mc=opts["fused"]._backend._ctx.uses_multicast)
 
 
@@ -89,3 +90,16 @@ def test_fused_nvls_multicast_send_path():
     for o in outs:
         assert torch.equal(o["fused"], o["split"]) and torch.equal(o["fused"], outs[0]["fused"])
 
+
+
+def test_stochastic_rounding_fused_equals_split_and_replicas_identical():
+    """Opt-in stochastic rounding on real GPUs: the rounding noise is keyed by (seed, step, element), so the fused
+    kernel, the split path and every rank draw the same bits."""
+    world = min(torch.cuda.device_count(), 8)
+    outs = run_distributed(_worker, world, "bfloat16", "majority", "neg", None, 10, True, False, True, backend="nccl",
+                           timeout=300)
+    base = run_distributed(_worker, world, "bfloat16", "majority", "neg", None, 10, False, False, False, backend="nccl",
+                           timeout=300)
+    for o in outs:
+        assert o["same"] and torch.equal(o["fused"], o["split"]) and torch.equal(o["fused"], outs[0]["fused"])
+    assert not torch.equal(outs[0]["fused"], base[0]["fused"])          # and it is not round-to-nearest
