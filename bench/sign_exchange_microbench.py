@@ -31,6 +31,9 @@ from distributed_lion_pytorch_b200.ops import lion_ops  # noqa: E402
 from distributed_lion_pytorch_b200.parallel import runtime as rt  # noqa: E402
 
 
+BURST = 1      # --burst K: K back-to-back steps per timed sample (amortises host launch path and barrier skew)
+
+
 def timeit(fn, iters, warm, device):
     flush = torch.empty(256 << 20, dtype=torch.uint8, device=device)
     for _ in range(warm):
@@ -43,10 +46,11 @@ def timeit(fn, iters, warm, device):
         dist.barrier()
         a, b = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
         a.record()
-        fn()
+        for _ in range(BURST):
+            fn()
         b.record()
         torch.cuda.synchronize()
-        t = torch.tensor([a.elapsed_time(b)], device=device)
+        t = torch.tensor([a.elapsed_time(b) / BURST], device=device)
         dist.all_reduce(t, op=dist.ReduceOp.MAX)
         ts.append(float(t))
     ts.sort()
@@ -58,8 +62,11 @@ def main():
     ap.add_argument("--sizes", default="1,16,124")
     ap.add_argument("--iters", type=int, default=8)
     ap.add_argument("--out", default=None)
+    ap.add_argument("--burst", type=int, default=1, help="steps per timed sample; > 1 reports the pipelined per-step time")
     ap.add_argument("--skip-reference-above", type=float, default=200.0)
     a = ap.parse_args()
+    global BURST
+    BURST = max(1, a.burst)
     device = rt.init_distributed()
     rank, W = rt.rank(), rt.world_size()
     peaks = json.loads((ROOT / "MEASURED_PEAKS.json").read_text()) if (ROOT / "MEASURED_PEAKS.json").exists() else {}
@@ -74,7 +81,7 @@ def main():
     rows = []
     for mp in [float(x) for x in a.sizes.split(",")]:
         n = int(mp * 1e6) // 8192 * 8192
-        res = {"n": n, "world": W}
+        res = {"n": n, "world": W, "burst": BURST}
         for comm in ("fused", "fused_multicast", "nccl_1bit"):
             import os
             os.environ["DLION_MULTICAST"] = "1" if comm == "fused_multicast" else "0"
