@@ -10,6 +10,7 @@ loadable); callers keep their unfused path for that case, so nothing here is req
 from __future__ import annotations
 
 import ctypes as C
+import logging
 import os
 from typing import Dict, Optional
 
@@ -66,8 +67,11 @@ def gemm(a: torch.Tensor, b: torch.Tensor, d: torch.Tensor, *, trans_a: bool = F
                   _cabi.dtype_code(d.dtype), algo_rank)
     with torch.cuda.device(d.device):
         rc = _cabi.lib().dlion_lt_gemm(C.byref(args), _cabi.stream_ptr(d.device))
-    if rc == -2:                # DLION_E_UNSUPPORTED: remember and let the caller fall back
+    if rc == -2:                # DLION_E_UNSUPPORTED: remember, say so once, and let the caller fall back
         _unsupported.add(sig)
+        logging.getLogger("dlion.lt_gemm").warning(
+            "cuBLASLt declined %s (%s); using the unfused path for this shape",
+            sig, _cabi.lib().dlion_last_error().decode(errors="replace"))
         return False
     if rc != 0:                 # not _cabi.check: these are the library's kernels, not counted as ours
         raise RuntimeError(f"libdlion lt_gemm failed (code {rc}): "
