@@ -262,3 +262,37 @@ def test_run_clm_on_text_files_with_eval_metrics(tmp_path):
     losses = [h["loss"] for h in hist if "loss" in h]
     assert losses[-1] < losses[0]                              # byte-level LM on repetitive text learns quickly
     assert {"all_results.json", "train_results.json", "eval_results.json", "README.md"} <= set(p.name for p in out.iterdir())
+
+
+def _worker_divergence(rank, world, outdir, mode):
+    from distributed_lion_pytorch_b200.models import build_model
+    from distributed_lion_pytorch_b200.train import AsyncTrainer, SyntheticTokenDataset, TrainingArguments
+    torch.manual_seed(0)
+    model = build_model("gpt2-tiny")
+    args = TrainingArguments(output_dir=outdir, per_device_train_batch_size=2, max_steps=5, learning_rate=1e-3, lion=True,
+                             async_grad=True, logging_steps=1, save_steps=100, seed=3, check_replicas=mode)
+
+    def corrupt(trainer, logs):                    # a worker's memory is silently corrupted after step 2
+        if trainer.state.global_step == 2 and rank == 1 and "loss" in logs:
+            with torch.no_grad():
+                next(model.parameters()).view(-1)[7] += 1.0
+    tr = AsyncTrainer(model=model, args=args, train_dataset=SyntheticTokenDataset(512, 32, 64, seed=1), callbacks=[corrupt])
+    try:
+        tr.train()
+        err = None
+    except RuntimeError as e:
+        err = str(e)
+    checks = [h["replicas_identical"] for h in tr.state.log_history if "replicas_identical" in h]
+    flat = torch.cat([p.detach().flatten() for p in model.parameters()])
+    return dict(err=err, checks=checks, params=flat, step=tr.state.global_step)
+
+
+def test_trainer_detects_and_repairs_a_diverged_replica(tmp_path):
+    outs = run_distributed(_worker_divergence, 2, str(tmp_path / "a"), "resync")
+    assert all(o["err"] is None and o["step"] == 5 for o in outs)
+    assert outs[0]["checks"] == [1, 1, 0, 1, 1]                           # seen at step 3, repaired, clean afterwards
+    assert torch.equal(outs[0]["params"], outs[1]["params"])
+    outs = run_distributed(_worker_divergence, 2, str(tmp_path / "b"), "raise")
+    assert all(o["err"] is not None and "diverged" in o["err"] and o["step"] == 3 for o in outs)
+    outs = run_distributed(_worker_divergence, 2, str(tmp_path / "c"), "off")
+    assert all(o["err"] is None and not o["checks"] for o in outs) and not torch.equal(outs[0]["params"], outs[1]["params"])
