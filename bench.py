@@ -248,11 +248,24 @@ def run_reference(a, device, rank, world):
         from transformers import GPT2Config, GPT2LMHeadModel, get_cosine_schedule_with_warmup
     except Exception as e:
         return {"unavailable": f"transformers not importable: {e}"}
-    if a.model != "gpt2":
-        return {"unavailable": "reference arm implements the GPT-2 recipe only"}
+    if a.lora or a.load_in_4bit:
+        return {"unavailable": "reference arm: peft / bitsandbytes are not installed on this image"}
     torch.manual_seed(1234)
-    cfg = GPT2Config()
-    model = GPT2LMHeadModel(cfg).to(device=device, dtype=torch.bfloat16)
+    if a.model == "gpt2":
+        cfg = GPT2Config()
+        model = GPT2LMHeadModel(cfg).to(device=device, dtype=torch.bfloat16)
+    elif a.model == "llama-2-7b":      # non-default: the second model BASELINE names (reference: sft_llama2.py:147)
+        from transformers import LlamaConfig, LlamaForCausalLM
+        cfg = LlamaConfig()            # transformers' defaults are the Llama-2-7B shape
+        old_dtype = torch.get_default_dtype()
+        torch.set_default_dtype(torch.bfloat16)
+        try:
+            with torch.device(device):
+                model = LlamaForCausalLM(cfg)
+        finally:
+            torch.set_default_dtype(old_dtype)
+    else:
+        return {"unavailable": f"reference arm implements gpt2 and llama-2-7b, not {a.model}"}
     model.train()
     net = model
     if world > 1:
