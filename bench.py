@@ -22,9 +22,7 @@ from __future__ import annotations
 import argparse
 import json
 import os
-import statistics
 import sys
-import threading
 import time
 from pathlib import Path
 
@@ -46,58 +44,13 @@ def parse():
     ap.add_argument("--ga", type=int, default=8)
     ap.add_argument("--comm", default="auto")
     ap.add_argument("--no-e2e", action="store_true")
+    ap.add_argument("--no-verify", action="store_true", help="skip the post-run fused == split / replica check")
     ap.add_argument("--lora", action="store_true", help="non-default: LoRA on q_proj/v_proj (the sft_llama2 arrangement)")
     ap.add_argument("--load-in-4bit", action="store_true", help="non-default: NF4 frozen base under --lora")
     return ap.parse_args()
 
 
-class ClockSampler(threading.Thread):
-    """Samples SM clock + throttle reasons of this rank's GPU every 200 ms during the timed region."""
-
-    def __init__(self, index: int):
-        super().__init__(daemon=True)
-        self.index, self.samples, self.reasons, self.max_mhz = index, [], set(), None
-        self._stop_evt = threading.Event()
-        self.ok = False
-        try:
-            import pynvml
-            pynvml.nvmlInit()
-            self.nv = pynvml
-            self.h = pynvml.nvmlDeviceGetHandleByIndex(index)
-            self.max_mhz = pynvml.nvmlDeviceGetMaxClockInfo(self.h, pynvml.NVML_CLOCK_SM)
-            self.ok = True
-        except Exception:
-            self.ok = False
-
-    def run(self):
-        if not self.ok:
-            return
-        nv = self.nv
-        names = {"hw_slowdown": getattr(nv, "nvmlClocksEventReasonHwSlowdown", 0x8),
-                 "sw_power_cap": getattr(nv, "nvmlClocksEventReasonSwPowerCap", 0x4),
-                 "hw_thermal_slowdown": getattr(nv, "nvmlClocksEventReasonHwThermalSlowdown", 0x40),
-                 "sw_thermal_slowdown": getattr(nv, "nvmlClocksEventReasonSwThermalSlowdown", 0x20),
-                 "hw_power_brake": getattr(nv, "nvmlClocksEventReasonHwPowerBrakeSlowdown", 0x80)}
-        while not self._stop_evt.is_set():
-            try:
-                self.samples.append(nv.nvmlDeviceGetClockInfo(self.h, nv.NVML_CLOCK_SM))
-                try:
-                    bits = nv.nvmlDeviceGetCurrentClocksEventReasons(self.h)
-                except Exception:
-                    bits = nv.nvmlDeviceGetCurrentClocksThrottleReasons(self.h)
-                for k, v in names.items():
-                    if bits & v:
-                        self.reasons.add(k)
-            except Exception:
-                pass
-            self._stop_evt.wait(0.2)
-
-    def stop(self):
-        self._stop_evt.set()
-        if self.is_alive():
-            self.join(timeout=2)
-        return {"sm_mhz": statistics.median(self.samples) if self.samples else None, "sm_max_mhz": self.max_mhz,
-                "reasons": sorted(self.reasons), "samples": len(self.samples)}
+from distributed_lion_pytorch_b200.utils.profiling import ClockSampler  # noqa: E402
 
 
 def make_batches(n_micro, batch, seq, vocab, seed, pin):
@@ -148,6 +101,40 @@ def timed_region(step_fn, steps, warmup, device, e2e: bool):
         dist.barrier()
     torch.cuda.synchronize(device)
     return total, per_step
+
+
+def load_peaks():
+    """Roofline denominators: the driver-measured MEASURED_PEAKS.json, else the profiling recipe's fallback."""
+    f = ROOT / "MEASURED_PEAKS.json"
+    if f.exists():
+        try:
+            d = json.loads(f.read_text())
+            return {"hbm_gbs": float(d["hbm_gbs"]), "source": "measured"}
+        except Exception:
+            pass
+    return {"hbm_gbs": 6650.0, "source": "fallback"}
+
+
+NVLINK_GBS = 770.0      # measured peer-copy rate per direction per GPU (B200_PROFILING.md)
+
+
+def optimizer_step_report(events, n_params, elem_size, world, device):
+    """Device time of clip + optimizer + zero_grad per step (CUDA events inside the timed steps, max over ranks)
+    against its roofline: the slower of the HBM bytes at the measured copy peak and the packed sign bits over
+    NVLink.  HBM bytes per parameter: g is read twice (the norm must be known before any element is scaled) and
+    cleared once, m and p are read and written once: 7 * elem_size, plus (W + 1) / 8 bytes of sign words."""
+    if not events:
+        return None
+    us = sum(a.elapsed_time(b) for a, b in events) / len(events) * 1e3
+    us = max_over_ranks(us, device)
+    peaks = load_peaks()
+    hbm_bytes = n_params * (7 * elem_size + ((world + 1) / 8 if world > 1 else 0))
+    nvl_bytes = n_params / 8 * (world - 1)
+    roof_us = max(hbm_bytes / (peaks["hbm_gbs"] * 1e9), nvl_bytes / (NVLINK_GBS * 1e9)) * 1e6
+    return {"optimizer_step_us": round(us, 1), "optimizer_step_roofline_us": round(roof_us, 1),
+            "optimizer_step_roofline_frac": round(roof_us / us, 3), "optimizer_step_includes": "grad-norm + clip + "
+            "sign exchange + vote + update + momentum + gradient zero-fill", "roofline_peaks": peaks["source"],
+            "optimizer_params": int(n_params)}
 
 
 def max_over_ranks(x, device):
@@ -208,7 +195,14 @@ def run_ours(a, device, rank, world):
     sampler = ClockSampler(torch.cuda.current_device())
     n0 = _cabi.LAUNCHES
     sampler.start()
-    total, per_step = timed_region(step_device, a.steps, a.warmup, device, e2e=False)
+    opt_events = []
+
+    def step_device_timed(i):
+        trainer.optimizer_step_events = opt_events if i >= a.warmup else None
+        step_device(i)
+
+    total, per_step = timed_region(step_device_timed, a.steps, a.warmup, device, e2e=False)
+    trainer.optimizer_step_events = None
     clocks = sampler.stop()
     launches = (_cabi.LAUNCHES - n0) * a.steps // (a.steps + a.warmup)
     e2e_total = None
@@ -224,8 +218,25 @@ def run_ours(a, device, rank, world):
         h2d = a.ga * 2 * a.batch * a.seq * 8
         res["e2e"] = {"value": tokens_per_step * a.steps / e2e_total, "unit": "tokens/s",
                       "h2d_bytes_per_step": h2d, "d2h_bytes_per_step": 4, "ms_per_step": e2e_total / a.steps * 1e3}
+    n_params = sum(b.numel for b in opt.buckets)
+    esize = opt.buckets[0].flat_p.element_size() if opt.buckets else 2
+    rep = optimizer_step_report(opt_events, n_params, esize, world, device)
+    if rep:
+        res.update(rep)
     if hasattr(opt._backend, "_ctx") and opt._backend._ctx is not None:
         opt._backend._ctx.check_status()
+        res["nvls_multicast"] = bool(opt._backend._ctx.uses_multicast)
+    # Proof, outside the timed region, that the step the numbers above come from is THE update: one more optimizer
+    # step taken twice — through the active back-end and through the split pack / all_gather / vote path on clones —
+    # compared bit for bit on every rank, plus the replica checksums (reference: distributed_lion.py:61-96).
+    if world > 1 and not a.no_verify:
+        for j in range(a.ga):
+            trainer.training_step(trainer.model, dev[j % len(dev)])
+        trainer._clip_gradients()
+        chk = opt.step_crosscheck()
+        opt.zero_grad()
+        res["fused_equals_split"] = chk["equal"]
+        res["replicas_identical"] = chk["replicas_identical"]
     return res
 
 
@@ -287,16 +298,27 @@ def run_reference(a, device, rank, world):
             (loss / a.ga).backward()
         return loss.detach() / a.ga
 
+    opt_events = []
+    rec = {"on": False}
+
     def finish():
+        if rec["on"]:
+            ea, eb = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
+            ea.record()
         torch.nn.utils.clip_grad_norm_(model.parameters(), 1.0)         # HF Trainer default max_grad_norm
         opt.step()
         sched.step()
         model.zero_grad()
+        if rec["on"]:
+            eb.record()
+            opt_events.append((ea, eb))
 
     def step_device(i):
         for j in range(a.ga):
             micro(dev[(i * a.ga + j) % len(dev)])
+        rec["on"] = i >= a.warmup
         finish()
+        rec["on"] = False
 
     def step_e2e(i):
         tot = None
@@ -318,6 +340,10 @@ def run_reference(a, device, rank, world):
     total = max_over_ranks(total, device)
     res = {"ms_per_step": total / a.steps * 1e3, "value": tokens_per_step * a.steps / total, "gpu_launches": 0,
            "clocks": clocks, "backend": "reference:" + opt.update_fn.__name__, "loss": last.get("loss")}
+    n_params = sum(p.numel() for p in model.parameters())
+    rep = optimizer_step_report(opt_events, n_params, 2, world, device)
+    if rep:
+        res.update(rep)
     if e2e_total is not None:
         e2e_total = max_over_ranks(e2e_total, device)
         res["e2e"] = {"value": tokens_per_step * a.steps / e2e_total, "unit": "tokens/s",
@@ -359,12 +385,18 @@ def main():
                                "lora": bool(a.lora), "load_in_4bit": bool(a.load_in_4bit),
                                "l2": "working set >> 126 MB L2 and a 256 MB scratch write between timed steps"},
                     "clocks": res["clocks"], "gpu_launches": res["gpu_launches"], "loss": res.get("loss")}
-            if "peak_mem_gb" in res:
-                line["peak_mem_gb"] = res["peak_mem_gb"]
+            for k in ("optimizer_step_us", "optimizer_step_roofline_us", "optimizer_step_roofline_frac",
+                      "optimizer_step_includes", "roofline_peaks", "optimizer_params", "fused_equals_split",
+                      "replicas_identical", "nvls_multicast", "peak_mem_gb"):
+                if k in res:
+                    line[k] = res[k]
             if "e2e" in res:
                 line["e2e"] = res["e2e"]
             print(json.dumps(line))
     rt.shutdown()
+    if res.get("fused_equals_split") is False or res.get("replicas_identical") is False:
+        print("[bench] the fused step disagrees with the split path or replicas diverged", file=sys.stderr)
+        return 3
     return 0
 
 

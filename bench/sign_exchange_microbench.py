@@ -11,8 +11,12 @@ events, max over ranks, L2 flushed between iterations:
   allreduce   plain DDP-style: NCCL bf16 all-reduce of the gradient + fused local Lion kernel
   reference   the reference's update_fn_distributed on the same flat tensor (one big tensor: its
               best case — it really runs once per parameter tensor, 148x for GPT-2 small)
-and prints each as time, achieved HBM GB/s on the 10 B/param algorithmic traffic and the
-fraction of the fused roofline max(HBM time, NVLink time).
+and prints each as time and as a fraction of the fused roofline max(HBM time, NVLink time).
+
+`*_full` rows time what a trainer step runs around the exchange as well — gradient norm, clip, update, gradient
+zero-fill: for `fused_full` that is `sumsq` + ONE fused kernel (clip and zero-fill ride inside it; roofline
+14 B/param: g read twice and cleared once, m and p read and written once); for the baselines it is norm + clip
+kernel + their step + memset.  Every row carries the SM clocks and throttle reasons sampled while it ran.
 """
 import argparse
 import gc
@@ -28,20 +32,26 @@ ROOT = Path(__file__).resolve().parent.parent
 sys.path.insert(0, str(ROOT))
 from distributed_lion import Lion  # noqa: E402
 from distributed_lion_pytorch_b200.ops import lion_ops  # noqa: E402
+from distributed_lion_pytorch_b200.ops import bucket_ops  # noqa: E402
 from distributed_lion_pytorch_b200.parallel import runtime as rt  # noqa: E402
+from distributed_lion_pytorch_b200.utils.profiling import ClockSampler  # noqa: E402
 
 
 BURST = 1      # --burst K: K back-to-back steps per timed sample (amortises host launch path and barrier skew)
 
 
-def timeit(fn, iters, warm, device):
+def timeit(fn, iters, warm, device, prep=None):
     flush = torch.empty(256 << 20, dtype=torch.uint8, device=device)
     for _ in range(warm):
+        if prep is not None:
+            prep()
         fn()
     torch.cuda.synchronize()
     dist.barrier()
     ts = []
     for i in range(iters):
+        if prep is not None:
+            prep()                      # e.g. refill the gradients a zero-filling step consumed (untimed)
         flush.fill_(i)
         dist.barrier()
         a, b = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
@@ -82,18 +92,35 @@ def main():
     for mp in [float(x) for x in a.sizes.split(",")]:
         n = int(mp * 1e6) // 8192 * 8192
         res = {"n": n, "world": W, "burst": BURST}
+        sampler = ClockSampler(torch.cuda.current_device())
+        sampler.start()
+        import os
         for comm in ("fused", "fused_multicast", "nccl_1bit"):
-            import os
             os.environ["DLION_MULTICAST"] = "1" if comm == "fused_multicast" else "0"
             p = torch.nn.Parameter(torch.randn(n, device=device, dtype=torch.bfloat16))
             p.grad = torch.randn(n, device=device, dtype=torch.bfloat16)
             opt = Lion([p], lr=1e-4, weight_decay=0.1, comm="fused" if comm.startswith("fused") else comm)
             t = timeit(lambda: opt.step(), a.iters, 3, device)
+            unavailable = False
             if comm.startswith("fused"):
                 opt._backend._ctx.check_status()
                 if comm == "fused_multicast" and not opt._backend._ctx.uses_multicast:
-                    t = None                      # fabric exposes no multicast pointer
+                    t, unavailable = None, True    # fabric exposes no multicast pointer
             res[comm] = t
+            # the trainer's sequence around the exchange: norm -> (clip) -> step -> zero_grad
+            if not unavailable:
+                opt.zero_grads_in_step = True
+                noise = torch.randn(n, device=device, dtype=torch.bfloat16)
+
+                def full_step():
+                    opt.clip_grad_norm_(1.0)
+                    opt.step()
+                    opt.zero_grad()
+                res[comm + "_full"] = timeit(full_step, a.iters, 3, device,
+                                             prep=(lambda: p.grad.copy_(noise)) if BURST == 1 else None)
+                if comm.startswith("fused"):
+                    opt._backend._ctx.check_status()
+                del noise
             del opt, p
             gc.collect()
             torch.cuda.empty_cache()
@@ -106,6 +133,16 @@ def main():
             g.div_(W)
             lion_ops.local_step(p, g, m, 1e-4, 0.1, 0.9, 0.99)
         res["allreduce"] = timeit(ddp_step, a.iters, 3, device)
+
+        def ddp_full():
+            dist.all_reduce(g)
+            g.div_(W)
+            bucket_ops.clip_grad_norm_flat_([g], 1.0)
+            lion_ops.local_step(p, g, m, 1e-4, 0.1, 0.9, 0.99)
+            g.zero_()
+        noise = torch.randn(n, device=device, dtype=torch.bfloat16)
+        res["allreduce_full"] = timeit(ddp_full, a.iters, 3, device, prep=(lambda: g.copy_(noise)) if BURST == 1 else None)
+        del noise
         if ref is not None and mp <= a.skip_reference_above:
             res["reference"] = timeit(lambda: ref.update_fn_distributed(p, g, m, 1e-4, 0.1, 0.9, 0.99), max(a.iters // 2, 2),
                                       1, device)
@@ -116,6 +153,20 @@ def main():
         t_nvl = ((W - 1) * n / 8) / (nvl * 1e9) * 1e3
         res["roofline_ms"] = max(t_hbm, t_nvl)
         res["fused_frac_of_roofline"] = res["roofline_ms"] / res["fused"]
+        if res.get("fused_multicast"):
+            res["fused_multicast_frac_of_roofline"] = res["roofline_ms"] / res["fused_multicast"]
+        res["roofline_full_ms"] = max((14 * n + (W + 1) * n / 8) / (hbm * 1e9) * 1e3, t_nvl)
+        for k in ("fused_full", "fused_multicast_full"):
+            if res.get(k):
+                res[k + "_frac_of_roofline"] = res["roofline_full_ms"] / res[k]
+        clocks = sampler.stop()
+        # worst case over ranks: the lowest median clock, the union of throttle reasons
+        mhz = torch.tensor([float(clocks["sm_mhz"] or 0)], device=device)
+        dist.all_reduce(mhz, op=dist.ReduceOp.MIN)
+        allr = [None] * W
+        dist.all_gather_object(allr, clocks["reasons"])
+        res["clocks"] = {"sm_mhz_min_over_ranks": float(mhz), "sm_max_mhz": clocks["sm_max_mhz"],
+                         "reasons": sorted({r for rs in allr for r in rs}), "samples": clocks["samples"]}
         rows.append(res)
         if rank == 0:
             print(json.dumps(res))

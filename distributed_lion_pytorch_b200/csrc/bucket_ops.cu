@@ -203,10 +203,11 @@ extern "C" int dlion_clip_scale(void* x, int64_t n, int dtype, const float* sums
 // the library keeps resident until the process exits (kSumsqStaticBytes = 16,640 bytes per
 // device).
 //
-// Size limit: one CTA sums one fixed chunk of kSumsqStaticChunk = 65,536 elements and owns one
-// partial slot, and there are kSumsqStaticSlots = 4,096 slots, so a call may cover at most
-// DLION_SUMSQ_STATIC_MAX_N = 4,096 * 65,536 = 268,435,456 elements (one fused-optimizer
-// chunk).  Larger n is refused with DLION_E_TOOBIG and a message; nothing is launched.
+// Size limit: the launch uses grid = ceil(n / kSumsqStaticChunk) CTAs (kSumsqStaticChunk = 65,536), every CTA
+// owns exactly one partial slot, and the array has kSumsqStaticSlots = 4,096 slots — so a call may cover at most
+// 4,096 * 65,536 = 268,435,456 elements (one fused-optimizer chunk).  (The CTAs walk the input grid-stride, in
+// interleaved 2,048-element strips, not one contiguous 65,536-element chunk each; only the slot count is fixed.)
+// Larger n is refused with DLION_E_TOOBIG and a message; nothing is launched.
 //
 // Rules of use
 //  * The array name is only a host-side handle: the kernel needs the DEVICE address, which is

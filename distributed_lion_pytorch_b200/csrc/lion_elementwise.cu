@@ -11,6 +11,34 @@ namespace dlion {
 
 constexpr int kThreads = 256;
 
+// Gradient clipping folded into the optimizer kernels: the coefficient clip_grad_norm_ would apply, read on
+// the device from the sum of squares (no host sync).  1 (and `false`) = nothing to clip; a NaN norm also
+// leaves the gradients alone, like dlion_clip_scale.
+struct ClipArg {
+  const float* sumsq;   // device pointer or nullptr
+  float max_norm;
+};
+__device__ __forceinline__ bool clip_coef(const ClipArg& c, float& coef) {
+  coef = 1.f;
+  if (c.sumsq == nullptr) return false;
+  const float k = c.max_norm / (sqrtf(__ldg(c.sumsq)) + 1e-6f);
+  if (!(k < 1.0f)) return false;
+  coef = k;
+  return true;
+}
+// g' = round_T(g * coef): what a separate clip kernel would have stored
+template <typename T>
+__device__ __forceinline__ void clip8(float (&g)[8], float coef) {
+#pragma unroll
+  for (int i = 0; i < 8; ++i) g[i] *= coef;
+  round8<T>(g);
+}
+template <typename T>
+__device__ __forceinline__ void zero8(T* __restrict__ ptr) {
+#pragma unroll
+  for (int i = 0; i < (int)(sizeof(T) * 8 / 16); ++i) reinterpret_cast<uint4*>(ptr)[i] = make_uint4(0u, 0u, 0u, 0u);
+}
+
 static inline int grid_for(int64_t nvec) {
   const int64_t want = (nvec + kThreads - 1) / kThreads;
   const int64_t cap = (int64_t)kNumSMs * 16;   // 8 resident CTAs/SM * 2 waves of grid-stride
@@ -19,17 +47,22 @@ static inline int grid_for(int64_t nvec) {
 
 // ------------------------------------------------------------------ N6
 template <typename T>
-__global__ void __launch_bounds__(kThreads) lion_local_kernel(T* __restrict__ p, const T* __restrict__ g,
+__global__ void __launch_bounds__(kThreads) lion_local_kernel(T* __restrict__ p, T* __restrict__ g,
                                                               T* __restrict__ m, int64_t n, float lr, float decay,
                                                               float beta1, float omb1, float beta2, float omb2,
-                                                              uint64_t sr_key, int64_t vec_base) {
+                                                              uint64_t sr_key, int64_t vec_base, ClipArg clip_arg,
+                                                              int zero_g) {
   const int64_t nvec = n >> 3;
   const int64_t stride = (int64_t)gridDim.x * blockDim.x;
+  float coef;
+  const bool clip = clip_coef(clip_arg, coef);
   for (int64_t v = (int64_t)blockIdx.x * blockDim.x + threadIdx.x; v < nvec; v += stride) {
     float pf[8], gf[8], mf[8];
     load8<T>(g + v * 8, gf);
     load8<T>(m + v * 8, mf);
     load8<T>(p + v * 8, pf);
+    if (clip) clip8<T>(gf, coef);
+    if (zero_g) zero8<T>(g + v * 8);
     float c[8], u[8];
     blend8<T>(mf, gf, beta1, omb1, c);
     const float thr = tie_to_zero<T>();
@@ -42,7 +75,10 @@ __global__ void __launch_bounds__(kThreads) lion_local_kernel(T* __restrict__ p,
   // ragged tail (< 8 elements): one thread (always round-to-nearest)
   if (blockIdx.x == 0 && threadIdx.x == 0) {
     for (int64_t e = nvec << 3; e < n; ++e) {
-      const float gf = DT<T>::to_f(g[e]), mf = DT<T>::to_f(m[e]), pf = DT<T>::to_f(p[e]);
+      float gf = DT<T>::to_f(g[e]);
+      const float mf = DT<T>::to_f(m[e]), pf = DT<T>::to_f(p[e]);
+      if (clip) gf = DT<T>::rnd(gf * coef);
+      if (zero_g) g[e] = DT<T>::from_f(0.f);
       const float c = DT<T>::rnd(lion_blend<T>(mf, gf, beta1, omb1));
       const float u = c > 0.f ? 1.f : (c < 0.f ? -1.f : 0.f);
       p[e] = DT<T>::from_f(lion_apply<T>(pf, u, lr, decay));
@@ -56,7 +92,9 @@ template <typename T>
 __global__ void __launch_bounds__(kThreads) sign_pack_kernel(const T* __restrict__ m, const T* __restrict__ g,
                                                              uint32_t* __restrict__ words, int64_t n, float beta1,
                                                              float omb1, float stoch_r, uint64_t seed, uint32_t step,
-                                                             uint32_t rank) {
+                                                             uint32_t rank, ClipArg clip_arg) {
+  float coef;
+  const bool clip = clip_coef(clip_arg, coef);
   // nvec4 = number of 32-element groups, rounded up: every lane quad owns one output word
   const int64_t nwords = (n + 31) >> 5;
   const int64_t nvec_padded = nwords << 2;
@@ -69,6 +107,7 @@ __global__ void __launch_bounds__(kThreads) sign_pack_kernel(const T* __restrict
       float gf[8], mf[8];
       load8<T>(g + e0, gf);
       load8<T>(m + e0, mf);
+      if (clip) clip8<T>(gf, coef);
       byte = sign_byte<T>(mf, gf, beta1, omb1, stoch_r, seed, step, rank, e0);
     } else if (e0 < n) {
       float gf[8], mf[8];
@@ -78,6 +117,7 @@ __global__ void __launch_bounds__(kThreads) sign_pack_kernel(const T* __restrict
         gf[i] = ok ? DT<T>::to_f(g[e0 + i]) : 0.f;
         mf[i] = ok ? DT<T>::to_f(m[e0 + i]) : 0.f;
       }
+      if (clip) clip8<T>(gf, coef);
       byte = sign_byte<T>(mf, gf, beta1, omb1, stoch_r, seed, step, rank, e0);
       byte &= (1u << (int)(n - e0)) - 1u;   // pad bits never vote
     }
@@ -91,11 +131,14 @@ __global__ void __launch_bounds__(kThreads) sign_pack_kernel(const T* __restrict
 
 // ------------------------------------------------------------------ vote + update
 template <typename T>
-__global__ void __launch_bounds__(kThreads) vote_update_kernel(T* __restrict__ p, const T* __restrict__ g,
+__global__ void __launch_bounds__(kThreads) vote_update_kernel(T* __restrict__ p, T* __restrict__ g,
                                                                T* __restrict__ m, const uint8_t* __restrict__ gathered,
                                                                int64_t row_bytes, int world, uint32_t live_mask,
                                                                int L, int64_t n, float lr, float decay, float beta2,
-                                                               float omb2, int vote, uint64_t sr_key) {
+                                                               float omb2, int vote, uint64_t sr_key, ClipArg clip_arg,
+                                                               int zero_g) {
+  float coef;
+  const bool clip = clip_coef(clip_arg, coef);
   const int64_t nvec = (n + 7) >> 3;
   const int64_t stride = (int64_t)gridDim.x * blockDim.x;
   for (int64_t v = (int64_t)blockIdx.x * blockDim.x + threadIdx.x; v < nvec; v += stride) {
@@ -126,6 +169,12 @@ __global__ void __launch_bounds__(kThreads) vote_update_kernel(T* __restrict__ p
         mf[i] = ok ? DT<T>::to_f(m[e0 + i]) : 0.f;
         pf[i] = ok ? DT<T>::to_f(p[e0 + i]) : 0.f;
       }
+    }
+    if (clip) clip8<T>(gf, coef);
+    if (zero_g) {
+      if (full) zero8<T>(g + e0);
+      else
+        for (int i = 0; i < 8 && e0 + i < n; ++i) g[e0 + i] = DT<T>::from_f(0.f);
     }
     float uf[8];
     if (vote == DLION_VOTE_AVERAGE) {
@@ -173,19 +222,29 @@ __global__ void __launch_bounds__(kThreads) vote_update_kernel(T* __restrict__ p
 
 using namespace dlion;
 
-extern "C" int dlion_lion_local_sr(void* p, const void* g, void* m, int64_t n, int dtype, float lr, float decay,
-                                   float beta1, float omb1, float beta2, float omb2, uint64_t sr_key,
-                                   int64_t elem_base, void* stream) {
+extern "C" int dlion_lion_local_clip(void* p, void* g, void* m, int64_t n, int dtype, float lr, float decay,
+                                     float beta1, float omb1, float beta2, float omb2, uint64_t sr_key,
+                                     int64_t elem_base, const float* clip_sumsq, float clip_max_norm, int zero_g,
+                                     void* stream) {
   DLION_CHECK_ARG(n >= 0, "dlion_lion_local: negative n");
+  DLION_CHECK_ARG(clip_sumsq == nullptr || clip_max_norm > 0.f, "dlion_lion_local: clip_max_norm must be positive");
   DLION_CHECK_ARG(elem_base >= 0 && (elem_base & 7) == 0, "dlion_lion_local: elem_base must be a multiple of 8");
   if (n == 0) return 0;
   DLION_CHECK_ARG(aligned16(p) && aligned16(g) && aligned16(m), "dlion_lion_local: pointers must be 16-byte aligned");
   cudaStream_t s = (cudaStream_t)stream;
   const int grid = grid_for(n >> 3);
-  DISPATCH_DTYPE(dtype, lion_local_kernel<T><<<grid, kThreads, 0, s>>>((T*)p, (const T*)g, (T*)m, n, lr, decay,
-                                                                         beta1, omb1, beta2, omb2, sr_key,
-                                                                         elem_base >> 3));
+  const ClipArg ca{clip_sumsq, clip_max_norm};
+  DISPATCH_DTYPE(dtype, lion_local_kernel<T><<<grid, kThreads, 0, s>>>((T*)p, (T*)g, (T*)m, n, lr, decay, beta1, omb1,
+                                                                         beta2, omb2, sr_key, elem_base >> 3, ca,
+                                                                         zero_g));
   return DLION_LAUNCH_CHECK("dlion_lion_local");
+}
+
+extern "C" int dlion_lion_local_sr(void* p, const void* g, void* m, int64_t n, int dtype, float lr, float decay,
+                                   float beta1, float omb1, float beta2, float omb2, uint64_t sr_key,
+                                   int64_t elem_base, void* stream) {
+  return dlion_lion_local_clip(p, const_cast<void*>(g), m, n, dtype, lr, decay, beta1, omb1, beta2, omb2, sr_key,
+                               elem_base, nullptr, 0.f, 0, stream);
 }
 
 extern "C" int dlion_lion_local(void* p, const void* g, void* m, int64_t n, int dtype, float lr, float decay,
@@ -193,22 +252,32 @@ extern "C" int dlion_lion_local(void* p, const void* g, void* m, int64_t n, int 
   return dlion_lion_local_sr(p, g, m, n, dtype, lr, decay, beta1, omb1, beta2, omb2, 0, 0, stream);
 }
 
-extern "C" int dlion_sign_pack(const void* m, const void* g, uint32_t* words, int64_t n, int dtype, float beta1,
-                               float omb1, float stoch_r, uint64_t seed, uint32_t step, uint32_t rank, void* stream) {
+extern "C" int dlion_sign_pack_clip(const void* m, const void* g, uint32_t* words, int64_t n, int dtype, float beta1,
+                                    float omb1, float stoch_r, uint64_t seed, uint32_t step, uint32_t rank,
+                                    const float* clip_sumsq, float clip_max_norm, void* stream) {
   DLION_CHECK_ARG(n >= 0, "dlion_sign_pack: negative n");
+  DLION_CHECK_ARG(clip_sumsq == nullptr || clip_max_norm > 0.f, "dlion_sign_pack: clip_max_norm must be positive");
   if (n == 0) return 0;
   DLION_CHECK_ARG(aligned16(g) && aligned16(m), "dlion_sign_pack: pointers must be 16-byte aligned");
   cudaStream_t s = (cudaStream_t)stream;
   const int grid = grid_for(((n + 31) >> 5) << 2);
+  const ClipArg ca{clip_sumsq, clip_max_norm};
   DISPATCH_DTYPE(dtype, sign_pack_kernel<T><<<grid, kThreads, 0, s>>>((const T*)m, (const T*)g, words, n, beta1, omb1,
-                                                                        stoch_r, seed, step, rank));
+                                                                        stoch_r, seed, step, rank, ca));
   return DLION_LAUNCH_CHECK("dlion_sign_pack");
 }
 
-extern "C" int dlion_vote_update_sr(void* p, const void* g, void* m, const uint32_t* gathered, int64_t row_words,
-                                    int world, uint32_t live_mask, int64_t n, int dtype, float lr, float decay,
-                                    float beta2, float omb2, int vote, uint64_t sr_key, void* stream) {
+extern "C" int dlion_sign_pack(const void* m, const void* g, uint32_t* words, int64_t n, int dtype, float beta1,
+                               float omb1, float stoch_r, uint64_t seed, uint32_t step, uint32_t rank, void* stream) {
+  return dlion_sign_pack_clip(m, g, words, n, dtype, beta1, omb1, stoch_r, seed, step, rank, nullptr, 0.f, stream);
+}
+
+extern "C" int dlion_vote_update_clip(void* p, void* g, void* m, const uint32_t* gathered, int64_t row_words,
+                                      int world, uint32_t live_mask, int64_t n, int dtype, float lr, float decay,
+                                      float beta2, float omb2, int vote, uint64_t sr_key, const float* clip_sumsq,
+                                      float clip_max_norm, int zero_g, void* stream) {
   DLION_CHECK_ARG(n >= 0, "dlion_vote_update: negative n");
+  DLION_CHECK_ARG(clip_sumsq == nullptr || clip_max_norm > 0.f, "dlion_vote_update: clip_max_norm must be positive");
   DLION_CHECK_ARG(world >= 1 && world <= DLION_MAX_RANKS, "dlion_vote_update: world %d outside [1, %d]", world,
                   DLION_MAX_RANKS);
   DLION_CHECK_ARG(vote >= 0 && vote <= 2, "dlion_vote_update: bad vote rule %d", vote);
@@ -222,10 +291,18 @@ extern "C" int dlion_vote_update_sr(void* p, const void* g, void* m, const uint3
   DLION_CHECK_ARG(aligned16(p) && aligned16(g) && aligned16(m), "dlion_vote_update: pointers must be 16-byte aligned");
   cudaStream_t s = (cudaStream_t)stream;
   const int grid = grid_for((n + 7) >> 3);
+  const ClipArg ca{clip_sumsq, clip_max_norm};
   DISPATCH_DTYPE(dtype, vote_update_kernel<T><<<grid, kThreads, 0, s>>>(
-                            (T*)p, (const T*)g, (T*)m, (const uint8_t*)gathered, row_words * 4, world, live_mask, L, n,
-                            lr, decay, beta2, omb2, vote, sr_key));
+                            (T*)p, (T*)g, (T*)m, (const uint8_t*)gathered, row_words * 4, world, live_mask, L, n, lr,
+                            decay, beta2, omb2, vote, sr_key, ca, zero_g));
   return DLION_LAUNCH_CHECK("dlion_vote_update");
+}
+
+extern "C" int dlion_vote_update_sr(void* p, const void* g, void* m, const uint32_t* gathered, int64_t row_words,
+                                    int world, uint32_t live_mask, int64_t n, int dtype, float lr, float decay,
+                                    float beta2, float omb2, int vote, uint64_t sr_key, void* stream) {
+  return dlion_vote_update_clip(p, const_cast<void*>(g), m, gathered, row_words, world, live_mask, n, dtype, lr, decay,
+                                beta2, omb2, vote, sr_key, nullptr, 0.f, 0, stream);
 }
 
 extern "C" int dlion_vote_update(void* p, const void* g, void* m, const uint32_t* gathered, int64_t row_words,

@@ -15,6 +15,14 @@
 // is hidden by distance, not by shared-memory capacity.  HBM traffic is the minimum: read g, m,
 // p once, write m, p once (10 B/param in bf16) + W/8 B/param of gathered words.
 //
+// Two things a training step needs next to the update are folded into the same pass instead of being
+// kernels of their own (reference: HF Trainer's clip_grad_norm_ before optimizer.step() and
+// model.zero_grad() after it, run_clm.py:588-622 via transformers.Trainer):
+//   clip     `clip_sumsq` points at the device-side sum of g^2; g' = round_T(g * coef) is formed in
+//            registers exactly where a separate clip kernel would round it, and feeds sign and momentum;
+//   zero     `zero_g`: each consumed g tile is overwritten with zeros by ONE cp.async.bulk
+//            shared->global copy from a zero page in shared memory (no thread stores anything).
+//
 // Warp roles (24 warps, 1 CTA per SM; every compute role has 2 warps per SM sub-partition):
 //   0      P-loader   one lane: cp.async.bulk (TMA 1-D) of g, m tiles into a 6-stage smem ring
 //   1      C-loader   one lane: cp.async.bulk of p tiles into an 8-stage smem ring
@@ -86,6 +94,9 @@ struct FusedParams {
   int32_t* status;
   int64_t spin_limit;
   uint64_t sr_key;
+  const float* clip_sumsq;
+  float clip_max_norm;
+  int zero_g;
 };
 
 // ------------------------------------------------------------------ PTX helpers
@@ -132,8 +143,20 @@ __device__ __forceinline__ void bulk_load(uint32_t dst_smem, const void* src, ui
                "l"(src), "r"(bytes), "r"(bar)
                : "memory");
 }
+// TMA 1-D bulk copy shared -> global (bulk async-group completion)
+__device__ __forceinline__ void bulk_store(void* dst, uint32_t src_smem, uint32_t bytes) {
+  asm volatile("cp.async.bulk.global.shared::cta.bulk_group [%0], [%1], %2;" ::"l"(dst), "r"(src_smem), "r"(bytes)
+               : "memory");
+}
+__device__ __forceinline__ void bulk_commit() { asm volatile("cp.async.bulk.commit_group;" ::: "memory"); }
+__device__ __forceinline__ void bulk_wait_all() { asm volatile("cp.async.bulk.wait_group 0;" ::: "memory"); }
 __device__ __forceinline__ void st_relaxed_sys(uint64_t* ptr, uint64_t v) {
   asm volatile("st.relaxed.sys.global.u64 [%0], %1;" ::"l"(ptr), "l"(v) : "memory");
+}
+__device__ __forceinline__ uint64_t ld_relaxed_sys(const uint64_t* ptr) {
+  uint64_t v;
+  asm volatile("ld.relaxed.sys.global.u64 %0, [%1];" : "=l"(v) : "l"(ptr) : "memory");
+  return v;
 }
 __device__ __forceinline__ uint64_t ld_acquire_sys(const uint64_t* ptr) {
   uint64_t v;
@@ -175,7 +198,8 @@ struct Cfg {
   static constexpr int OFF_BARS = OFF_PLANES + kCStages * 5 * PLANE_BYTES;
   static constexpr int NUM_BARS = 2 * kPStages + 3 * kCStages;
   static constexpr int OFF_CTRS = OFF_BARS + NUM_BARS * 8;
-  static constexpr int SMEM_TOTAL = OFF_CTRS + 64;
+  static constexpr int OFF_ZERO = (OFF_CTRS + 64 + 127) / 128 * 128;   // zero page: source of the g zero-fill
+  static constexpr int SMEM_TOTAL = OFF_ZERO + kArrayBytes;
 };
 
 template <int N> struct VecOf;
@@ -250,8 +274,12 @@ __global__ void __launch_bounds__(kFusedThreads, 1) lion_fused_kernel(const __gr
     *words_done = 0u;
     for (int s = 0; s < kSenders; ++s) sent[s] = 0u;
     asm volatile("fence.mbarrier_init.release.cluster;" ::: "memory");
-    asm volatile("fence.proxy.async.shared::cta;" ::: "memory");
   }
+  if (P.zero_g) {
+    uint4* z = reinterpret_cast<uint4*>(smem + C::OFF_ZERO);
+    for (int i = threadIdx.x; i < kArrayBytes / 16; i += kFusedThreads) z[i] = make_uint4(0u, 0u, 0u, 0u);
+  }
+  asm volatile("fence.proxy.async.shared::cta;" ::: "memory");   // generic-proxy smem writes -> visible to TMA
   __syncthreads();
   if (n_my == 0) return;
 
@@ -298,15 +326,18 @@ __global__ void __launch_bounds__(kFusedThreads, 1) lion_fused_kernel(const __gr
       if (k > 0) mbar_wait(smem_u32(emptyC + slot), (uint32_t)((k - 1) & 1), P.status, 2);
       const uint64_t target = epoch_hi | (uint64_t)(i + 1);
       if (waits && !gave_up && seen < target) {
+        // poll with relaxed loads (no L1 invalidate per poll), back off, and pay ONE acquire once the
+        // counter is there: everything the sender stored before its release is then visible
         int64_t it = 0;
-        while ((seen = ld_acquire_sys(f)) < target) {
+        while (ld_relaxed_sys(f) < target) {
           if (++it > spin_limit) {
             report(P.status, 1, cta, lane);
             gave_up = true;
             break;
           }
-          __nanosleep(40);
+          __nanosleep(it < 4 ? 32 : 128);
         }
+        if (!gave_up) seen = ld_acquire_sys(f);
       }
       gave_up = __any_sync(0xffffffffu, gave_up);   // also orders every lane after the acquires
       const int64_t woff = ((int64_t)cta + (int64_t)i * G) * C::WORDS + lane * C::WPL;
@@ -406,6 +437,17 @@ __global__ void __launch_bounds__(kFusedThreads, 1) lion_fused_kernel(const __gr
   } else if (warp < kWarpC0) {
     // ============================ P-compute ============================
     const int pt = threadIdx.x - kWarpP0 * 32;
+    // gradient clipping folded in: the coefficient torch.nn.utils.clip_grad_norm_ would apply
+    float coef = 1.f;
+    bool clip = false;
+    if (P.clip_sumsq != nullptr) {
+      const float c = P.clip_max_norm / (sqrtf(__ldg(P.clip_sumsq)) + 1e-6f);
+      if (c < 1.0f) {          // also false for a NaN norm: leave the gradients alone
+        coef = c;
+        clip = true;
+      }
+    }
+    const uint32_t zero_page = smem_u32(smem + C::OFF_ZERO);
     for (int i = 0; i < n_my; ++i) {
       const int slot = i % kPStages, k = i / kPStages;
       if (i >= kWordRing) {                           // ring capacity: tile i-kWordRing must have left
@@ -430,12 +472,21 @@ __global__ void __launch_bounds__(kFusedThreads, 1) lion_fused_kernel(const __gr
       const T* sm = reinterpret_cast<const T*>(pring + slot * kPStageBytes + kArrayBytes);
       const int64_t tile = (int64_t)cta + (int64_t)i * G;
       uint32_t* wb = wring + (i % kWordRing) * C::WORDS;
+      if (P.zero_g && pt == 0) {                     // the tile's g is in shared memory: clear it in HBM
+        bulk_store(const_cast<T*>(g) + tile * C::TILE, zero_page, kArrayBytes);
+        bulk_commit();
+      }
 #pragma unroll
       for (int u = 0; u < C::UPT_P; ++u) {
         const int unit = pt + u * kPThreads;
         float gf[8], mf[8];
         load8<T>(sg + unit * 8, gf);
         load8<T>(sm + unit * 8, mf);
+        if (clip) {
+#pragma unroll
+          for (int e = 0; e < 8; ++e) gf[e] *= coef;
+          round8<T>(gf);                             // a separate clip kernel would round through T here
+        }
         const uint32_t byte = sign_byte<T>(mf, gf, P.beta1, P.omb1, P.stoch_r, P.seed, P.step, (uint32_t)my_rank,
                                            P.elem_base + tile * C::TILE + unit * 8);
         uint32_t wv = byte << (8 * (lane & 3));
@@ -450,6 +501,7 @@ __global__ void __launch_bounds__(kFusedThreads, 1) lion_fused_kernel(const __gr
       named_bar_sync(1, kPThreads);                  // every word of tile i is in the ring
       if (pt == 0) st_release_cta(words_done, (uint32_t)(i + 1));
     }
+    if (P.zero_g && pt == 0) bulk_wait_all();        // the zero page must outlive every copy that reads it
   } else {
     // ============================ C-compute ============================
     const int ct = threadIdx.x - kWarpC0 * 32;
@@ -553,6 +605,8 @@ static int launch_fused(const dlion_fused_args* a, cudaStream_t s) {
   P.mc_arena = a->emulate_ranks > 0 ? nullptr : a->mc_arena;
   P.arena_words = a->arena_words; P.grid = a->grid; P.emulate_ranks = a->emulate_ranks; P.emu_stride = a->emu_stride;
   P.status = a->status; P.spin_limit = a->spin_limit; P.sr_key = a->sr_key;
+  P.clip_sumsq = a->clip_sumsq; P.clip_max_norm = a->clip_max_norm; P.zero_g = a->zero_g;
+  DLION_CHECK_ARG(a->clip_sumsq == nullptr || a->clip_max_norm > 0.f, "dlion_fused_step: clip_max_norm must be positive");
   void* kargs[] = {(void*)&P};
   return check_cuda(cudaLaunchCooperativeKernel((void*)lion_fused_kernel<T>, dim3(a->grid * vr), dim3(kFusedThreads),
                                                 kargs, (size_t)C::SMEM_TOTAL, s),

@@ -30,3 +30,12 @@ def require_library() -> bool:
 
 def library_loaded() -> bool:
     return _cabi._LIB is not None
+
+
+def mark_grad_written(param) -> None:
+    """Record that a backward pass produced a gradient for ``param`` in this step.  Autograd calls it through a
+    post-accumulate hook; the custom backward functions that add into ``param.grad`` themselves (GEMM-epilogue
+    weight gradients, the one-launch bias / LayerNorm reductions, the chunked cross-entropy) call it directly,
+    because they hand autograd ``None`` and no hook fires.  ``Lion.step`` consumes the marks
+    (reference: ``if p.grad is not None`` at distributed_lion.py:180)."""
+    param._dlion_touched = True

@@ -35,6 +35,7 @@ class FusedArgs(C.Structure):
         ("arena", C.c_void_p * MAX_RANKS), ("flags", C.c_void_p * MAX_RANKS), ("mc_arena", C.c_void_p),
         ("arena_words", C.c_int64), ("grid", C.c_int), ("emulate_ranks", C.c_int),
         ("emu_stride", C.c_int64), ("status", C.c_void_p), ("spin_limit", C.c_int64), ("sr_key", C.c_uint64),
+        ("clip_sumsq", C.c_void_p), ("clip_max_norm", C.c_float), ("zero_g", C.c_int),
     ]
 
 
@@ -74,6 +75,9 @@ def _declare(L: C.CDLL) -> None:
         "dlion_device_sm_count": [C.POINTER(i32)],
         "dlion_lion_local": [vp, vp, vp, i64, i32, f32, f32, f32, f32, f32, f32, vp],
         "dlion_lion_local_sr": [vp, vp, vp, i64, i32, f32, f32, f32, f32, f32, f32, u64, i64, vp],
+        "dlion_lion_local_clip": [vp, vp, vp, i64, i32, f32, f32, f32, f32, f32, f32, u64, i64, vp, f32, i32, vp],
+        "dlion_sign_pack_clip": [vp, vp, vp, i64, i32, f32, f32, f32, u64, u32, u32, vp, f32, vp],
+        "dlion_vote_update_clip": [vp, vp, vp, vp, i64, i32, u32, i64, i32, f32, f32, f32, f32, i32, u64, vp, f32, i32, vp],
         "dlion_sign_pack": [vp, vp, vp, i64, i32, f32, f32, f32, u64, u32, u32, vp],
         "dlion_vote_update": [vp, vp, vp, vp, i64, i32, u32, i64, i32, f32, f32, f32, f32, i32, vp],
         "dlion_vote_update_sr": [vp, vp, vp, vp, i64, i32, u32, i64, i32, f32, f32, f32, f32, i32, u64, vp],

@@ -4,7 +4,9 @@
 over non-ignored tokens).  The token dimension is tiled; per tile: one cuBLAS GEMM makes a
 bf16 logits block, the CE kernel (csrc/cross_entropy.cu) turns it into per-row losses and, in
 place, into d loss / d logits; two more GEMMs fold that block into dh and dW straight away
-(the gradient is produced during the forward, as the loss is always the last node).
+(the gradient is produced during the forward, as the loss is always the last node).  Only the
+row *stride* of the block is padded (16-byte rows for the kernel); the GEMMs address the first V
+columns through a strided view, so the LM-head weight is never copied or padded.
 
 ``linear_log_probs(h, weight, labels)`` returns per-token log-probabilities (for DPO); its
 backward recomputes each logits block and applies the per-row upstream gradient in the kernel.
@@ -27,16 +29,30 @@ IGNORE_INDEX = -100
 _DEFAULT_CHUNK = int(os.environ.get("DLION_CE_CHUNK", "4096"))   # rows of logits alive at a time
 
 
-def _pad_rows(weight: torch.Tensor, mult: int = 64) -> torch.Tensor:
-    """[V, H] -> [Vp, H] with zero rows so every logits row is 16-byte aligned and the GEMMs
-    see friendly leading dimensions; ``wp[:V]`` is a contiguous prefix view."""
-    V = weight.shape[0]
-    Vp = (V + mult - 1) // mult * mult
-    if Vp == V:
-        return weight
-    wp = weight.new_zeros(Vp, weight.shape[1])
-    wp[:V].copy_(weight)
-    return wp
+def _padded_vocab(V: int, mult: int = 64) -> int:
+    """Row stride of a logits block: the vocabulary rounded up so that every row starts 16-byte aligned (the CE
+    kernel's vector accesses) — only the *stride* is padded; the GEMMs read and write the first V columns of each
+    row through a strided view (cuBLAS takes a leading dimension), so the LM-head weight is never copied."""
+    return (V + mult - 1) // mult * mult
+
+
+def _logits_block(hc: torch.Tensor, w: torch.Tensor, Vp: int):
+    """[c, H] x [V, H]^T -> (buffer [c, Vp], view [c, V]); the pad columns are never read as logits."""
+    V = w.shape[0]
+    buf = torch.empty(hc.shape[0], Vp, dtype=hc.dtype, device=hc.device)
+    view = buf[:, :V] if Vp != V else buf
+    torch.mm(hc, w.t(), out=view)
+    return buf, view
+
+
+def _compute_dtype(h: torch.Tensor) -> torch.dtype:
+    """The dtype the logits GEMMs run in: the autocast dtype when autocast is on (mixed-precision training of fp32
+    master weights: ``Trainer.autocast`` for ``--bf16`` / ``--fp16`` without ``--torch_dtype``), else h's own."""
+    if h.is_cuda and torch.is_autocast_enabled("cuda"):
+        return torch.get_autocast_dtype("cuda")
+    if not h.is_cuda and _EMULATE and torch.is_autocast_enabled("cpu"):
+        return torch.get_autocast_dtype("cpu")
+    return h.dtype
 
 
 _EMULATE = os.environ.get("DLION_EMULATE_KERNELS") == "1"   # CPU stand-ins, to test the autograd plumbing
@@ -81,41 +97,53 @@ def _device_guard(t: torch.Tensor):
     return torch.cuda.device(t.device) if t.is_cuda else contextlib.nullcontext()
 
 
+def _no_autocast(t: torch.Tensor):
+    return torch.autocast(t.device.type, enabled=False)
+
+
 class _LinearCE(torch.autograd.Function):
+    """The body runs with autocast OFF on operands cast once to the compute dtype: ``out=`` / in-place GEMMs are not
+    autocast-aware, so under autocast bf16 logits would otherwise meet fp32 weights."""
+
     @staticmethod
     def forward(ctx, h, weight, labels, ignore_index: int, chunk: int):
         N, H = h.shape
         V = weight.shape[0]
-        wp = _pad_rows(weight)
-        Vp = wp.shape[0]
+        cd = _compute_dtype(h)
+        hq = h if h.dtype == cd else h.to(cd)
+        wq = weight if weight.dtype == cd else weight.to(cd)
+        Vp = _padded_vocab(V)
         losses = torch.empty(N, dtype=torch.float32, device=h.device)
         n_valid = (labels != ignore_index).sum().clamp_(min=1).to(torch.float32)
         need_grad = ctx.needs_input_grad[0] or ctx.needs_input_grad[1]
-        dh = torch.empty_like(h) if need_grad else None
-        dwp = torch.zeros_like(wp) if need_grad else None
-        with _device_guard(h):
+        dh = torch.empty_like(hq) if need_grad else None
+        # dW accumulates in the weight's own dtype: fp32 master weights get an fp32 accumulator
+        dw = torch.zeros_like(weight) if need_grad else None
+        with _device_guard(h), _no_autocast(h):
             for s in range(0, N, chunk):
                 e = min(N, s + chunk)
-                hc = h[s:e]
-                logits = hc @ wp.t()                                   # [c, Vp]
-                _ce_kernel(logits, labels[s:e], losses[s:e], V, ignore_index, need_grad)
+                hc = hq[s:e]
+                buf, logits = _logits_block(hc, wq, Vp)                # [c, V] view of a [c, Vp] buffer
+                _ce_kernel(buf, labels[s:e], losses[s:e], V, ignore_index, need_grad)
                 if need_grad:
-                    torch.mm(logits, wp, out=dh[s:e])                  # d h   (unscaled)
-                    dwp.addmm_(logits.t(), hc)                         # d W   (unscaled)
+                    torch.mm(logits, wq, out=dh[s:e])                  # d h   (unscaled)
+                    if dw.dtype == cd:
+                        dw.addmm_(logits.t(), hc)                      # d W   (unscaled), beta = 1 epilogue
+                    else:
+                        dw.add_(logits.t() @ hc)
         loss = losses.sum() / n_valid
         if need_grad:
-            ctx.save_for_backward(dh, dwp, n_valid)
-            ctx.V = V
+            ctx.save_for_backward(dh, dw, n_valid)
+            ctx.h_dtype = h.dtype
         return loss
 
     @staticmethod
     def backward(ctx, grad_out):
-        dh, dwp, n_valid = ctx.saved_tensors
+        dh, dw, n_valid = ctx.saved_tensors
         scale = (grad_out.float() / n_valid)
         dh.mul_(scale.to(dh.dtype))
-        dw = dwp[:ctx.V]
         dw.mul_(scale.to(dw.dtype))
-        return dh, dw, None, None, None
+        return (dh if dh.dtype == ctx.h_dtype else dh.to(ctx.h_dtype)), dw, None, None, None
 
 
 class _LinearLogProbs(torch.autograd.Function):
@@ -123,16 +151,18 @@ class _LinearLogProbs(torch.autograd.Function):
     def forward(ctx, h, weight, labels, ignore_index: int, chunk: int):
         N, H = h.shape
         V = weight.shape[0]
-        wp = _pad_rows(weight)
-        Vp = wp.shape[0]
+        cd = _compute_dtype(h)
+        hq = h if h.dtype == cd else h.to(cd)
+        wq = weight if weight.dtype == cd else weight.to(cd)
+        Vp = _padded_vocab(V)
         losses = torch.empty(N, dtype=torch.float32, device=h.device)
-        with _device_guard(h):
+        with _device_guard(h), _no_autocast(h):
             for s in range(0, N, chunk):
                 e = min(N, s + chunk)
-                logits = h[s:e] @ wp.t()
-                _ce_kernel(logits, labels[s:e], losses[s:e], V, ignore_index, False)
+                buf, _ = _logits_block(hq[s:e], wq, Vp)
+                _ce_kernel(buf, labels[s:e], losses[s:e], V, ignore_index, False)
         ctx.save_for_backward(h, weight, labels)
-        ctx.ignore_index, ctx.chunk = ignore_index, chunk
+        ctx.ignore_index, ctx.chunk, ctx.cd = ignore_index, chunk, cd
         return -losses
 
     @staticmethod
@@ -140,21 +170,26 @@ class _LinearLogProbs(torch.autograd.Function):
         h, weight, labels = ctx.saved_tensors
         N, H = h.shape
         V = weight.shape[0]
-        wp = _pad_rows(weight)
-        Vp = wp.shape[0]
-        dh = torch.empty_like(h)
-        dwp = torch.zeros_like(wp)
+        cd = ctx.cd
+        hq = h if h.dtype == cd else h.to(cd)
+        wq = weight if weight.dtype == cd else weight.to(cd)
+        Vp = _padded_vocab(V)
+        dh = torch.empty_like(hq)
+        dw = torch.zeros_like(weight)
         # logp = -ce  =>  d logits = (softmax - onehot) * (-grad_logp)
         row_scale = (-grad_logp).float().contiguous()
-        with _device_guard(h):
+        with _device_guard(h), _no_autocast(h):
             for s in range(0, N, ctx.chunk):
                 e = min(N, s + ctx.chunk)
-                hc = h[s:e]
-                logits = hc @ wp.t()
-                _ce_kernel(logits, labels[s:e], None, V, ctx.ignore_index, False, row_scale=row_scale[s:e])
-                torch.mm(logits, wp, out=dh[s:e])
-                dwp.addmm_(logits.t(), hc)
-        return dh, dwp[:V], None, None, None
+                hc = hq[s:e]
+                buf, logits = _logits_block(hc, wq, Vp)
+                _ce_kernel(buf, labels[s:e], None, V, ctx.ignore_index, False, row_scale=row_scale[s:e])
+                torch.mm(logits, wq, out=dh[s:e])
+                if dw.dtype == cd:
+                    dw.addmm_(logits.t(), hc)
+                else:
+                    dw.add_(logits.t() @ hc)
+        return (dh if dh.dtype == h.dtype else dh.to(h.dtype)), dw, None, None, None
 
 
 def linear_cross_entropy(h: torch.Tensor, weight: torch.Tensor, labels: torch.Tensor,

@@ -15,7 +15,7 @@ from typing import Optional
 
 import torch
 
-from . import _cabi, require_library
+from . import _cabi, mark_grad_written, require_library
 
 _FUSE_WGRAD = os.environ.get("DLION_FUSE_WGRAD", "1") == "1"
 _FUSE_COLSUM = os.environ.get("DLION_FUSE_COLSUM", "1") == "1"
@@ -75,6 +75,7 @@ def bias_grad(dy2: torch.Tensor, bias: torch.Tensor):
     """Gradient of a bias added to every row of the tensor whose gradient is ``dy2``: accumulated straight into
     ``bias.grad`` when that buffer exists (returns ``None``), returned otherwise."""
     if _can_accumulate(bias, dy2) and bias.grad.shape == (dy2.shape[1],):
+        mark_grad_written(bias)
         return column_sum(dy2, bias.dtype, accumulate_into=bias.grad)
     return column_sum(dy2, bias.dtype)
 
@@ -116,6 +117,7 @@ class _FusedLinear(torch.autograd.Function):
             dx = (dy2 @ (weight.t() if ctx.in_out else weight)).view(ctx.x_shape)
         if ctx.needs_input_grad[1]:
             if _can_accumulate(weight, dy2):
+                mark_grad_written(weight)
                 if ctx.in_out:
                     weight.grad.addmm_(x2.t(), dy2)          # dW += x^T dy, accumulated in the GEMM epilogue
                 else:

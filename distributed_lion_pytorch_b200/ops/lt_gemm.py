@@ -118,6 +118,8 @@ class _LinearGelu(torch.autograd.Function):
             dx = (dpre @ weight.t()).view(ctx.x_shape)
         if ctx.needs_input_grad[1]:
             if _can_accumulate(weight, dpre):
+                from . import mark_grad_written
+                mark_grad_written(weight)
                 weight.grad.addmm_(x2.t(), dpre)
             else:
                 dw = x2.t() @ dpre

@@ -64,6 +64,11 @@ class _FusedNorm(torch.autograd.Function):
         from .linear import _can_accumulate
         acc_w = ctx.needs_input_grad[2] and _can_accumulate(weight, weight)
         acc_b = ctx.has_bias and ctx.needs_input_grad[3] and _can_accumulate(bias, bias)
+        from . import mark_grad_written
+        if acc_w:
+            mark_grad_written(weight)
+        if acc_b:
+            mark_grad_written(bias)
         dw = weight.grad if acc_w else torch.empty_like(weight)
         db = (bias.grad if acc_b else torch.empty_like(weight)) if ctx.has_bias else None
         with torch.cuda.device(dy.device):

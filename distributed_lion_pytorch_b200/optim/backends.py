@@ -39,7 +39,11 @@ class _Backend:
     def _use_kernels(self, b: Bucket) -> bool:
         return self.opt._kernels_ok(b.device)
 
-    def step(self, b: Bucket, lr: float, wd: float, beta1: float, beta2: float, missing: List[int]) -> None:
+    def step(self, b: Bucket, lr: float, wd: float, beta1: float, beta2: float, missing: List[int],
+             clip=None, zero_g: bool = False) -> bool:
+        """One optimizer step on bucket ``b``.  ``clip=(sumsq_dev, max_norm)`` is the gradient clip to fold into the
+        kernels, ``zero_g`` asks them to clear the gradient bucket once consumed.  Returns True when the gradient
+        bucket was left zeroed (only kernel paths do that; the caller then skips its memset)."""
         raise NotImplementedError
 
 
@@ -47,9 +51,10 @@ class LocalBackend(_Backend):
     """Single-worker Lion (reference: distributed_lion.py:47-59)."""
     name = "local"
 
-    def step(self, b, lr, wd, beta1, beta2, missing):
+    def step(self, b, lr, wd, beta1, beta2, missing, clip=None, zero_g=False):
         if missing:
             # reference semantics: a parameter without a gradient is left untouched this step
+            # (distributed_lion.py:180) — no decay, no momentum decay, no sign(beta1*m) move
             skip = set(missing)
             spans = [(pv, gv, mv, off) for i, (pv, gv, mv, off) in
                      enumerate(zip(b.p_views, b.g_views, b.m_views, b.offsets)) if i not in skip]
@@ -59,10 +64,13 @@ class LocalBackend(_Backend):
         if self._use_kernels(b):
             from ..ops import lion_ops
             for p, g, m, off in spans:
-                lion_ops.local_step(p, g, m, lr, wd, beta1, beta2, sr_key=key, elem_base=off)
-        else:
-            for p, g, m, off in spans:
-                sem.local_lion_step_(p.view(-1), g.view(-1), m.view(-1), lr, wd, beta1, beta2, sr_key=key, elem_base=off)
+                lion_ops.local_step(p.view(-1), g.view(-1), m.view(-1), lr, wd, beta1, beta2, sr_key=key, elem_base=off,
+                                    clip=clip, zero_g=zero_g)
+            return bool(zero_g)      # skipped spans hold no gradient: the whole bucket is clean
+        assert clip is None, "the eager path clips eagerly (Lion.clip_grad_norm_)"
+        for p, g, m, off in spans:
+            sem.local_lion_step_(p.view(-1), g.view(-1), m.view(-1), lr, wd, beta1, beta2, sr_key=key, elem_base=off)
+        return False
 
 
 class AllGatherBackend(_Backend):
@@ -88,15 +96,20 @@ class AllGatherBackend(_Backend):
             chunks = list(out.unbind(0))
             dist.all_gather(chunks, inp, group=pg)
 
-    def step(self, b, lr, wd, beta1, beta2, missing):
+    def step(self, b, lr, wd, beta1, beta2, missing, clip=None, zero_g=False):
         opt = self.opt
         W = self.world_size
         mine, gathered = self._wire(b)
-        kern = self._use_kernels(b)
+        # the vote kernels count ballots in 5 bit planes (<= DLION_MAX_RANKS workers); larger jobs — which the
+        # reference's all_gather path supports — take the torch / cpu_ops vote path below
+        from ..ops import _cabi
+        kern = self._use_kernels(b) and W <= _cabi.MAX_RANKS
+        if clip is not None and not kern:
+            raise RuntimeError("a folded gradient clip needs the kernel path (Lion.clip_grad_norm_ decides this)")
         if kern:
             from ..ops import lion_ops
             lion_ops.sign_pack(b.flat_m, b.flat_g, beta1, mine, max_grad_norm=opt.max_grad_norm,
-                               seed=opt.seed, step=opt._steps_done, rank=opt.rank)
+                               seed=opt.seed, step=opt._steps_done, rank=opt.rank, clip=clip)
         else:
             gen = opt.cpu_generator() if opt.max_grad_norm is not None else None
             from ..ops import cpu_ops
@@ -106,11 +119,15 @@ class AllGatherBackend(_Backend):
         L = opt.live_count()
         if kern:
             lion_ops.vote_update(b.flat_p, b.flat_g, b.flat_m, gathered, W, opt.live_mask, lr, wd, beta2,
-                                 opt.vote, opt.tie, sr_key=opt.sr_key())
+                                 opt.vote, opt.tie, sr_key=opt.sr_key(), clip=clip, zero_g=zero_g)
+            return bool(zero_g)
+        if b.device.type == "cuda":
+            cnt = sem.count_votes(gathered, b.numel, opt.live_mask)
         else:
             from ..ops import cpu_ops
             cnt = cpu_ops.count_votes(gathered, b.numel, opt.live_mask)
-            sem.apply_vote_(b.flat_p, b.flat_g, b.flat_m, cnt, L, lr, wd, beta2, opt.vote, opt.tie, sr_key=opt.sr_key())
+        sem.apply_vote_(b.flat_p, b.flat_g, b.flat_m, cnt, L, lr, wd, beta2, opt.vote, opt.tie, sr_key=opt.sr_key())
+        return False
 
 
 class FusedBackend(_Backend):
@@ -147,7 +164,7 @@ class FusedBackend(_Backend):
         logging.getLogger("dlion.lion").warning("fused NVLink exchange unavailable (%s); using nccl_1bit", err)
         return False
 
-    def step(self, b, lr, wd, beta1, beta2, missing):
+    def step(self, b, lr, wd, beta1, beta2, missing, clip=None, zero_g=False):
         opt = self.opt
         if b.device.type != "cuda":
             raise RuntimeError("comm='fused' needs CUDA tensors; use comm='nccl_1bit' on CPU")
@@ -155,9 +172,11 @@ class FusedBackend(_Backend):
             # peer mapping is unavailable on at least one rank: every rank switches to the split path
             fallback = AllGatherBackend(opt)
             opt._backend = fallback
-            return fallback.step(b, lr, wd, beta1, beta2, missing)
+            return fallback.step(b, lr, wd, beta1, beta2, missing, clip=clip, zero_g=zero_g)
         self._ctx.step(b, lr, wd, beta1, beta2, vote=opt.vote, tie=opt.tie, live_mask=opt.live_mask,
-                       max_grad_norm=opt.max_grad_norm, seed=opt.seed, step_index=opt._steps_done, sr_key=opt.sr_key())
+                       max_grad_norm=opt.max_grad_norm, seed=opt.seed, step_index=opt._steps_done, sr_key=opt.sr_key(),
+                       clip=clip, zero_g=zero_g, wait_mask=opt.wait_mask)
+        return bool(zero_g)
 
 
 def pick_auto(opt) -> _Backend:

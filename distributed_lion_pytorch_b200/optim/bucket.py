@@ -92,20 +92,30 @@ def build_bucket(group_index: int, params: List[torch.nn.Parameter], state: dict
     return b
 
 
-def gather_grads(b: Bucket, *, use_kernel: bool = True):
+def gather_grads(b: Bucket, *, use_kernel: bool = True, untouched_is_missing: bool = False):
     """Make ``b.flat_g`` hold this step's gradients.  Views that already alias the bucket
     cost nothing; foreign ``.grad`` tensors are copied in (one multi-tensor kernel on CUDA);
     missing grads contribute zeros.  Returns ``(number of tensors copied, indices of the
-    parameters whose grad is None)``."""
+    parameters without a gradient this step)``.
+
+    ``untouched_is_missing``: a parameter whose ``.grad`` aliases the bucket but which no backward pass wrote to
+    since the last step (``p._dlion_touched`` is False — see ``Lion._install_grad_tracking``) counts as missing
+    too: the reference skips ``p.grad is None`` parameters (distributed_lion.py:180), and once gradients alias
+    the bucket "None" can only be told apart from "zero" this way.  The marks are consumed here."""
     src, dst, missing = [], [], []
     for i, (p, gv) in enumerate(zip(b.params, b.g_views)):
         g = p.grad
+        touched = getattr(p, "_dlion_touched", None)
+        if touched:
+            p._dlion_touched = False
         if g is None:
             gv.zero_()
             missing.append(i)
         elif g.is_sparse:
             raise RuntimeError("Lion does not support sparse gradients")
         elif g.data_ptr() == gv.data_ptr() and g.dtype == gv.dtype:
+            if untouched_is_missing and touched is False:
+                missing.append(i)       # aliased, and nothing accumulated into it: "grad is None" upstream
             continue
         else:
             src.append(g)

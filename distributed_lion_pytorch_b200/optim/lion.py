@@ -18,7 +18,12 @@ What is different from the reference (on purpose):
   gradient instead of desynchronising the collective sequence (D6);
 * new keyword-only options: ``vote`` (majority | average), ``tie`` (neg | zero), ``comm``
   (auto | fused | nccl_1bit | local), ``live_mask`` / :meth:`set_live_mask`, ``seed``,
-  ``stochastic_rounding`` (bf16 parameter writes; off by default = the reference's arithmetic).
+  ``stochastic_rounding`` (bf16 parameter writes; off by default = the reference's arithmetic);
+* the two neighbours of ``step()`` in every training loop can ride in the same kernel pass:
+  :meth:`clip_grad_norm_` measures the gradient norm and hands the *scaling* to the next ``step()``
+  (the kernels work on ``round(g * coef)`` in registers), and ``zero_grads_in_step=True`` lets the
+  kernels clear the gradient bucket once consumed, so ``zero_grad()`` after ``step()`` is free.
+  Both are off unless asked for (``Trainer`` asks); results are bit-identical to the separate passes.
 
 Communication back-ends (``comm``):
 
@@ -53,7 +58,8 @@ class Lion(Optimizer):
                  weight_decay: float = 0.0, max_grad_norm: Optional[float] = None, *,
                  vote: str = "majority", tie: str = "neg", comm: str = "auto",
                  process_group=None, live_mask: Optional[int] = None, seed: int = 0,
-                 flat_grads: bool = True, use_kernels: Optional[bool] = None, stochastic_rounding: bool = False):
+                 flat_grads: bool = True, use_kernels: Optional[bool] = None, stochastic_rounding: bool = False,
+                 zero_grads_in_step: bool = False, wait_mask: Optional[int] = None):
         if not lr > 0.0:
             raise ValueError(f"lr must be positive, got {lr}")
         if not all(0.0 <= b <= 1.0 for b in betas):
@@ -78,6 +84,15 @@ class Lion(Optimizer):
         # SURVEY §7.3 — at lr ~ 1e-4 a sign update is below half a bf16 ulp of a typical weight).  The noise is a
         # counter hash of (seed, step, element), identical on every rank, so replicas stay bit-identical.
         self.stochastic_rounding = bool(stochastic_rounding)
+        # opt-in: step() leaves the flat gradient buckets zeroed (the kernels clear g once consumed), which turns
+        # the zero_grad() that follows into a no-op.  Off by default: torch optimizers leave .grad alone in step().
+        self.zero_grads_in_step = bool(zero_grads_in_step)
+        # ranks whose progress flags the fused kernel waits for (None = every rank).  A rank the caller KNOWS to be
+        # gone is taken out of both masks so that nobody spins on flags that will never arrive.
+        self.wait_mask = wait_mask
+        self._pending_clip = None       # (sumsq_dev, max_norm) measured by clip_grad_norm_, consumed by step()
+        self._g_zeroed = False          # the last step() left every flat gradient bucket zeroed
+        self._track_hooks = []
         self._buckets: Optional[List[Bucket]] = None
         self._bucket_sig = None
         self._frozen_actives: List[list] = []
@@ -85,6 +100,25 @@ class Lion(Optimizer):
         self._steps_done = 0
         self._cpu_gen: Optional[torch.Generator] = None
         self.last_step_stats: Dict[str, float] = {}
+        self._install_grad_tracking()
+
+    # ------------------------------------------------------------------ which parameters got a gradient this step
+    def _install_grad_tracking(self) -> None:
+        """With flat buckets ``p.grad`` aliases the bucket from the first step on and is never ``None`` again, so
+        "did this parameter receive a gradient in this step" (reference: ``if p.grad is not None`` at
+        distributed_lion.py:180) needs its own record: a post-accumulate hook (and ``ops.mark_grad_written`` in the
+        custom backward functions that add into ``.grad`` themselves) sets ``p._dlion_touched``; ``step()`` reads
+        and clears it.  Only the single-worker path consults it — with W > 1 a parameter without a gradient
+        contributes zeros (see the module docstring, D6)."""
+        from ..ops import mark_grad_written
+        seen = set()
+        for group in self.param_groups:
+            for p in group["params"]:
+                if id(p) in seen or not p.requires_grad or not p.is_leaf:
+                    continue
+                seen.add(id(p))
+                if hasattr(p, "register_post_accumulate_grad_hook"):
+                    self._track_hooks.append(p.register_post_accumulate_grad_hook(mark_grad_written))
 
     # ------------------------------------------------------------------ public extras
     def set_live_mask(self, mask: Optional[int]) -> None:
@@ -191,6 +225,11 @@ class Lion(Optimizer):
         super().add_param_group(param_group)
         if getattr(self, "_buckets", None) is not None:
             self.refresh_active_set()
+        if hasattr(self, "_track_hooks"):           # not during Optimizer.__init__
+            from ..ops import mark_grad_written
+            for p in self.param_groups[-1]["params"]:
+                if p.requires_grad and p.is_leaf and hasattr(p, "register_post_accumulate_grad_hook"):
+                    self._track_hooks.append(p.register_post_accumulate_grad_hook(mark_grad_written))
 
     # ------------------------------------------------------------------ backend choice
     def _kernels_ok(self, device: torch.device) -> bool:
@@ -229,16 +268,69 @@ class Lion(Optimizer):
                 loss = closure()
         self._resolve_backend()
         self._ensure_buckets()
+        clip, self._pending_clip = self._pending_clip, None
+        zero_g = self.zero_grads_in_step and self.flat_grads
+        local = self._backend.name == "local"
+        cleaned = bool(self._buckets)
         for b in self._buckets:
-            _, missing = gather_grads(b, use_kernel=self._kernels_ok(b.device))
+            _, missing = gather_grads(b, use_kernel=self._kernels_ok(b.device), untouched_is_missing=local)
             group = self.param_groups[b.group_index]
             beta1, beta2 = group["betas"]
-            self._backend.step(b, float(group["lr"]), float(group["weight_decay"]), float(beta1), float(beta2),
-                               missing)
+            cleaned &= bool(self._backend.step(b, float(group["lr"]), float(group["weight_decay"]), float(beta1),
+                                               float(beta2), missing, clip=clip, zero_g=zero_g))
             if self.flat_grads:
                 alias_grads(b)
+        self._g_zeroed = cleaned
         self._steps_done += 1
         return loss
+
+    # ------------------------------------------------------------------ gradient clipping folded into step()
+    def _grads_aliased(self) -> bool:
+        """Every bucketed parameter's ``.grad`` IS its slice of the flat gradient bucket, and no parameter of this
+        optimizer holds a gradient outside the buckets."""
+        if not (self._buckets and self.flat_grads):
+            return False
+        owned = set()
+        for b in self._buckets:
+            for p, gv in zip(b.params, b.g_views):
+                g = p.grad
+                if g is None or g.data_ptr() != gv.data_ptr() or g.dtype != gv.dtype:
+                    return False
+                owned.add(id(p))
+        return all(p.grad is None or id(p) in owned for grp in self.param_groups for p in grp["params"])
+
+    @torch.no_grad()
+    def clip_grad_norm_(self, max_norm: float, extra_sumsq: Optional[torch.Tensor] = None) -> torch.Tensor:
+        """``torch.nn.utils.clip_grad_norm_`` over this optimizer's parameters (local gradients only — HF Trainer's
+        ``max_grad_norm``, which the reference inherits: SURVEY §3.1).  Returns the total norm (a tensor; no host
+        sync).
+
+        In steady state (gradients aliased to the flat buckets, CUDA, library loaded) only the *norm* is computed
+        here — one ``sumsq`` launch per bucket — and the scaling is handed to the next :meth:`step`, whose kernels
+        form ``round(g * coef)`` in registers: the gradient bucket is read twice per optimizer step instead of
+        three times and written zero times instead of once.  ``p.grad`` therefore still holds the *unclipped*
+        values afterwards; the parameters and momenta after ``step()`` are bit-identical to clip-then-step.
+        Otherwise (first step, CPU, foreign ``.grad`` tensors) the gradients are scaled in place, eagerly.
+
+        ``extra_sumsq`` (fp32[1] on the same device): sum of squares of gradients that are clipped together with
+        ours but live elsewhere (another optimizer's parameters)."""
+        max_norm = float(max_norm)
+        if self._grads_aliased() and self._buckets[0].device.type == "cuda" and self._kernels_ok(self._buckets[0].device) \
+                and len({b.device for b in self._buckets}) == 1:
+            from ..ops import bucket_ops
+            parts = [bucket_ops.sumsq(b.flat_g) for b in self._buckets]
+            if extra_sumsq is not None:
+                parts.append(extra_sumsq.view(1).float())
+            total = parts[0] if len(parts) == 1 else torch.stack([x.view(()) for x in parts]).sum().view(1)
+            self._pending_clip = (total, max_norm)
+            return total.sqrt().view(())
+        self._pending_clip = None
+        params = [p for grp in self.param_groups for p in grp["params"] if p.grad is not None]
+        if not params:
+            return torch.zeros(())
+        if extra_sumsq is not None:
+            raise RuntimeError("extra_sumsq needs the flat-bucket CUDA path")
+        return torch.nn.utils.clip_grad_norm_(params, max_norm)
 
     def zero_grad(self, set_to_none: bool = True) -> None:
         """With flat gradient buckets the gradients are cleared by one memset per bucket and
@@ -246,8 +338,11 @@ class Lion(Optimizer):
         the flat tensor the optimizer kernel reads."""
         if self._buckets and self.flat_grads:
             owned = set()
+            clean, self._g_zeroed = self._g_zeroed, False       # the step's kernels already cleared the buckets
+            self._pending_clip = None                           # a norm measured on these gradients is void now
             for b in self._buckets:
-                b.flat_g.zero_()
+                if not clean:
+                    b.flat_g.zero_()
                 alias_grads(b)
                 owned.update(id(p) for p in b.params)
             for group in self.param_groups:
@@ -293,17 +388,58 @@ class Lion(Optimizer):
 
     @torch.no_grad()
     def resync_replicas(self, src: int = 0) -> None:
-        """Collective: overwrite every replica's parameters with rank ``src``'s.  This is how a
+        """Collective over ``process_group`` (``src`` is a rank *within that group*): overwrite every replica's
+        parameters with rank ``src``'s.  This is how a
         worker that really missed steps rejoins (SURVEY §7.3: rejoin = parameter re-broadcast);
         momenta stay per worker, as the algorithm prescribes."""
         from ..parallel import runtime as rt
         self._ensure_buckets()
         if self._buckets:
-            rt.broadcast_parameters([b.flat_p for b in self._buckets], src)
+            rt.broadcast_parameters([b.flat_p for b in self._buckets], src, group=self.process_group)
         else:
-            rt.broadcast_parameters([p for g in self.param_groups for p in g["params"]], src)
+            rt.broadcast_parameters([p for g in self.param_groups for p in g["params"]], src, group=self.process_group)
 
     # ------------------------------------------------------------------ diagnostics
+    @torch.no_grad()
+    def step_crosscheck(self) -> Dict[str, bool]:
+        """Collective diagnostic (call on every rank in place of one ``step()``): take this optimizer step twice —
+        through the active back-end on the real buckets, and through the split ``nccl_1bit`` path (pack kernel →
+        ``all_gather`` → vote/update kernel) on clones of the same parameters, gradients and momenta — and compare
+        the results bit for bit.  Returns ``{"equal": …, "replicas_identical": …}``, both reduced over ranks.
+
+        This is how ``bench.py`` and the multi-GPU tests prove that the fused NVLink kernel computed *the* update
+        (reference: distributed_lion.py:61-96) at full size on real hardware, not merely a finite loss.  Costs one
+        extra copy of p, g, m."""
+        import dataclasses
+        from . import backends
+        self._resolve_backend()
+        self._ensure_buckets()
+        kern = bool(self._buckets) and self._kernels_ok(self._buckets[0].device)
+        clones = []
+        for b in self._buckets:
+            gather_grads(b, use_kernel=kern)
+            clones.append((b.flat_p.clone(), b.flat_g.clone(), b.flat_m.clone()))
+        clip, steps_done = self._pending_clip, self._steps_done
+        hp = [(float(self.param_groups[b.group_index]["lr"]), float(self.param_groups[b.group_index]["weight_decay"]),
+               *map(float, self.param_groups[b.group_index]["betas"])) for b in self._buckets]
+        self.step()
+        equal = True
+        if self.world_size > 1:
+            split = backends.AllGatherBackend(self)
+            self._steps_done = steps_done               # same noise streams as the step just taken
+            try:
+                for b, (p, g, m), (lr, wd, b1, b2) in zip(self._buckets, clones, hp):
+                    shadow = dataclasses.replace(b, flat_p=p, flat_g=g, flat_m=m, scratch={})
+                    split.step(shadow, lr, wd, b1, b2, [], clip=clip if kern else None, zero_g=False)
+                    equal = equal and bool(torch.equal(p, b.flat_p)) and bool(torch.equal(m, b.flat_m))
+            finally:
+                self._steps_done = steps_done + 1
+            dev = self._buckets[0].device if self._buckets else torch.device("cpu")
+            flag = torch.tensor([1 if equal else 0], dtype=torch.int32, device=dev)
+            dist.all_reduce(flag, op=dist.ReduceOp.MIN, group=self.process_group)
+            equal = bool(int(flag.item()))
+        return {"equal": equal, "replicas_identical": self.replicas_identical()}
+
     @torch.no_grad()
     def replica_checksum(self) -> torch.Tensor:
         """One int64 per bucket: the wrap-around sum of the parameter bits.  Bit-identical replicas — the

@@ -88,10 +88,14 @@ def shutdown() -> None:
 
 
 @torch.no_grad()
-def broadcast_parameters(tensors: Iterable[torch.Tensor], src: int = 0, bucket_bytes: int = 256 << 20) -> None:
-    """Make every replica start from rank ``src``'s values (what DDP's constructor does, X4)."""
+def broadcast_parameters(tensors: Iterable[torch.Tensor], src: int = 0, bucket_bytes: int = 256 << 20,
+                         group=None) -> None:
+    """Make every replica start from rank ``src``'s values (what DDP's constructor does, X4).  With ``group``,
+    ``src`` is a rank *within that group* and only its members take part."""
     if not is_dist():
         return
+    pg = group
+    gsrc = dist.get_global_rank(pg, src) if pg is not None else src
     group: List[torch.Tensor] = []
     size = 0
 
@@ -100,10 +104,10 @@ def broadcast_parameters(tensors: Iterable[torch.Tensor], src: int = 0, bucket_b
         if not group:
             return
         if len(group) == 1:
-            dist.broadcast(group[0], src)
+            dist.broadcast(group[0], gsrc, group=pg)
         else:
             flat = torch.cat([t.reshape(-1) for t in group])
-            dist.broadcast(flat, src)
+            dist.broadcast(flat, gsrc, group=pg)
             off = 0
             for t in group:
                 t.copy_(flat[off:off + t.numel()].view_as(t))

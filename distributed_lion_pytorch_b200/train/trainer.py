@@ -130,6 +130,7 @@ class Trainer:
         self.timer = StepTimer(enabled=bool(getattr(self.args, "profile_steps", False)))
         self._wandb = None
         self._last_grad_norm = None
+        self.optimizer_step_events = None       # set to a list to collect (start, end) CUDA events per step
         if self.args.gradient_checkpointing and hasattr(self.model, "gradient_checkpointing_enable"):
             self.model.gradient_checkpointing_enable()
 
@@ -212,9 +213,16 @@ class Trainer:
         rt.all_reduce_mean_(flats if flats else [p.grad for p in self.model.parameters() if p.grad is not None])
 
     def _clip_gradients(self) -> Optional[torch.Tensor]:
+        """Local gradient-norm clipping (HF Trainer's ``max_grad_norm``, default 1.0, which the reference inherits).
+        With ``Lion`` in steady state this only *measures* the norm (one ``sumsq`` launch per bucket); the scaling
+        rides inside the optimizer kernel (``Lion.clip_grad_norm_``), so no clip kernel runs."""
         mg = self.args.max_grad_norm
         if mg is None or mg <= 0:
             return None
+        if isinstance(self.optimizer, Lion):
+            mine = self._lion_param_ids()
+            if all(p.grad is None or id(p) in mine for p in self.model.parameters()):
+                return self.optimizer.clip_grad_norm_(mg)
         flats = self._flat_grads()
         if flats and flats[0].is_cuda:
             from ..ops import bucket_ops, require_library
@@ -223,9 +231,20 @@ class Trainer:
         params = [p for p in self.model.parameters() if p.grad is not None]
         return torch.nn.utils.clip_grad_norm_(params, mg)
 
+    def _lion_param_ids(self) -> set:
+        ids = getattr(self, "_lion_ids", None)
+        n = sum(len(g["params"]) for g in self.optimizer.param_groups)
+        if ids is None or len(ids) != n:
+            ids = self._lion_ids = {id(p) for g in self.optimizer.param_groups for p in g["params"]}
+        return ids
+
     def _optimizer_step(self) -> None:
-        if isinstance(self.optimizer, Lion) and self._dropout_schedule is not None:
-            self.optimizer.set_live_mask(self._dropout_schedule.mask(self.state.global_step))
+        if isinstance(self.optimizer, Lion):
+            if self._dropout_schedule is not None:
+                self.optimizer.set_live_mask(self._dropout_schedule.mask(self.state.global_step))
+            # this loop always calls zero_grad() right after step(): let the optimizer kernel clear the gradient
+            # bucket while it has it in hand, so that zero_grad() has nothing left to do
+            self.optimizer.zero_grads_in_step = True
         self.optimizer.step()
         self.lr_scheduler.step()
         if isinstance(self.optimizer, Lion):
@@ -265,10 +284,17 @@ class Trainer:
             total = loss if total is None else total + loss
         with self.timer.phase("grad_sync"):
             self._sync_gradients()
+        ev = self.optimizer_step_events
+        if ev is not None:                      # bench.py: device time of clip + optimizer + zero_grad
+            a, b = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
+            a.record()
         with self.timer.phase("clip"):
             self._last_grad_norm = self._clip_gradients()
         with self.timer.phase("optimizer"):
             self._optimizer_step()
+        if ev is not None:
+            b.record()
+            ev.append((a, b))
         self.state.global_step += 1
         return total
 

@@ -24,7 +24,7 @@
 extern "C" {
 #endif
 
-#define DLION_VERSION 100
+#define DLION_VERSION 101
 
 typedef enum { DLION_F32 = 0, DLION_BF16 = 1, DLION_F16 = 2 } dlion_dtype;
 
@@ -61,6 +61,23 @@ int dlion_lion_local(void* p, const void* g, void* m, int64_t n, int dtype, floa
  * a Lion update is below half a bf16 ulp of a typical weight). */
 int dlion_lion_local_sr(void* p, const void* g, void* m, int64_t n, int dtype, float lr, float decay, float beta1,
                         float omb1, float beta2, float omb2, uint64_t sr_key, int64_t elem_base, void* stream);
+
+/* The same three kernels with the step's neighbours folded in (reference: HF Trainer's clip_grad_norm_ before
+ * optimizer.step() and zero_grad() after it, which upstream inherits — run_clm.py:588-622):
+ *   clip_sumsq != NULL  device pointer to sum(g^2) over all gradients of the model; the kernel works on
+ *                       g' = round_T(g * min(1, clip_max_norm / (sqrt(*clip_sumsq) + 1e-6))) — bit for bit what
+ *                       dlion_clip_scale followed by the plain kernel computes — without rewriting g;
+ *   zero_g != 0         g is overwritten with zeros once consumed (lion_local, vote_update). */
+int dlion_lion_local_clip(void* p, void* g, void* m, int64_t n, int dtype, float lr, float decay, float beta1,
+                          float omb1, float beta2, float omb2, uint64_t sr_key, int64_t elem_base,
+                          const float* clip_sumsq, float clip_max_norm, int zero_g, void* stream);
+int dlion_sign_pack_clip(const void* m, const void* g, uint32_t* words, int64_t n, int dtype, float beta1, float omb1,
+                         float stoch_r, uint64_t seed, uint32_t step, uint32_t rank, const float* clip_sumsq,
+                         float clip_max_norm, void* stream);
+int dlion_vote_update_clip(void* p, void* g, void* m, const uint32_t* gathered, int64_t row_words, int world,
+                           uint32_t live_mask, int64_t n, int dtype, float lr, float decay, float beta2, float omb2,
+                           int vote, uint64_t sr_key, const float* clip_sumsq, float clip_max_norm, int zero_g,
+                           void* stream);
 
 /* Sign + pack: words[e/32] bit e%32 = (b1*m + (1-b1)*g)[e] > 0; tail bits of the last word are 0.
  * stoch_r > 0 selects stochastic binarisation, bit ~ Bernoulli((c + r) / 2r) with a Philox
@@ -127,6 +144,15 @@ typedef struct {
   int64_t spin_limit;  /* flag polls before giving up (0 = default) */
   uint64_t sr_key;     /* != 0: stochastic rounding of the bf16 parameter write, keyed by (sr_key, element index) —
                           identical on every rank; 0 = round to nearest (the reference's arithmetic) */
+  /* Folded neighbours of the step (reference: HF Trainer calls clip_grad_norm_ before optimizer.step() and
+   * model.zero_grad() after it; upstream inherits both through transformers.Trainer, run_clm.py:588-622).
+   * clip_sumsq != NULL: device pointer to sum(g^2) over ALL gradients of the model (dlion_sumsq); the kernel uses
+   * g' = round_T(g * min(1, clip_max_norm / (sqrt(*clip_sumsq) + 1e-6))) for the sign and the momentum — bit for
+   * bit what dlion_clip_scale followed by this kernel would compute — and g itself is not rewritten.
+   * zero_g != 0: g is overwritten with zeros once consumed (the zero_grad that would follow the step). */
+  const float* clip_sumsq;
+  float clip_max_norm;
+  int zero_g;
 } dlion_fused_args;
 
 #define DLION_FUSED_MAX_CTAS 1024

@@ -238,3 +238,63 @@ def test_add_param_group_after_first_step_is_picked_up(ref_mod):
                     list(a_new.parameters()) + list(b_new.parameters())):
         assert torch.equal(x, y)
     assert len(o_new.buckets) == 2
+
+
+class _Intermittent(torch.nn.Module):
+    """A parameter (``b``) that is part of the graph only on even calls — conditionally-used branches,
+    alternating heads and routed experts look like this to the optimizer."""
+
+    def __init__(self):
+        super().__init__()
+        torch.manual_seed(7)
+        self.a = torch.nn.Linear(6, 4)
+        self.b = torch.nn.Linear(4, 4)
+        self.calls = 0
+
+    def forward(self, x):
+        h = self.a(x)
+        if self.calls % 2 == 0:
+            h = self.b(h)
+        self.calls += 1
+        return h
+
+
+def test_parameter_without_gradient_is_left_untouched_like_the_reference(ref_mod):
+    """reference: ``if p.grad is not None`` (distributed_lion.py:180) — a parameter that received no gradient in
+    a step gets no weight decay, no momentum decay and no sign(beta1*m) move.  With flat buckets ``p.grad`` aliases
+    the bucket from the second step on and is never None again; the per-step "written" marks must keep the
+    reference's behaviour."""
+    m_ref, m_new = _Intermittent(), _Intermittent()
+    o_ref = ref_mod.Lion(m_ref.parameters(), lr=1e-2, weight_decay=0.1)
+    o_new = Lion(m_new.parameters(), lr=1e-2, weight_decay=0.1)
+    torch.manual_seed(3)
+    xs = [torch.randn(5, 6) for _ in range(6)]
+    for x in xs:
+        for model, opt in ((m_ref, o_ref), (m_new, o_new)):
+            opt.zero_grad()
+            model(x).pow(2).mean().backward()
+            opt.step()
+    for (n, a), b in zip(m_ref.named_parameters(), m_new.parameters()):
+        assert torch.equal(a, b), n
+    for a, b in zip(m_ref.parameters(), m_new.parameters()):
+        assert torch.equal(o_ref.state[a]["exp_avg"], o_new.state[b]["exp_avg"])
+
+
+def test_clip_grad_norm_eager_path_matches_torch():
+    """On CPU (no kernels) ``Lion.clip_grad_norm_`` scales the gradients in place like torch's utility."""
+    m1, m2 = _model(4), _model(4)
+    o1 = Lion(m1.parameters(), lr=1e-3)
+    o2 = Lion(m2.parameters(), lr=1e-3)
+    torch.manual_seed(0)
+    x = torch.randn(5, 13)
+    for step in range(3):
+        for m, o in ((m1, o1), (m2, o2)):
+            o.zero_grad()
+            (m(x).pow(2).mean() * 100).backward()
+        n1 = o1.clip_grad_norm_(0.5)
+        n2 = torch.nn.utils.clip_grad_norm_(m2.parameters(), 0.5)
+        assert torch.allclose(n1, n2)
+        o1.step()
+        o2.step()
+    for a, b in zip(m1.parameters(), m2.parameters()):
+        assert torch.equal(a, b)

@@ -253,3 +253,29 @@ def test_stochastic_rounding_keeps_replicas_bit_identical(comm):
     for o in outs[1:]:
         assert all(torch.equal(a, b) for a, b in zip(o[0], outs[0][0]))      # same noise on every rank
     assert all(o[1] for o in outs) and outs[0][2] > 0
+
+
+def _worker_crosscheck(rank, world):
+    """step_crosscheck / clip_grad_norm_ / zero_grads_in_step plumbing on the gloo path (the kernels' folded forms
+    are covered by the GPU tests): an optimizer step taken through the active back-end equals the split path on
+    clones, replicas stay identical, and the eager clip keeps twin optimizers in lock-step."""
+    from distributed_lion import Lion
+    m = _make(0, torch.float32)
+    o = Lion(m.parameters(), lr=1e-2, weight_decay=0.1, zero_grads_in_step=True)
+    g = torch.Generator().manual_seed(100 + rank)
+    res = []
+    for _ in range(3):
+        x = torch.randn(6, 33, generator=g)
+        (m(x).pow(2).mean() * 30).backward()
+        norm = o.clip_grad_norm_(1.0)
+        chk = o.step_crosscheck()
+        o.zero_grad()
+        res.append((float(norm) > 0, chk["equal"], chk["replicas_identical"]))
+    return dict(res=res, steps=o.steps_done, params=torch.cat([p.detach().flatten() for p in m.parameters()]))
+
+
+def test_step_crosscheck_and_clip_on_gloo():
+    outs = run_distributed(_worker_crosscheck, 2)
+    for o in outs:
+        assert o["steps"] == 3 and all(all(t) for t in o["res"])
+    assert torch.equal(outs[0]["params"], outs[1]["params"])

@@ -103,3 +103,100 @@ def test_stochastic_rounding_fused_equals_split_and_replicas_identical():
     for o in outs:
         assert o["same"] and torch.equal(o["fused"], o["split"]) and torch.equal(o["fused"], outs[0]["fused"])
     assert not torch.equal(outs[0]["fused"], base[0]["fused"])          # and it is not round-to-nearest
+
+
+# --------------------------------------------------------------------------- real size, real NVLink
+def _big_params(dev, seed, small=False):
+    """Two param groups; each holds bf16 AND fp32 tensors, so the optimizer owns four buckets that share one flag
+    table and one arena (which has to re-grow when the larger bucket comes second).  The bf16 bucket of group 0
+    has > 64 M elements with odd shapes (padding inside the bucket)."""
+    g = torch.Generator(device=dev).manual_seed(seed)
+    mk = lambda shape, dt: torch.nn.Parameter((torch.randn(*shape, device=dev, generator=g) * 0.05).to(dt))  # noqa: E731
+    if small:      # same structure, ~8 M elements: for grids of a few CTAs
+        g0 = [mk((501, 1003), torch.float32), mk((1024, 4096), torch.bfloat16), mk((501, 7001), torch.bfloat16),
+              mk((77,), torch.bfloat16)]
+        g1 = [mk((256, 4096), torch.bfloat16), mk((555,), torch.float32)]
+        return g0, g1
+    g0 = [mk((1001, 1003), torch.float32), mk((4096, 8192), torch.bfloat16), mk((3001, 7001), torch.bfloat16),
+          mk((2048, 2048), torch.float32), mk((1024, 10001), torch.bfloat16), mk((77,), torch.bfloat16)]
+    g1 = [mk((1024, 4096), torch.bfloat16), mk((555,), torch.float32), mk((2000, 999), torch.bfloat16)]
+    return g0, g1
+
+
+def _worker_big(rank, world, chunk_elems, steps, multicast, grid, skew):
+    import os
+    import random
+    import time
+    os.environ["DLION_MULTICAST"] = "1" if multicast else "0"
+    os.environ["DLION_CHUNK_ELEMS"] = str(chunk_elems)
+    if grid:
+        os.environ["DLION_FUSED_GRID"] = str(grid)
+    from distributed_lion import Lion
+    dev = torch.device("cuda", rank)
+    opts, params = {}, {}
+    for comm in ("fused", "nccl_1bit"):
+        g0, g1 = _big_params(dev, seed=0, small=bool(grid))
+        params[comm] = g0 + g1
+        opts[comm] = Lion([dict(params=g0, lr=1e-3, weight_decay=0.1), dict(params=g1, lr=3e-4, weight_decay=0.0)],
+                          comm=comm, zero_grads_in_step=True)
+    gen = torch.Generator(device=dev).manual_seed(1000 + rank)
+    rnd = random.Random(5 + rank)
+    bad_step = -1
+    for s in range(steps):
+        for i, p in enumerate(params["fused"]):
+            # a norm well above the clip threshold in some steps, below it in others
+            gr = (torch.randn(p.shape, device=dev, generator=gen) * (1e-3 if s % 3 else 1e-5)).to(p.dtype)
+            for comm in ("fused", "nccl_1bit"):
+                q = params[comm][i]
+                if q.grad is None:
+                    q.grad = gr.clone()
+                else:
+                    q.grad.copy_(gr)
+        if skew:
+            torch.cuda.synchronize()
+            time.sleep(rnd.random() * 0.004)             # ranks enter the kernel at different times
+        for comm in ("fused", "nccl_1bit"):
+            opts[comm].clip_grad_norm_(1.0)
+            opts[comm].step()
+            opts[comm].zero_grad()
+        if s % 10 == 9 or s == steps - 1:
+            same = all(torch.equal(bf.flat_p, bs.flat_p) and torch.equal(bf.flat_m, bs.flat_m)
+                       for bf, bs in zip(opts["fused"].buckets, opts["nccl_1bit"].buckets))
+            if not same and bad_step < 0:
+                bad_step = s
+    torch.cuda.synchronize()
+    ctx = opts["fused"]._backend._ctx
+    ctx.check_status()
+    nb = [(str(b.dtype), b.numel) for b in opts["fused"].buckets]
+    return dict(bad_step=bad_step, identical=opts["fused"].replicas_identical(), backend=opts["fused"].backend_name,
+                buckets=nb, launches=ctx.epoch, mc=ctx.uses_multicast, grid=ctx.grid_for(torch.bfloat16),
+                clean=all(int(b.flat_g.count_nonzero()) == 0 for b in opts["fused"].buckets))
+
+
+@pytest.mark.parametrize("multicast", [False, True])
+def test_fused_real_size_multi_chunk_multi_bucket(multicast):
+    """The fused kernel at real size on real NVLink: > 64 M-element bf16 bucket + fp32 buckets + a second param
+    group (four buckets, one flag table, the arena re-grown once), DLION_CHUNK_ELEMS = 4 Mi (about 20 launches and
+    epochs per step, every ring wraps many times), gradient clip and zero-fill folded into the kernel, 50 steps —
+    compared bit for bit with the split pack / all_gather / vote path every 10 steps on every rank."""
+    world = min(torch.cuda.device_count(), 8)
+    outs = run_distributed(_worker_big, world, 1 << 22, 50, multicast, 0, False, backend="nccl", timeout=900)
+    if multicast and not outs[0]["mc"]:
+        pytest.skip("no NVLS multicast pointer on this fabric")
+    assert outs[0]["backend"] == "fused"
+    assert max(n for _, n in outs[0]["buckets"]) >= 64 * 1000 * 1000 and len(outs[0]["buckets"]) == 4
+    assert outs[0]["launches"] >= 50 * 18
+    for o in outs:
+        assert o["bad_step"] < 0, f"fused != split from step {o['bad_step']}"
+        assert o["identical"] and o["clean"]
+    print(f"W={world} buckets={outs[0]['buckets']} launches={outs[0]['launches']} multicast={outs[0]['mc']}")
+
+
+@pytest.mark.parametrize("grid", [3, 37])
+def test_fused_small_grid_skewed_arrival_real_gpus(grid):
+    """Few CTAs own many tiles each (every smem ring and the 32-tile sender ring wrap and fill), ranks arrive up to
+    4 ms apart, 1 Mi-element chunks: the protocol's back-pressure paths on real peer memory."""
+    world = min(torch.cuda.device_count(), 8)
+    outs = run_distributed(_worker_big, world, 1 << 20, 6, grid == 37, grid, True, backend="nccl", timeout=900)
+    for o in outs:
+        assert o["grid"] == grid and o["bad_step"] < 0 and o["identical"] and o["clean"]

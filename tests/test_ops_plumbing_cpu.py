@@ -73,3 +73,30 @@ def test_gpt2_tied_embedding_gets_both_gradients(emulate):
     out = m(ids, return_logits=True)
     F.cross_entropy(out.logits[:, :-1].reshape(-1, 512), ids[:, 1:].reshape(-1)).backward()
     assert torch.allclose(g, m.transformer.wte.weight.grad, atol=1e-5)
+
+
+def test_linear_cross_entropy_under_autocast_with_fp32_master_weights(emulate):
+    """Mixed precision: fp32 parameters under autocast (``Trainer.autocast`` for --bf16 without --torch_dtype).
+    The logits GEMMs run in bf16, ``out=`` / in-place GEMMs are not autocast-aware, and the gradients must come
+    back in the parameters' fp32 (this path used to raise 'Expected out tensor to have dtype
+    BFloat16')."""
+    from distributed_lion_pytorch_b200.models import build_model
+    from distributed_lion_pytorch_b200.ops.cross_entropy import linear_cross_entropy, linear_log_probs
+    torch.manual_seed(0)
+    N, H, V = 40, 16, 97
+    h = torch.randn(N, H, requires_grad=True)
+    w = torch.randn(V, H, requires_grad=True)
+    labels = torch.randint(0, V, (N,))
+    with torch.autocast("cpu", dtype=torch.bfloat16):
+        loss = linear_cross_entropy(h, w, labels, chunk=16)
+        lp = linear_log_probs(h, w, labels, chunk=16)
+    (loss + lp.sum() * 0.01).backward()
+    assert h.grad.dtype == torch.float32 and w.grad.dtype == torch.float32
+    ref = F.cross_entropy(h.detach() @ w.detach().t(), labels)
+    assert abs(float(loss) - float(ref)) < 0.15            # bf16 logits
+    m = build_model("gpt2-tiny")
+    ids = torch.randint(0, 512, (2, 16))
+    with torch.autocast("cpu", dtype=torch.bfloat16):
+        out = m(ids, labels=ids)
+    out.loss.backward()
+    assert all(p.grad is not None and p.grad.dtype == torch.float32 for p in m.parameters())

@@ -70,3 +70,51 @@ def test_static_scratch_refuses_oversized_input():
     assert rc == -3
     msg = L.dlion_last_error().decode()
     assert "exceeds the built-in scratch" in msg and str(limit) in msg
+
+
+def test_static_scratch_empty_input_and_largest_input():
+    """The two ends of the size range: n = 0 gives 0, and n = the stated maximum (every one of the 4,096 slots in
+    use) still equals the caller-scratch entry point."""
+    L, _cabi = _lib()
+    stream = torch.cuda.current_stream().cuda_stream
+    out = torch.full((1,), -1.0, dtype=torch.float32, device="cuda")
+    x = torch.ones(8, device="cuda", dtype=torch.bfloat16)
+    rc = L.dlion_sumsq_static(x.data_ptr(), 0, _cabi.dtype_code(x.dtype), out.data_ptr(), stream)
+    assert rc == 0, L.dlion_last_error()
+    torch.cuda.synchronize()
+    assert float(out) == 0.0
+    limit = int(L.dlion_sumsq_static_max_n())
+    try:
+        big = torch.empty(limit, device="cuda", dtype=torch.bfloat16)      # 512 MiB
+    except torch.OutOfMemoryError:
+        pytest.skip("not enough free device memory for the largest input")
+    big.fill_(0.5)
+    big[::4099] = 2.0
+    for _ in range(2):
+        rc = L.dlion_sumsq_static(big.data_ptr(), limit, _cabi.dtype_code(big.dtype), out.data_ptr(), stream)
+        assert rc == 0, L.dlion_last_error()
+        want = _reference(L, _cabi, big)
+        torch.cuda.synchronize()
+        assert torch.allclose(out, want, rtol=1e-5), (float(out), float(want))
+
+
+def test_static_scratch_on_a_side_stream_and_on_every_device():
+    """A caller's own (non-default) stream, and — where the box has more than one GPU — each device's own copy of
+    the array (the address is looked up per device, with that device current)."""
+    L, _cabi = _lib()
+    for d in range(torch.cuda.device_count()):
+        dev = torch.device("cuda", d)
+        with torch.cuda.device(dev):
+            side = torch.cuda.Stream(device=dev)
+            gen = torch.Generator(device=dev).manual_seed(11 + d)
+            x = torch.randn((1 << 20) + 3, device=dev, generator=gen).bfloat16()
+            out = torch.full((1,), -1.0, dtype=torch.float32, device=dev)
+            torch.cuda.synchronize(dev)
+            for _ in range(2):
+                rc = L.dlion_sumsq_static(x.data_ptr(), x.numel(), _cabi.dtype_code(x.dtype), out.data_ptr(),
+                                          side.cuda_stream)
+                assert rc == 0, L.dlion_last_error()
+                side.synchronize()
+                want = _reference(L, _cabi, x)
+                torch.cuda.synchronize(dev)
+                assert torch.allclose(out, want, rtol=1e-5), (d, float(out), float(want))
