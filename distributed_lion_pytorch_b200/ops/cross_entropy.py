@@ -4,9 +4,7 @@
 over non-ignored tokens).  The token dimension is tiled; per tile: one cuBLAS GEMM makes a
 bf16 logits block, the CE kernel (csrc/cross_entropy.cu) turns it into per-row losses and, in
 place, into d loss / d logits; two more GEMMs fold that block into dh and dW straight away
-(the gradient is produced during the forward, as the loss is always the last node).  Only the
-row *stride* of the block is padded (16-byte rows for the kernel); the GEMMs address the first V
-columns through a strided view, so the LM-head weight is never copied or padded.
+(the gradient is produced during the forward, as the loss is always the last node).
 
 ``linear_log_probs(h, weight, labels)`` returns per-token log-probabilities (for DPO); its
 backward recomputes each logits block and applies the per-row upstream gradient in the kernel.
@@ -29,20 +27,22 @@ IGNORE_INDEX = -100
 _DEFAULT_CHUNK = int(os.environ.get("DLION_CE_CHUNK", "4096"))   # rows of logits alive at a time
 
 
-def _padded_vocab(V: int, mult: int = 64) -> int:
-    """Row stride of a logits block: the vocabulary rounded up so that every row starts 16-byte aligned (the CE
-    kernel's vector accesses) — only the *stride* is padded; the GEMMs read and write the first V columns of each
-    row through a strided view (cuBLAS takes a leading dimension), so the LM-head weight is never copied."""
-    return (V + mult - 1) // mult * mult
+def _pad_rows(weight: torch.Tensor, mult: int = 64) -> torch.Tensor:
+    """[V, H] -> [Vp, H] with zero rows so every logits row is 16-byte aligned and the GEMMs see
+    friendly dimensions; ``wp[:V]`` is a contiguous prefix view.
 
-
-def _logits_block(hc: torch.Tensor, w: torch.Tensor, Vp: int):
-    """[c, H] x [V, H]^T -> (buffer [c, Vp], view [c, V]); the pad columns are never read as logits."""
-    V = w.shape[0]
-    buf = torch.empty(hc.shape[0], Vp, dtype=hc.dtype, device=hc.device)
-    view = buf[:, :V] if Vp != V else buf
-    torch.mm(hc, w.t(), out=view)
-    return buf, view
+    Measured alternative, rejected (``scripts/ab_ce_gemm_shapes.py``, B200, GPT-2 shape): leaving the weight
+    alone and padding only the logits *stride* (GEMMs on ``buf[:, :V]`` views) makes cuBLAS fall off its TMA
+    kernels — 2,895 us instead of 226 us for the logits GEMM, 2,072 instead of 204 us for dh — while this copy
+    costs 36 us per micro-batch."""
+    V = weight.shape[0]
+    Vp = (V + mult - 1) // mult * mult
+    if Vp == V:
+        return weight
+    wp = weight.new_empty(Vp, weight.shape[1])
+    wp[:V].copy_(weight)
+    wp[V:].zero_()
+    return wp
 
 
 def _compute_dtype(h: torch.Tensor) -> torch.dtype:
@@ -111,38 +111,42 @@ class _LinearCE(torch.autograd.Function):
         V = weight.shape[0]
         cd = _compute_dtype(h)
         hq = h if h.dtype == cd else h.to(cd)
-        wq = weight if weight.dtype == cd else weight.to(cd)
-        Vp = _padded_vocab(V)
+        wp = _pad_rows(weight if weight.dtype == cd else weight.to(cd))
         losses = torch.empty(N, dtype=torch.float32, device=h.device)
         n_valid = (labels != ignore_index).sum().clamp_(min=1).to(torch.float32)
         need_grad = ctx.needs_input_grad[0] or ctx.needs_input_grad[1]
         dh = torch.empty_like(hq) if need_grad else None
-        # dW accumulates in the weight's own dtype: fp32 master weights get an fp32 accumulator
-        dw = torch.zeros_like(weight) if need_grad else None
+        dwp = torch.empty_like(wp) if need_grad else None              # written with beta = 0 by the first chunk
         with _device_guard(h), _no_autocast(h):
             for s in range(0, N, chunk):
                 e = min(N, s + chunk)
                 hc = hq[s:e]
-                buf, logits = _logits_block(hc, wq, Vp)                # [c, V] view of a [c, Vp] buffer
-                _ce_kernel(buf, labels[s:e], losses[s:e], V, ignore_index, need_grad)
+                logits = hc @ wp.t()                                   # [c, Vp]
+                _ce_kernel(logits, labels[s:e], losses[s:e], V, ignore_index, need_grad)
                 if need_grad:
-                    torch.mm(logits, wq, out=dh[s:e])                  # d h   (unscaled)
-                    if dw.dtype == cd:
-                        dw.addmm_(logits.t(), hc)                      # d W   (unscaled), beta = 1 epilogue
+                    torch.mm(logits, wp, out=dh[s:e])                  # d h   (unscaled)
+                    if s == 0:
+                        torch.mm(logits.t(), hc, out=dwp)              # d W   (unscaled)
                     else:
-                        dw.add_(logits.t() @ hc)
+                        dwp.addmm_(logits.t(), hc)                     # beta = 1 epilogue
         loss = losses.sum() / n_valid
         if need_grad:
-            ctx.save_for_backward(dh, dw, n_valid)
-            ctx.h_dtype = h.dtype
+            if N == 0:
+                dwp.zero_()
+            ctx.save_for_backward(dh, dwp, n_valid)
+            ctx.V, ctx.h_dtype, ctx.w_dtype = V, h.dtype, weight.dtype
         return loss
 
     @staticmethod
     def backward(ctx, grad_out):
-        dh, dw, n_valid = ctx.saved_tensors
+        dh, dwp, n_valid = ctx.saved_tensors
         scale = (grad_out.float() / n_valid)
         dh.mul_(scale.to(dh.dtype))
-        dw.mul_(scale.to(dw.dtype))
+        dw = dwp[:ctx.V]
+        if dw.dtype == ctx.w_dtype:
+            dw.mul_(scale.to(dw.dtype))
+        else:                                                          # fp32 master weights under autocast
+            dw = dw.to(ctx.w_dtype).mul_(scale.to(ctx.w_dtype))
         return (dh if dh.dtype == ctx.h_dtype else dh.to(ctx.h_dtype)), dw, None, None, None
 
 
@@ -153,14 +157,13 @@ class _LinearLogProbs(torch.autograd.Function):
         V = weight.shape[0]
         cd = _compute_dtype(h)
         hq = h if h.dtype == cd else h.to(cd)
-        wq = weight if weight.dtype == cd else weight.to(cd)
-        Vp = _padded_vocab(V)
+        wp = _pad_rows(weight if weight.dtype == cd else weight.to(cd))
         losses = torch.empty(N, dtype=torch.float32, device=h.device)
         with _device_guard(h), _no_autocast(h):
             for s in range(0, N, chunk):
                 e = min(N, s + chunk)
-                buf, _ = _logits_block(hq[s:e], wq, Vp)
-                _ce_kernel(buf, labels[s:e], losses[s:e], V, ignore_index, False)
+                logits = hq[s:e] @ wp.t()
+                _ce_kernel(logits, labels[s:e], losses[s:e], V, ignore_index, False)
         ctx.save_for_backward(h, weight, labels)
         ctx.ignore_index, ctx.chunk, ctx.cd = ignore_index, chunk, cd
         return -losses
@@ -172,24 +175,27 @@ class _LinearLogProbs(torch.autograd.Function):
         V = weight.shape[0]
         cd = ctx.cd
         hq = h if h.dtype == cd else h.to(cd)
-        wq = weight if weight.dtype == cd else weight.to(cd)
-        Vp = _padded_vocab(V)
+        wp = _pad_rows(weight if weight.dtype == cd else weight.to(cd))
         dh = torch.empty_like(hq)
-        dw = torch.zeros_like(weight)
+        dwp = torch.empty_like(wp)
         # logp = -ce  =>  d logits = (softmax - onehot) * (-grad_logp)
         row_scale = (-grad_logp).float().contiguous()
         with _device_guard(h), _no_autocast(h):
             for s in range(0, N, ctx.chunk):
                 e = min(N, s + ctx.chunk)
                 hc = hq[s:e]
-                buf, logits = _logits_block(hc, wq, Vp)
-                _ce_kernel(buf, labels[s:e], None, V, ctx.ignore_index, False, row_scale=row_scale[s:e])
-                torch.mm(logits, wq, out=dh[s:e])
-                if dw.dtype == cd:
-                    dw.addmm_(logits.t(), hc)
+                logits = hc @ wp.t()
+                _ce_kernel(logits, labels[s:e], None, V, ctx.ignore_index, False, row_scale=row_scale[s:e])
+                torch.mm(logits, wp, out=dh[s:e])
+                if s == 0:
+                    torch.mm(logits.t(), hc, out=dwp)
                 else:
-                    dw.add_(logits.t() @ hc)
-        return (dh if dh.dtype == h.dtype else dh.to(h.dtype)), dw, None, None, None
+                    dwp.addmm_(logits.t(), hc)
+            if N == 0:
+                dwp.zero_()
+        dw = dwp[:V]
+        return (dh if dh.dtype == h.dtype else dh.to(h.dtype)), (dw if dw.dtype == weight.dtype else dw.to(weight.dtype)), \
+            None, None, None
 
 
 def linear_cross_entropy(h: torch.Tensor, weight: torch.Tensor, labels: torch.Tensor,
