@@ -17,8 +17,68 @@ constexpr int kColsumParts = kNumSMs * 4;
 // FUSED: the CTA that finishes last on a 256-column tile (ticket per tile, self-resetting) folds the
 // tile's partial rows and writes — or accumulates into — the final [cols] vector, so the bias gradient
 // needs one launch instead of three (partials, fold, add into .grad).
-template <typename T, bool FUSED>
-__global__ void __launch_bounds__(256) colsum_kernel(const T* __restrict__ x, float* __restrict__ partial,
+// What is being summed.  A source yields the 8 values of (row, 8-column group) and may write a by-product while
+// it has them in registers — the producing elementwise kernel and the bias-gradient reduction become one pass.
+template <typename T>
+struct PlainSource {                     // x[rows, cols] as stored
+  const T* __restrict__ x;
+  int cols;
+  __device__ __forceinline__ void fetch(int64_t r, int cg, float (&v)[8]) const { load8<T>(x + r * cols + cg * 8, v); }
+};
+// d(pre) = dy * gelu_tanh'(pre), written to dpre, and summed over rows: GPT-2's c_fc bias gradient falls out of
+// the activation backward (reference: HF NewGELUActivation backward + Conv1D bias grad, two passes over dY there)
+template <typename T>
+struct GeluBwdSource {
+  const T* __restrict__ pre;
+  const T* __restrict__ dy;
+  T* __restrict__ dpre;
+  int cols;
+  __device__ __forceinline__ void fetch(int64_t r, int cg, float (&d)[8]) const {
+    constexpr float kK = 0.7978845608028654f, kC = 0.044715f;
+    float f[8];
+    const int64_t off = r * cols + cg * 8;
+    load8<T>(pre + off, f);
+    load8<T>(dy + off, d);
+#pragma unroll
+    for (int i = 0; i < 8; ++i) {
+      const float x2 = f[i] * f[i];
+      float t;
+      const float u = kK * fmaf(kC * x2, f[i], f[i]);
+      if constexpr (sizeof(T) == 2) asm("tanh.approx.f32 %0, %1;" : "=f"(t) : "f"(u));
+      else t = tanhf(u);
+      const float du = kK * fmaf(3.0f * kC, x2, 1.0f);
+      d[i] *= 0.5f * (1.0f + t) + 0.5f * f[i] * (1.0f - t * t) * du;
+    }
+    store8<T>(dpre + off, d);
+    round8<T>(d);                        // sum what was stored: the same bias gradient a separate pass would give
+  }
+};
+// d(qkv)[B, S, 3, H, D] packed from attention's dq, dk, dv ([B, H, S, D] with arbitrary b/h/s strides, d contiguous)
+// and summed over (b, s): replaces the stack/cat kernel of unbind's backward AND c_attn's bias-gradient pass.
+template <typename T>
+struct QkvPackSource {
+  const T* __restrict__ src[3];
+  int64_t sb[3], sh[3], ss[3];
+  T* __restrict__ out;                   // [B*S, 3*H*D]
+  int S, H, D, cols;
+  __device__ __forceinline__ void fetch(int64_t r, int cg, float (&v)[8]) const {
+    const int col = cg * 8;
+    const int hd = H * D;
+    const int t = col / hd, rem = col - t * hd;
+    const int h = rem / D, d = rem - h * D;
+    const int64_t b = r / S, s = r - b * S;
+    // selects, not indexing: a runtime index would put the parameter arrays in local memory
+    const T* base = t == 0 ? src[0] : (t == 1 ? src[1] : src[2]);
+    const int64_t ob = t == 0 ? sb[0] : (t == 1 ? sb[1] : sb[2]);
+    const int64_t oh = t == 0 ? sh[0] : (t == 1 ? sh[1] : sh[2]);
+    const int64_t os = t == 0 ? ss[0] : (t == 1 ? ss[1] : ss[2]);
+    load8<T>(base + b * ob + h * oh + s * os + d, v);
+    store8<T>(out + r * cols + col, v);
+  }
+};
+
+template <typename T, bool FUSED, typename Source>
+__global__ void __launch_bounds__(256) colsum_kernel(const Source src, float* __restrict__ partial,
                                                      int64_t rows, int cols, unsigned int* __restrict__ tickets,
                                                      T* __restrict__ out, int accumulate) {
   __shared__ float sm[8][32][9];
@@ -32,14 +92,14 @@ __global__ void __launch_bounds__(256) colsum_kernel(const T* __restrict__ x, fl
     int64_t r = (int64_t)blockIdx.y * 8 + rl;
     for (; r + step < rows; r += 2 * step) {      // two rows in flight per thread
       float a[8], b[8];
-      load8<T>(x + r * cols + cg * 8, a);
-      load8<T>(x + (r + step) * cols + cg * 8, b);
+      src.fetch(r, cg, a);
+      src.fetch(r + step, cg, b);
 #pragma unroll
       for (int i = 0; i < 8; ++i) acc[i] += a[i] + b[i];
     }
     if (r < rows) {
       float a[8];
-      load8<T>(x + r * cols + cg * 8, a);
+      src.fetch(r, cg, a);
 #pragma unroll
       for (int i = 0; i < 8; ++i) acc[i] += a[i];
     }
@@ -108,7 +168,8 @@ extern "C" int dlion_colsum(const void* x, int64_t rows, int cols, float* partia
   if (rows == 0) return 0;
   const dim3 grid((cols + 255) / 256, dlion_colsum_parts(rows, cols));
   cudaStream_t s = (cudaStream_t)stream;
-  DISPATCH_DTYPE(dtype, (colsum_kernel<T, false><<<grid, 256, 0, s>>>((const T*)x, partial, rows, cols, nullptr, nullptr, 0)));
+  DISPATCH_DTYPE(dtype, (colsum_kernel<T, false, PlainSource<T>><<<grid, 256, 0, s>>>(PlainSource<T>{(const T*)x, cols},
+                                                                                     partial, rows, cols, nullptr, nullptr, 0)));
   return DLION_LAUNCH_CHECK("dlion_colsum");
 }
 
@@ -121,7 +182,51 @@ extern "C" int dlion_colsum_fused(const void* x, int64_t rows, int cols, float* 
                   "dlion_colsum_fused: bad pointers");
   const dim3 grid((cols + 255) / 256, dlion_colsum_parts(rows, cols));
   cudaStream_t s = (cudaStream_t)stream;
-  DISPATCH_DTYPE(dtype, (colsum_kernel<T, true><<<grid, 256, 0, s>>>((const T*)x, partial, rows, cols, tickets, (T*)out,
-                                                                     accumulate)));
+  DISPATCH_DTYPE(dtype, (colsum_kernel<T, true, PlainSource<T>><<<grid, 256, 0, s>>>(PlainSource<T>{(const T*)x, cols},
+                                                                                    partial, rows, cols, tickets, (T*)out,
+                                                                                    accumulate)));
   return DLION_LAUNCH_CHECK("dlion_colsum_fused");
+}
+
+extern "C" int dlion_gelu_tanh_bwd_colsum(const void* pre, const void* dy, void* dpre, int64_t rows, int cols,
+                                          float* partial, unsigned int* tickets, void* out, int accumulate, int dtype,
+                                          void* stream) {
+  DLION_CHECK_ARG(rows > 0 && cols > 0 && (cols & 7) == 0, "dlion_gelu_tanh_bwd_colsum: cols (%d) must be a positive multiple of 8", cols);
+  DLION_CHECK_ARG(aligned16(pre) && aligned16(dy) && aligned16(dpre) && partial != nullptr && tickets != nullptr && out != nullptr,
+                  "dlion_gelu_tanh_bwd_colsum: bad pointers");
+  const dim3 grid((cols + 255) / 256, dlion_colsum_parts(rows, cols));
+  cudaStream_t s = (cudaStream_t)stream;
+  DISPATCH_DTYPE(dtype, (colsum_kernel<T, true, GeluBwdSource<T>><<<grid, 256, 0, s>>>(
+                            GeluBwdSource<T>{(const T*)pre, (const T*)dy, (T*)dpre, cols}, partial, rows, cols, tickets,
+                            (T*)out, accumulate)));
+  return DLION_LAUNCH_CHECK("dlion_gelu_tanh_bwd_colsum");
+}
+
+extern "C" int dlion_qkv_pack_colsum(const void* dq, const void* dk, const void* dv, const int64_t* strides_bhs,
+                                     void* dqkv, int batch, int seq, int heads, int head_dim, float* partial,
+                                     unsigned int* tickets, void* out, int accumulate, int dtype, void* stream) {
+  const int cols = 3 * heads * head_dim;
+  const int64_t rows = (int64_t)batch * seq;
+  DLION_CHECK_ARG(rows > 0 && heads > 0 && head_dim > 0 && (head_dim & 7) == 0,
+                  "dlion_qkv_pack_colsum: head_dim (%d) must be a positive multiple of 8", head_dim);
+  DLION_CHECK_ARG(aligned16(dq) && aligned16(dk) && aligned16(dv) && aligned16(dqkv) && strides_bhs != nullptr &&
+                      partial != nullptr && tickets != nullptr && out != nullptr,
+                  "dlion_qkv_pack_colsum: bad pointers");
+  for (int i = 0; i < 9; ++i)
+    DLION_CHECK_ARG((strides_bhs[i] & 7) == 0, "dlion_qkv_pack_colsum: strides must be multiples of 8 elements");
+  const dim3 grid((cols + 255) / 256, dlion_colsum_parts(rows, cols));
+  cudaStream_t s = (cudaStream_t)stream;
+  DISPATCH_DTYPE(dtype, {
+    QkvPackSource<T> src;
+    const void* ptrs[3] = {dq, dk, dv};
+    for (int t = 0; t < 3; ++t) {
+      src.src[t] = (const T*)ptrs[t];
+      src.sb[t] = strides_bhs[3 * t];
+      src.sh[t] = strides_bhs[3 * t + 1];
+      src.ss[t] = strides_bhs[3 * t + 2];
+    }
+    src.out = (T*)dqkv; src.S = seq; src.H = heads; src.D = head_dim; src.cols = cols;
+    colsum_kernel<T, true, QkvPackSource<T>><<<grid, 256, 0, s>>>(src, partial, rows, cols, tickets, (T*)out, accumulate);
+  });
+  return DLION_LAUNCH_CHECK("dlion_qkv_pack_colsum");
 }

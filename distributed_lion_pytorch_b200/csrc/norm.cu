@@ -201,24 +201,33 @@ __device__ __forceinline__ void block_allreduce_sum_n(float (&v)[NV], float* sme
 constexpr int bwd_ctas_per_sm(int vpt, int block) {
   return vpt == 1 ? (1024 / block > 16 ? 16 : 1024 / block) : (vpt == 2 ? 3 : 2);
 }
+// with the dx column sums riding along (8 more accumulators per thread) the narrow-row kernel gets the registers
+// of one CTA in five back, so that nothing spills
+constexpr int bwd_ctas_per_sm_dxs(int vpt, int block) {
+  return vpt == 1 ? (bwd_ctas_per_sm(vpt, block) * 4 + 4) / 5 : bwd_ctas_per_sm(vpt, block);
+}
 
-template <typename T, int VPT, int BLOCK, bool RMS, int ROWS, bool DROP>
-__global__ void __launch_bounds__(BLOCK, bwd_ctas_per_sm(VPT, BLOCK)) norm_bwd_kernel(const T* __restrict__ dy, const T* __restrict__ dsum_in,
+template <typename T, int VPT, int BLOCK, bool RMS, int ROWS, bool DROP, bool DXS>
+__global__ void __launch_bounds__(BLOCK, DXS ? bwd_ctas_per_sm_dxs(VPT, BLOCK) : bwd_ctas_per_sm(VPT, BLOCK)) norm_bwd_kernel(const T* __restrict__ dy, const T* __restrict__ dsum_in,
                                                          const T* __restrict__ xs, const T* __restrict__ w,
                                                          const float* __restrict__ mean_in,
                                                          const float* __restrict__ rstd_in, T* __restrict__ dx,
                                                          T* __restrict__ dres, float* __restrict__ dw_part,
-                                                         float* __restrict__ db_part, int64_t rows, int cols,
+                                                         float* __restrict__ db_part, float* __restrict__ dxs_part,
+                                                         int64_t rows, int cols,
                                                          float inv_keep, uint32_t thr16, uint64_t seed) {
   __shared__ float red[2 * ROWS * 32];
   const int nvec = cols >> 3;
   float wv[VPT][8], dwv[VPT][8], dbv[VPT][8];
+  // column sums of dx, the gradient handed to the layer that produced x: when that layer is a biased linear
+  // (GPT-2's attn.c_proj / mlp.c_proj) they ARE its bias gradient, so its own pass over dx disappears
+  float dxv[VPT][8];
 #pragma unroll
   for (int k = 0; k < VPT; ++k) {
     const int j = threadIdx.x + k * BLOCK;
     if (j < nvec) load8<T>(w + j * 8, wv[k]);
 #pragma unroll
-    for (int i = 0; i < 8; ++i) dwv[k][i] = 0.f, dbv[k][i] = 0.f;
+    for (int i = 0; i < 8; ++i) dwv[k][i] = 0.f, dbv[k][i] = 0.f, dxv[k][i] = 0.f;
   }
   const float inv_cols = 1.0f / (float)cols;
   for (int64_t row0 = (int64_t)blockIdx.x * ROWS; row0 < rows; row0 += (int64_t)gridDim.x * ROWS) {
@@ -277,6 +286,10 @@ __global__ void __launch_bounds__(BLOCK, bwd_ctas_per_sm(VPT, BLOCK)) norm_bwd_k
             for (int i = 0; i < 8; ++i) o[i] = ((keep >> i) & 1u) ? o[i] * inv_keep : 0.f;
           }
           store8<T>(dx + row * cols + j * 8, o);
+          if (DXS) {
+#pragma unroll
+            for (int i = 0; i < 8; ++i) dxv[k][i] += o[i];
+          }
         }
       }
     }
@@ -285,6 +298,11 @@ __global__ void __launch_bounds__(BLOCK, bwd_ctas_per_sm(VPT, BLOCK)) norm_bwd_k
   for (int k = 0; k < VPT; ++k) {
     const int j = threadIdx.x + k * BLOCK;
     if (j < nvec) {
+      if (DXS) {
+        float* dxp = dxs_part + (int64_t)blockIdx.x * cols + j * 8;
+        reinterpret_cast<float4*>(dxp)[0] = make_float4(dxv[k][0], dxv[k][1], dxv[k][2], dxv[k][3]);
+        reinterpret_cast<float4*>(dxp)[1] = make_float4(dxv[k][4], dxv[k][5], dxv[k][6], dxv[k][7]);
+      }
       float* dwp = dw_part + (int64_t)blockIdx.x * cols + j * 8;
       reinterpret_cast<float4*>(dwp)[0] = make_float4(dwv[k][0], dwv[k][1], dwv[k][2], dwv[k][3]);
       reinterpret_cast<float4*>(dwp)[1] = make_float4(dwv[k][4], dwv[k][5], dwv[k][6], dwv[k][7]);
@@ -304,12 +322,14 @@ __global__ void __launch_bounds__(BLOCK, bwd_ctas_per_sm(VPT, BLOCK)) norm_bwd_k
 template <typename T>
 __global__ void __launch_bounds__(1024) norm_bwd_finalize_kernel(const float* __restrict__ dw_part,
                                                                  const float* __restrict__ db_part,
-                                                                 T* __restrict__ dw, T* __restrict__ db, int parts,
+                                                                 const float* __restrict__ dxs_part,
+                                                                 T* __restrict__ dw, T* __restrict__ db,
+                                                                 T* __restrict__ dxs, int parts,
                                                                  int cols, int acc_mask) {
-  __shared__ float4 sw[128][8], sb[128][8];
+  __shared__ float4 sw[128][8], sb[128][8], sx[128][8];
   const int tx = threadIdx.x, ty = threadIdx.y;
   const int c0 = blockIdx.x * 32 + tx * 4;
-  float4 aw = make_float4(0.f, 0.f, 0.f, 0.f), ab = aw;
+  float4 aw = make_float4(0.f, 0.f, 0.f, 0.f), ab = aw, ax = aw;
   if (c0 < cols) {
     for (int r = ty; r < parts; r += 128) {
       const float4 v = *reinterpret_cast<const float4*>(dw_part + (int64_t)r * cols + c0);
@@ -318,10 +338,15 @@ __global__ void __launch_bounds__(1024) norm_bwd_finalize_kernel(const float* __
         const float4 u = *reinterpret_cast<const float4*>(db_part + (int64_t)r * cols + c0);
         ab.x += u.x; ab.y += u.y; ab.z += u.z; ab.w += u.w;
       }
+      if (dxs_part != nullptr) {
+        const float4 u = *reinterpret_cast<const float4*>(dxs_part + (int64_t)r * cols + c0);
+        ax.x += u.x; ax.y += u.y; ax.z += u.z; ax.w += u.w;
+      }
     }
   }
   sw[ty][tx] = aw;
   sb[ty][tx] = ab;
+  sx[ty][tx] = ax;
   __syncthreads();
   for (int half = 64; half > 0; half >>= 1) {      // tree over the 128 row lanes
     if (ty < half) {
@@ -329,10 +354,23 @@ __global__ void __launch_bounds__(1024) norm_bwd_finalize_kernel(const float* __
       sw[ty][tx] = make_float4(a.x + b2.x, a.y + b2.y, a.z + b2.z, a.w + b2.w);
       a = sb[ty][tx]; b2 = sb[ty + half][tx];
       sb[ty][tx] = make_float4(a.x + b2.x, a.y + b2.y, a.z + b2.z, a.w + b2.w);
+      if (dxs_part != nullptr) {
+        a = sx[ty][tx]; b2 = sx[ty + half][tx];
+        sx[ty][tx] = make_float4(a.x + b2.x, a.y + b2.y, a.z + b2.z, a.w + b2.w);
+      }
     }
     __syncthreads();
   }
   if (ty == 0 && c0 < cols) {
+    if (dxs != nullptr && dxs_part != nullptr) {
+      float4 x4 = sx[0][tx];
+      if (acc_mask & 4) {
+        x4.x += DT<T>::to_f(dxs[c0]); x4.y += DT<T>::to_f(dxs[c0 + 1]);
+        x4.z += DT<T>::to_f(dxs[c0 + 2]); x4.w += DT<T>::to_f(dxs[c0 + 3]);
+      }
+      dxs[c0] = DT<T>::from_f(x4.x); dxs[c0 + 1] = DT<T>::from_f(x4.y);
+      dxs[c0 + 2] = DT<T>::from_f(x4.z); dxs[c0 + 3] = DT<T>::from_f(x4.w);
+    }
     float4 a = sw[0][tx], b2 = sb[0][tx];
     if (acc_mask & 1) {     // accumulate into the existing gradient: one fp32 add, one rounding (no add kernel later)
       a.x += DT<T>::to_f(dw[c0]); a.y += DT<T>::to_f(dw[c0 + 1]);
@@ -398,16 +436,34 @@ static int bwd_max_parts(int cols) {
 
 template <typename T, int VPT, int BLOCK>
 static int launch_bwd(const void* dy, const void* dsum_in, const void* xs, const void* w, const float* mean,
-                      const float* rstd, void* dx, void* dres, float* dwp, float* dbp, int64_t rows, int cols, int rms,
-                      DropArgs d, cudaStream_t s) {
-  const int rows_per_trip = bwd_rows_per_trip(cols);
+                      const float* rstd, void* dx, void* dres, float* dwp, float* dbp, float* dxsp, int64_t rows, int cols,
+                      int rms, DropArgs d, cudaStream_t s) {
+  const bool dxs = dxsp != nullptr;
+  const int rows_per_trip = dxs ? 1 : bwd_rows_per_trip(cols);
   const int64_t trips = (rows + rows_per_trip - 1) / rows_per_trip;
-  const int cap = kNumSMs * bwd_ctas_per_sm(VPT, BLOCK);
+  const int cap = kNumSMs * (dxs ? bwd_ctas_per_sm_dxs(VPT, BLOCK) : bwd_ctas_per_sm(VPT, BLOCK));
   const int grid = (int)(trips < cap ? trips : cap);
+  if (dxs) {          // LayerNorm with narrow rows only (dlion_norm_bwd_dxsum_supported): GPT-2's shapes
+    if constexpr (VPT == 1) {
+      if (!rms) {
+        if (d.on)
+          norm_bwd_kernel<T, VPT, BLOCK, false, 1, true, true><<<grid, BLOCK, 0, s>>>(
+              (const T*)dy, (const T*)dsum_in, (const T*)xs, (const T*)w, mean, rstd, (T*)dx, (T*)dres, dwp, dbp, dxsp,
+              rows, cols, d.inv_keep, d.thr16, d.seed);
+        else
+          norm_bwd_kernel<T, VPT, BLOCK, false, 1, false, true><<<grid, BLOCK, 0, s>>>(
+              (const T*)dy, (const T*)dsum_in, (const T*)xs, (const T*)w, mean, rstd, (T*)dx, (T*)dres, dwp, dbp, dxsp,
+              rows, cols, d.inv_keep, d.thr16, d.seed);
+        return DLION_LAUNCH_CHECK("dlion_norm_bwd");
+      }
+    }
+    set_error("dlion_norm_bwd_dxsum: dx column sums are available for LayerNorm with cols <= 2048 only");
+    return DLION_E_UNSUPPORTED;
+  }
 #define DLION_NORM_BWD(RMS_, DROP_, ROWS_)                                                                        \
-  norm_bwd_kernel<T, VPT, BLOCK, RMS_, ROWS_, DROP_><<<grid, BLOCK, 0, s>>>(                                        \
-      (const T*)dy, (const T*)dsum_in, (const T*)xs, (const T*)w, mean, rstd, (T*)dx, (T*)dres, dwp, dbp, rows,    \
-      cols, d.inv_keep, d.thr16, d.seed)
+  norm_bwd_kernel<T, VPT, BLOCK, RMS_, ROWS_, DROP_, false><<<grid, BLOCK, 0, s>>>(                                 \
+      (const T*)dy, (const T*)dsum_in, (const T*)xs, (const T*)w, mean, rstd, (T*)dx, (T*)dres, dwp, dbp, dxsp,    \
+      rows, cols, d.inv_keep, d.thr16, d.seed)
 #define DLION_NORM_BWD_R(RMS_, DROP_)                                                                            \
   do {                                                                                                           \
     if (VPT == 1 && rows_per_trip == 2) DLION_NORM_BWD(RMS_, DROP_, (VPT == 1 ? 2 : 1));                         \
@@ -442,9 +498,9 @@ static int fwd_t(const void* x, const void* res, const void* w, const void* b, v
 }
 template <typename T>
 static int bwd_t(const void* dy, const void* dsum_in, const void* xs, const void* w, const float* mean,
-                 const float* rstd, void* dx, void* dres, float* dwp, float* dbp, int64_t rows, int cols, int rms,
-                 DropArgs d, cudaStream_t s) {
-  NORM_SHAPE_DISPATCH(launch_bwd, dy, dsum_in, xs, w, mean, rstd, dx, dres, dwp, dbp, rows, cols, rms, d, s);
+                 const float* rstd, void* dx, void* dres, float* dwp, float* dbp, float* dxsp, int64_t rows, int cols,
+                 int rms, DropArgs d, cudaStream_t s) {
+  NORM_SHAPE_DISPATCH(launch_bwd, dy, dsum_in, xs, w, mean, rstd, dx, dres, dwp, dbp, dxsp, rows, cols, rms, d, s);
 }
 
 static DropArgs make_drop(float p, uint64_t seed) {
@@ -494,14 +550,31 @@ extern "C" int dlion_norm_bwd_parts(int64_t rows, int cols) {
   return (int)(trips < cap ? trips : cap);
 }
 
+extern "C" int dlion_norm_bwd_dxsum_supported(int cols, int rms) { return !rms && (cols >> 3) <= 256 ? 1 : 0; }
+
+extern "C" int dlion_norm_bwd_dxsum_parts(int64_t rows, int cols) {      // mirrors launch_bwd's dxs branch
+  int vpt, block;
+  norm_shape(cols, &vpt, &block);
+  const int cap = kNumSMs * bwd_ctas_per_sm_dxs(vpt, block);
+  return (int)(rows < cap ? rows : cap);
+}
+
 extern "C" int dlion_norm_bwd(const void* dy, const void* dsum_in, const void* xsum, const void* weight,
                               const float* mean, const float* rstd, void* dx, void* dres, float* dw_partial,
                               float* db_partial, int64_t rows, int cols, int rms, float drop_p, uint64_t drop_seed,
                               int dtype, void* stream) {
+  return dlion_norm_bwd_dxsum(dy, dsum_in, xsum, weight, mean, rstd, dx, dres, dw_partial, db_partial, nullptr, rows,
+                              cols, rms, drop_p, drop_seed, dtype, stream);
+}
+
+extern "C" int dlion_norm_bwd_dxsum(const void* dy, const void* dsum_in, const void* xsum, const void* weight,
+                                    const float* mean, const float* rstd, void* dx, void* dres, float* dw_partial,
+                                    float* db_partial, float* dxs_partial, int64_t rows, int cols, int rms, float drop_p,
+                                    uint64_t drop_seed, int dtype, void* stream) {
   DLION_CHECK_ARG(rows >= 0 && cols > 0 && (cols & 7) == 0, "dlion_norm_bwd: cols (%d) must be a positive multiple of 8",
                   cols);
   DLION_CHECK_ARG(aligned16(dy) && aligned16(dsum_in) && aligned16(xsum) && aligned16(weight) && aligned16(dx) &&
-                      aligned16(dres) && aligned16(dw_partial) && aligned16(db_partial),
+                      aligned16(dres) && aligned16(dw_partial) && aligned16(db_partial) && aligned16(dxs_partial),
                   "dlion_norm_bwd: pointers must be 16-byte aligned");
   DLION_CHECK_ARG(drop_p >= 0.f && drop_p < 1.f, "dlion_norm_bwd: dropout probability %f outside [0, 1)", drop_p);
   if (rows == 0) return 0;
@@ -509,28 +582,38 @@ extern "C" int dlion_norm_bwd(const void* dy, const void* dsum_in, const void* x
   const DropArgs d = make_drop(drop_p, drop_seed);
   switch (dtype) {
     case DLION_F32:
-      return bwd_t<float>(dy, dsum_in, xsum, weight, mean, rstd, dx, dres, dw_partial, db_partial, rows, cols, rms, d, s);
+      return bwd_t<float>(dy, dsum_in, xsum, weight, mean, rstd, dx, dres, dw_partial, db_partial, dxs_partial, rows,
+                          cols, rms, d, s);
     case DLION_BF16:
-      return bwd_t<__nv_bfloat16>(dy, dsum_in, xsum, weight, mean, rstd, dx, dres, dw_partial, db_partial, rows, cols,
-                                  rms, d, s);
+      return bwd_t<__nv_bfloat16>(dy, dsum_in, xsum, weight, mean, rstd, dx, dres, dw_partial, db_partial, dxs_partial,
+                                  rows, cols, rms, d, s);
     case DLION_F16:
-      return bwd_t<__half>(dy, dsum_in, xsum, weight, mean, rstd, dx, dres, dw_partial, db_partial, rows, cols, rms, d,
-                           s);
+      return bwd_t<__half>(dy, dsum_in, xsum, weight, mean, rstd, dx, dres, dw_partial, db_partial, dxs_partial, rows,
+                           cols, rms, d, s);
   }
   set_error("dlion_norm_bwd: unsupported dtype %d", dtype);
   return DLION_E_UNSUPPORTED;
 }
 
-extern "C" int dlion_norm_bwd_finalize_acc(const float* dw_partial, const float* db_partial, void* dweight,
-                                           void* dbias, int parts, int cols, int acc_mask, int dtype, void* stream) {
+extern "C" int dlion_norm_bwd_finalize_dxsum(const float* dw_partial, const float* db_partial,
+                                             const float* dxs_partial, void* dweight, void* dbias, void* dxsum,
+                                             int parts, int cols, int acc_mask, int dtype, void* stream) {
   DLION_CHECK_ARG(parts > 0 && cols > 0 && (cols & 3) == 0 && dw_partial && dweight,
                   "dlion_norm_bwd_finalize: bad arguments");
+  DLION_CHECK_ARG((dxs_partial == nullptr) == (dxsum == nullptr), "dlion_norm_bwd_finalize: dxs_partial and dxsum go together");
   cudaStream_t s = (cudaStream_t)stream;
   const dim3 block(8, 128);
   const int grid = (cols + 31) / 32;
-  DISPATCH_DTYPE(dtype, norm_bwd_finalize_kernel<T><<<grid, block, 0, s>>>(dw_partial, db_partial, (T*)dweight,
-                                                                             (T*)dbias, parts, cols, acc_mask));
+  DISPATCH_DTYPE(dtype, norm_bwd_finalize_kernel<T><<<grid, block, 0, s>>>(dw_partial, db_partial, dxs_partial,
+                                                                             (T*)dweight, (T*)dbias, (T*)dxsum, parts,
+                                                                             cols, acc_mask));
   return DLION_LAUNCH_CHECK("dlion_norm_bwd_finalize");
+}
+
+extern "C" int dlion_norm_bwd_finalize_acc(const float* dw_partial, const float* db_partial, void* dweight,
+                                           void* dbias, int parts, int cols, int acc_mask, int dtype, void* stream) {
+  return dlion_norm_bwd_finalize_dxsum(dw_partial, db_partial, nullptr, dweight, dbias, nullptr, parts, cols, acc_mask,
+                                       dtype, stream);
 }
 
 extern "C" int dlion_norm_bwd_finalize(const float* dw_partial, const float* db_partial, void* dweight, void* dbias,

@@ -23,6 +23,7 @@ from ..ops.cross_entropy import linear_cross_entropy, linear_log_probs
 from ..ops.linear import fused_linear
 from ..ops.lt_gemm import linear_gelu
 from ..ops.norm import add_layer_norm
+from ..ops.qkv import split_qkv
 from .common import CausalLMOutput, ConfigBase, PreTrainedMixin, shift_labels
 
 
@@ -83,9 +84,10 @@ class LayerNormParams(nn.Module):
         self.bias = nn.Parameter(torch.zeros(n))
         self.eps = eps
 
-    def forward(self, x, residual=None, dropout_p: float = 0.0):
-        """LayerNorm(dropout(x) + residual); the dropout of the branch output is fused in."""
-        return add_layer_norm(x, residual, self.weight, self.bias, self.eps, dropout_p, self.training)
+    def forward(self, x, residual=None, dropout_p: float = 0.0, x_bias=None):
+        """LayerNorm(dropout(x) + residual); the dropout of the branch output is fused in.  ``x_bias``: the bias of
+        the linear layer that produced ``x`` — its gradient falls out of this norm's backward pass."""
+        return add_layer_norm(x, residual, self.weight, self.bias, self.eps, dropout_p, self.training, x_bias)
 
 
 class GPT2Attention(nn.Module):
@@ -98,8 +100,8 @@ class GPT2Attention(nn.Module):
 
     def forward(self, x, attn_mask=None):
         B, S, E = x.shape
-        # unbind (backward = one stack) rather than three selects (backward = 3 zero-fills + 3 copies + 2 adds)
-        q, k, v = (t.transpose(1, 2) for t in self.c_attn(x).view(B, S, 3, self.n_head, self.head_dim).unbind(2))
+        # views in forward; in backward ONE kernel packs dq, dk, dv into d(qkv) and reduces c_attn's bias gradient
+        q, k, v = split_qkv(self.c_attn(x), self.n_head, self.c_attn.bias)
         y = F.scaled_dot_product_attention(q, k, v, attn_mask=attn_mask, is_causal=attn_mask is None,
                                            dropout_p=self.attn_pdrop if self.training else 0.0)
         return self.c_proj(y.transpose(1, 2).reshape(B, S, E))
@@ -132,13 +134,15 @@ class GPT2Block(nn.Module):
         self.mlp = GPT2MLP(cfg)
         self.resid_pdrop = cfg.resid_pdrop
 
-    def forward(self, hidden, residual, attn_mask=None, in_dropout: float = 0.0):
+    def forward(self, hidden, residual, attn_mask=None, in_dropout: float = 0.0, in_bias=None):
         """(branch output, residual stream) in → same out.  The residual add AND the dropout of the
         incoming branch output live inside the norm kernel; this block's own MLP output is returned
-        un-dropped and is dropped by whoever normalises it next (the next block's ln_1, or ln_f)."""
-        x, residual = self.ln_1(hidden, residual, in_dropout)
+        un-dropped and is dropped by whoever normalises it next (the next block's ln_1, or ln_f).
+        ``in_bias``: the bias of the layer that produced ``hidden`` (the previous block's ``mlp.c_proj``): the
+        norm backward reduces its gradient on the way."""
+        x, residual = self.ln_1(hidden, residual, in_dropout, in_bias)
         a = self.attn(x, attn_mask)
-        x, residual = self.ln_2(a, residual, self.resid_pdrop)
+        x, residual = self.ln_2(a, residual, self.resid_pdrop, self.attn.c_proj.bias)
         return self.mlp(x), residual
 
 
@@ -193,13 +197,15 @@ class GPT2LMHeadModel(nn.Module, PreTrainedMixin):
             mask = causal[None, None] & attention_mask[:, None, None, :].bool()
         hidden, residual = h, None
         p_in = t.embd_pdrop                      # layer 0 drops the embedding sum, later layers the previous MLP output
+        b_in = None                              # bias of the linear that produced `hidden` (none for the embeddings)
         for blk in t.h:
             if self.gradient_checkpointing and self.training:
-                hidden, residual = checkpoint(blk, hidden, residual, mask, p_in, use_reentrant=False)
+                hidden, residual = checkpoint(blk, hidden, residual, mask, p_in, b_in, use_reentrant=False)
             else:
-                hidden, residual = blk(hidden, residual, mask, p_in)
+                hidden, residual = blk(hidden, residual, mask, p_in, b_in)
             p_in = blk.resid_pdrop
-        out, _ = t.ln_f(hidden, residual, p_in)
+            b_in = blk.mlp.c_proj.bias
+        out, _ = t.ln_f(hidden, residual, p_in, b_in)
         return out
 
     def forward(self, input_ids, labels=None, attention_mask=None, return_logits: Optional[bool] = None, **_):

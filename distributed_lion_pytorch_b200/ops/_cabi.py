@@ -96,6 +96,12 @@ def _declare(L: C.CDLL) -> None:
         "dlion_colsum_tiles": [i32],
         "dlion_colsum_fused": [vp, i64, i32, vp, vp, vp, i32, i32, vp],
         "dlion_norm_bwd_finalize_acc": [vp, vp, vp, vp, i32, i32, i32, i32, vp],
+        "dlion_gelu_tanh_bwd_colsum": [vp, vp, vp, i64, i32, vp, vp, vp, i32, i32, vp],
+        "dlion_qkv_pack_colsum": [vp, vp, vp, C.POINTER(i64), vp, i32, i32, i32, i32, vp, vp, vp, i32, i32, vp],
+        "dlion_norm_bwd_dxsum_supported": [i32, i32],
+        "dlion_norm_bwd_dxsum_parts": [i64, i32],
+        "dlion_norm_bwd_dxsum": [vp, vp, vp, vp, vp, vp, vp, vp, vp, vp, vp, i64, i32, i32, f32, u64, i32, vp],
+        "dlion_norm_bwd_finalize_dxsum": [vp, vp, vp, vp, vp, vp, i32, i32, i32, i32, vp],
         "dlion_gelu_tanh_fwd": [vp, vp, i64, i32, vp],
         "dlion_gelu_tanh_bwd": [vp, vp, vp, i64, i32, vp],
         "dlion_swiglu_fwd": [vp, vp, vp, i64, i32, vp],

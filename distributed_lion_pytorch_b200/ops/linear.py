@@ -71,9 +71,39 @@ def column_sum(dy2: torch.Tensor, out_dtype: torch.dtype, accumulate_into: Optio
     return out
 
 
-def bias_grad(dy2: torch.Tensor, bias: torch.Tensor):
+HANDOFFS = 0      # bias gradients that arrived ready-made with the incoming gradient (tests read this)
+
+
+def attach_column_sums(grad: torch.Tensor, bias: torch.Tensor, sums: torch.Tensor) -> None:
+    """Producer side of the bias-gradient hand-off: a backward kernel that already has ``grad`` in registers (the
+    norm backward for the linear in front of it, the qkv packer for ``c_attn``) also reduced it over rows; the sums
+    travel WITH the gradient tensor, as a Python attribute, to the backward of the linear that owns ``bias``.
+    If autograd hands that linear a different tensor object (it had to add several gradients, say), the attribute
+    is simply not there and the linear reduces ``grad`` itself — never both."""
+    grad._dlion_colsum = (id(bias), sums)
+
+
+def _take_column_sums(dy: torch.Tensor, bias: torch.Tensor) -> Optional[torch.Tensor]:
+    tag = getattr(dy, "_dlion_colsum", None)
+    if tag is None or tag[0] != id(bias) or tag[1].shape != bias.shape or tag[1].dtype != bias.dtype:
+        return None
+    global HANDOFFS
+    HANDOFFS += 1
+    return tag[1]
+
+
+def bias_grad(dy2: torch.Tensor, bias: torch.Tensor, dy: Optional[torch.Tensor] = None):
     """Gradient of a bias added to every row of the tensor whose gradient is ``dy2``: accumulated straight into
-    ``bias.grad`` when that buffer exists (returns ``None``), returned otherwise."""
+    ``bias.grad`` when that buffer exists (returns ``None``), returned otherwise.  ``dy`` is the gradient tensor as
+    autograd delivered it (``dy2`` may be a reshaped view): if its producer attached the column sums, no pass over
+    ``dy2`` is made at all."""
+    ready = _take_column_sums(dy, bias) if dy is not None else None
+    if ready is not None:
+        if _can_accumulate(bias, dy2) and bias.grad.shape == ready.shape:
+            mark_grad_written(bias)
+            bias.grad.add_(ready)
+            return None
+        return ready
     if _can_accumulate(bias, dy2) and bias.grad.shape == (dy2.shape[1],):
         mark_grad_written(bias)
         return column_sum(dy2, bias.dtype, accumulate_into=bias.grad)
@@ -125,7 +155,7 @@ class _FusedLinear(torch.autograd.Function):
             else:
                 dw = x2.t() @ dy2 if ctx.in_out else dy2.t() @ x2
         if bias is not None and ctx.needs_input_grad[2]:
-            db = bias_grad(dy2, bias)                        # one launch: column sums folded and added into bias.grad
+            db = bias_grad(dy2, bias, dy)                    # ready-made, or one launch folded and added into bias.grad
         return dx, dw, db, None
 
 

@@ -110,10 +110,33 @@ class _LinearGelu(torch.autograd.Function):
         if not d2.is_contiguous():
             d2 = d2.contiguous()
         dpre = torch.empty_like(pre)
-        with torch.cuda.device(pre.device):
-            _cabi.check(_cabi.lib().dlion_gelu_tanh_bwd(pre.data_ptr(), d2.data_ptr(), dpre.data_ptr(), pre.numel(),
-                                                        _cabi.dtype_code(pre.dtype), _cabi.stream_ptr(pre.device)), "gelu_bwd")
         dx = dw = db = None
+        want_db = ctx.needs_input_grad[2]
+        from . import linear as _lin
+        rows, cols = pre.shape
+        fuse_db = want_db and _lin._FUSE_COLSUM and cols % 8 == 0 \
+            and int(_cabi.lib().dlion_colsum_tiles(cols)) <= _lin._MAX_TILES and bias.dtype == pre.dtype
+        with torch.cuda.device(pre.device):
+            if fuse_db:
+                # d(pre) and the c_fc bias gradient from ONE pass over dY (the column sums are reduced while the
+                # activation backward has the values in registers)
+                L = _cabi.lib()
+                acc = _can_accumulate(bias, dpre) and bias.grad.shape == (cols,)
+                out = bias.grad if acc else torch.empty(cols, dtype=bias.dtype, device=pre.device)
+                partial = torch.empty(int(L.dlion_colsum_parts(rows, cols)), cols, dtype=torch.float32, device=pre.device)
+                if acc:
+                    from . import mark_grad_written
+                    mark_grad_written(bias)
+                _cabi.check(L.dlion_gelu_tanh_bwd_colsum(pre.data_ptr(), d2.data_ptr(), dpre.data_ptr(), rows, cols,
+                                                         partial.data_ptr(), _lin._tickets(pre.device).data_ptr(),
+                                                         out.data_ptr(), int(acc), _cabi.dtype_code(pre.dtype),
+                                                         _cabi.stream_ptr(pre.device)), "gelu_bwd_colsum")
+                db = None if acc else out
+                want_db = False
+            else:
+                _cabi.check(_cabi.lib().dlion_gelu_tanh_bwd(pre.data_ptr(), d2.data_ptr(), dpre.data_ptr(), pre.numel(),
+                                                            _cabi.dtype_code(pre.dtype), _cabi.stream_ptr(pre.device)),
+                            "gelu_bwd")
         if ctx.needs_input_grad[0]:
             dx = (dpre @ weight.t()).view(ctx.x_shape)
         if ctx.needs_input_grad[1]:
@@ -123,7 +146,7 @@ class _LinearGelu(torch.autograd.Function):
                 weight.grad.addmm_(x2.t(), dpre)
             else:
                 dw = x2.t() @ dpre
-        if ctx.needs_input_grad[2]:
+        if want_db:
             db = bias_grad(dpre, bias)
         return dx, dw, db
 

@@ -22,7 +22,7 @@ def _use_kernel(x: torch.Tensor) -> bool:
 
 class _FusedNorm(torch.autograd.Function):
     @staticmethod
-    def forward(ctx, x, residual, weight, bias, eps: float, rms: bool, drop_p: float, seed: int):
+    def forward(ctx, x, residual, weight, bias, eps: float, rms: bool, drop_p: float, seed: int, x_bias=None):
         cols = x.shape[-1]
         xc = x.contiguous()
         rc = residual.contiguous() if residual is not None else None
@@ -40,6 +40,10 @@ class _FusedNorm(torch.autograd.Function):
         ctx.save_for_backward(summed, weight, mean, rstd, bias)
         ctx.rms, ctx.has_res, ctx.has_bias = rms, residual is not None, bias is not None
         ctx.drop_p, ctx.seed = float(drop_p), int(seed)
+        # the bias of the linear layer that produced x (if any): its gradient is the column sum of OUR dx
+        ctx.x_bias = x_bias if (x_bias is not None and x_bias.requires_grad and x_bias.shape == (cols,)
+                                and x_bias.dtype == x.dtype
+                                and _cabi.lib().dlion_norm_bwd_dxsum_supported(cols, int(rms))) else None
         ctx.set_materialize_grads(False)      # an unused residual output costs nothing in backward
         return y, summed
 
@@ -53,7 +57,8 @@ class _FusedNorm(torch.autograd.Function):
         dyc = dy.contiguous()
         dsc = dsum.contiguous() if dsum is not None else None
         L = _cabi.lib()
-        parts = int(L.dlion_norm_bwd_parts(rows, cols))
+        xb = ctx.x_bias if ctx.needs_input_grad[0] else None
+        parts = int(L.dlion_norm_bwd_dxsum_parts(rows, cols) if xb is not None else L.dlion_norm_bwd_parts(rows, cols))
         dx = torch.empty_like(summed)
         drop = ctx.drop_p > 0
         dres = torch.empty_like(summed) if (drop and ctx.has_res) else None
@@ -71,20 +76,26 @@ class _FusedNorm(torch.autograd.Function):
             mark_grad_written(bias)
         dw = weight.grad if acc_w else torch.empty_like(weight)
         db = (bias.grad if acc_b else torch.empty_like(weight)) if ctx.has_bias else None
+        dxsp = torch.empty(parts, cols, dtype=torch.float32, device=dy.device) if xb is not None else None
+        dxsum = torch.empty(cols, dtype=weight.dtype, device=dy.device) if xb is not None else None
         with torch.cuda.device(dy.device):
             st = _cabi.stream_ptr(dy.device)
-            _cabi.check(L.dlion_norm_bwd(dyc.data_ptr(), _cabi.ptr(dsc), summed.data_ptr(), weight.data_ptr(),
-                                         _cabi.ptr(mean), rstd.data_ptr(), dx.data_ptr(), _cabi.ptr(dres),
-                                         dwp.data_ptr(), _cabi.ptr(dbp), rows, cols, int(ctx.rms), ctx.drop_p, ctx.seed,
-                                         _cabi.dtype_code(dy.dtype), st), "norm_bwd")
-            _cabi.check(L.dlion_norm_bwd_finalize_acc(dwp.data_ptr(), _cabi.ptr(dbp), dw.data_ptr(), _cabi.ptr(db),
-                                                      parts, cols, int(acc_w) | (int(acc_b) << 1),
-                                                      _cabi.dtype_code(weight.dtype), st), "norm_bwd_finalize")
+            _cabi.check(L.dlion_norm_bwd_dxsum(dyc.data_ptr(), _cabi.ptr(dsc), summed.data_ptr(), weight.data_ptr(),
+                                               _cabi.ptr(mean), rstd.data_ptr(), dx.data_ptr(), _cabi.ptr(dres),
+                                               dwp.data_ptr(), _cabi.ptr(dbp), _cabi.ptr(dxsp), rows, cols, int(ctx.rms),
+                                               ctx.drop_p, ctx.seed, _cabi.dtype_code(dy.dtype), st), "norm_bwd")
+            _cabi.check(L.dlion_norm_bwd_finalize_dxsum(dwp.data_ptr(), _cabi.ptr(dbp), _cabi.ptr(dxsp), dw.data_ptr(),
+                                                        _cabi.ptr(db), _cabi.ptr(dxsum), parts, cols,
+                                                        int(acc_w) | (int(acc_b) << 1), _cabi.dtype_code(weight.dtype),
+                                                        st), "norm_bwd_finalize")
+        if xb is not None:
+            from .linear import attach_column_sums
+            attach_column_sums(dx, xb, dxsum)        # rides with dx to the backward of the linear that produced x
         if ctx.has_res:
             g_res = dres if drop else dx
         else:
             g_res = None
-        return dx, g_res, (None if acc_w else dw), (None if acc_b else db), None, None, None, None
+        return dx, g_res, (None if acc_w else dw), (None if acc_b else db), None, None, None, None, None
 
 
 def _draw_seed() -> int:
@@ -107,11 +118,16 @@ def _ref_norm(x, residual, weight, bias, eps, rms, drop_p=0.0):
 
 def add_layer_norm(x: torch.Tensor, residual: Optional[torch.Tensor], weight: torch.Tensor,
                    bias: Optional[torch.Tensor], eps: float = 1e-5, dropout_p: float = 0.0,
-                   training: bool = False) -> Tuple[torch.Tensor, torch.Tensor]:
-    """``s = dropout(x) + residual``; returns ``(LayerNorm(s), s)``.  One kernel on CUDA."""
+                   training: bool = False, x_bias: Optional[torch.Tensor] = None) -> Tuple[torch.Tensor, torch.Tensor]:
+    """``s = dropout(x) + residual``; returns ``(LayerNorm(s), s)``.  One kernel on CUDA.
+
+    ``x_bias``: the bias parameter of the linear layer whose output ``x`` is (GPT-2: ``attn.c_proj`` in front of
+    ``ln_2``, ``mlp.c_proj`` in front of the next ``ln_1`` / ``ln_f``).  The backward kernel then also reduces dx
+    over rows — that IS that bias's gradient — and hands it over with dx, so the linear's backward makes no pass
+    of its own over dx."""
     p = float(dropout_p) if training else 0.0
     if _use_kernel(x):
-        return _FusedNorm.apply(x, residual, weight, bias, eps, False, p, _draw_seed() if p > 0 else 0)
+        return _FusedNorm.apply(x, residual, weight, bias, eps, False, p, _draw_seed() if p > 0 else 0, x_bias)
     return _ref_norm(x, residual, weight, bias, eps, False, p)
 
 

@@ -221,6 +221,21 @@ int dlion_norm_bwd_finalize(const float* dw_partial, const float* db_partial, vo
 int dlion_norm_bwd_finalize_acc(const float* dw_partial, const float* db_partial, void* dweight, void* dbias,
                                 int parts, int cols, int acc_mask, int dtype, void* stream);
 
+/* The same two with one more reduction riding along: dxs_partial[parts, cols] receives per-CTA column sums of dx,
+ * folded by the finalize into dxsum[cols] (bit 2 of acc_mask = accumulate).  dx is the gradient handed to whatever
+ * produced x; when that is a biased linear (GPT-2's attn.c_proj / mlp.c_proj in front of ln_2 / the next ln_1)
+ * dxsum IS its bias gradient and the layer's own pass over dx (`grad_output.sum(0)` in HF's Conv1D backward,
+ * reached from accelerator.backward, async_trainer.py:33) is not needed. */
+int dlion_norm_bwd_dxsum_supported(int cols, int rms);      /* LayerNorm with cols <= 2048 */
+int dlion_norm_bwd_dxsum_parts(int64_t rows, int cols);     /* partial rows written when dxs_partial != NULL */
+int dlion_norm_bwd_dxsum(const void* dy, const void* dsum_in, const void* xsum, const void* weight, const float* mean,
+                         const float* rstd, void* dx, void* dres, float* dw_partial, float* db_partial,
+                         float* dxs_partial, int64_t rows, int cols, int rms, float drop_p, uint64_t drop_seed,
+                         int dtype, void* stream);
+int dlion_norm_bwd_finalize_dxsum(const float* dw_partial, const float* db_partial, const float* dxs_partial,
+                                  void* dweight, void* dbias, void* dxsum, int parts, int cols, int acc_mask, int dtype,
+                                  void* stream);
+
 /* Bias gradient: fp32 partial column sums of x [rows, cols] (cols % 8 == 0) into
  * partial[dlion_colsum_parts(rows, cols)][cols]; fold them with dlion_norm_bwd_finalize
  * (db_partial = NULL).  reference: `grad_output.sum(0)` of every biased Conv1D in HF GPT-2's
@@ -234,6 +249,20 @@ int dlion_colsum(const void* x, int64_t rows, int cols, float* partial, int dtyp
 int dlion_colsum_tiles(int cols);
 int dlion_colsum_fused(const void* x, int64_t rows, int cols, float* partial, unsigned int* tickets, void* out,
                        int accumulate, int dtype, void* stream);
+
+/* Producer + bias-gradient reduction in one pass (same tiling, tickets and partial buffer as dlion_colsum_fused):
+ *   dlion_gelu_tanh_bwd_colsum  dpre = dy * gelu_tanh'(pre) is written AND its column sums land in out[cols] —
+ *                               GPT-2's c_fc bias gradient without a second pass over the [tokens, 4*hidden] tensor;
+ *   dlion_qkv_pack_colsum       d(qkv)[B, S, 3, H, D] is packed from attention's dq / dk / dv ([B, H, S, D] with the
+ *                               element strides strides_bhs[9] = {b, h, s} x {q, k, v}, d contiguous; HOST array) AND
+ *                               its column sums (c_attn's bias gradient) land in out[3*H*D].
+ * reference: the NewGELUActivation / unbind backward kernels followed by `grad_output.sum(0)` of the biased
+ * Conv1D in HF GPT-2's backward, reached from accelerator.backward (async_trainer.py:33). */
+int dlion_gelu_tanh_bwd_colsum(const void* pre, const void* dy, void* dpre, int64_t rows, int cols, float* partial,
+                               unsigned int* tickets, void* out, int accumulate, int dtype, void* stream);
+int dlion_qkv_pack_colsum(const void* dq, const void* dk, const void* dv, const int64_t* strides_bhs, void* dqkv,
+                          int batch, int seq, int heads, int head_dim, float* partial, unsigned int* tickets, void* out,
+                          int accumulate, int dtype, void* stream);
 
 /* MLP activations as single passes over n elements (n % 8 == 0): GPT-2's tanh-form GELU and
  * Llama's silu(gate) * up, forward and backward.
