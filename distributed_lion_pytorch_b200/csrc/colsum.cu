@@ -8,6 +8,8 @@
 // rows are folded by dlion_norm_bwd_finalize's kernel.
 // reference: the `grad_output.sum(0)` of every biased HF GPT-2 Conv1D in backward, reached from
 // accelerator.backward (async_trainer.py:33).
+#include <stdlib.h>
+
 #include "common.cuh"
 
 namespace dlion {
@@ -19,11 +21,58 @@ constexpr int kColsumParts = kNumSMs * 4;
 // needs one launch instead of three (partials, fold, add into .grad).
 // What is being summed.  A source yields the 8 values of (row, 8-column group) and may write a by-product while
 // it has them in registers — the producing elementwise kernel and the bias-gradient reduction become one pass.
+// Ordered 16-byte accesses: `asm volatile` statements keep their program order among themselves, so a batch of
+// these loads stays AHEAD of the first of these stores — ptxas otherwise sinks the later rows' loads below the
+// earlier rows' math to save registers and one row at a time is in flight (measured: 4.2 TB/s).
+__device__ __forceinline__ uint4 ldg_stream16(const void* ptr) {
+  uint4 r;
+  asm volatile("ld.global.L1::no_allocate.v4.u32 {%0, %1, %2, %3}, [%4];"
+               : "=r"(r.x), "=r"(r.y), "=r"(r.z), "=r"(r.w) : "l"(ptr) : "memory");
+  return r;
+}
+__device__ __forceinline__ void stg_stream16(void* ptr, const uint4& v) {
+  asm volatile("st.global.L1::no_allocate.v4.u32 [%0], {%1, %2, %3, %4};" ::"l"(ptr), "r"(v.x), "r"(v.y), "r"(v.z), "r"(v.w)
+               : "memory");
+}
+template <typename T>
+__device__ __forceinline__ Raw8<T> load_stream8(const T* __restrict__ ptr) {
+  Raw8<T> r;
+#pragma unroll
+  for (int i = 0; i < (int)(sizeof(T) * 8 / 16); ++i) r.q[i] = ldg_stream16(reinterpret_cast<const uint4*>(ptr) + i);
+  return r;
+}
+template <typename T>
+__device__ __forceinline__ void store_stream8(T* __restrict__ ptr, const float (&v)[8]) {
+  if constexpr (sizeof(T) == 4) {
+    stg_stream16(ptr, make_uint4(__float_as_uint(v[0]), __float_as_uint(v[1]), __float_as_uint(v[2]), __float_as_uint(v[3])));
+    stg_stream16(ptr + 4, make_uint4(__float_as_uint(v[4]), __float_as_uint(v[5]), __float_as_uint(v[6]), __float_as_uint(v[7])));
+  } else {
+    uint32_t w[4];
+#pragma unroll
+    for (int i = 0; i < 4; ++i) {
+      if constexpr (DT<T>::id == DLION_BF16) {
+        const __nv_bfloat162 h = __floats2bfloat162_rn(v[2 * i], v[2 * i + 1]);
+        w[i] = *reinterpret_cast<const uint32_t*>(&h);
+      } else {
+        const __half2 h = __floats2half2_rn(v[2 * i], v[2 * i + 1]);
+        w[i] = *reinterpret_cast<const uint32_t*>(&h);
+      }
+    }
+    stg_stream16(ptr, make_uint4(w[0], w[1], w[2], w[3]));
+  }
+}
+
+// A source is split in two so that the kernel can put the raw loads of several rows in flight before the first
+// dependent instruction (and before any store: a by-product store between two rows' loads would pin their order):
+//   load(r, cg)            -> Raw   the 16-byte global loads of one (row, column group), nothing else
+//   finish(raw, r, cg, v)           convert / compute, store the by-product, leave the 8 values to sum in v
 template <typename T>
 struct PlainSource {                     // x[rows, cols] as stored
   const T* __restrict__ x;
   int cols;
-  __device__ __forceinline__ void fetch(int64_t r, int cg, float (&v)[8]) const { load8<T>(x + r * cols + cg * 8, v); }
+  struct Raw { Raw8<T> a; };
+  __device__ __forceinline__ Raw load(int64_t r, int cg) const { return Raw{load_stream8<T>(x + r * cols + cg * 8)}; }
+  __device__ __forceinline__ void finish(const Raw& raw, int64_t, int, float (&v)[8]) const { unpack_raw8<T>(raw.a, v); }
 };
 // d(pre) = dy * gelu_tanh'(pre), written to dpre, and summed over rows: GPT-2's c_fc bias gradient falls out of
 // the activation backward (reference: HF NewGELUActivation backward + Conv1D bias grad, two passes over dY there)
@@ -33,12 +82,16 @@ struct GeluBwdSource {
   const T* __restrict__ dy;
   T* __restrict__ dpre;
   int cols;
-  __device__ __forceinline__ void fetch(int64_t r, int cg, float (&d)[8]) const {
+  struct Raw { Raw8<T> x, d; };
+  __device__ __forceinline__ Raw load(int64_t r, int cg) const {
+    const int64_t off = r * cols + cg * 8;
+    return Raw{load_stream8<T>(pre + off), load_stream8<T>(dy + off)};
+  }
+  __device__ __forceinline__ void finish(const Raw& raw, int64_t r, int cg, float (&d)[8]) const {
     constexpr float kK = 0.7978845608028654f, kC = 0.044715f;
     float f[8];
-    const int64_t off = r * cols + cg * 8;
-    load8<T>(pre + off, f);
-    load8<T>(dy + off, d);
+    unpack_raw8<T>(raw.x, f);
+    unpack_raw8<T>(raw.d, d);
 #pragma unroll
     for (int i = 0; i < 8; ++i) {
       const float x2 = f[i] * f[i];
@@ -49,7 +102,7 @@ struct GeluBwdSource {
       const float du = kK * fmaf(3.0f * kC, x2, 1.0f);
       d[i] *= 0.5f * (1.0f + t) + 0.5f * f[i] * (1.0f - t * t) * du;
     }
-    store8<T>(dpre + off, d);
+    store_stream8<T>(dpre + r * cols + cg * 8, d);
     round8<T>(d);                        // sum what was stored: the same bias gradient a separate pass would give
   }
 };
@@ -61,7 +114,8 @@ struct QkvPackSource {
   int64_t sb[3], sh[3], ss[3];
   T* __restrict__ out;                   // [B*S, 3*H*D]
   int S, H, D, cols;
-  __device__ __forceinline__ void fetch(int64_t r, int cg, float (&v)[8]) const {
+  struct Raw { Raw8<T> a; };
+  __device__ __forceinline__ Raw load(int64_t r, int cg) const {
     const int col = cg * 8;
     const int hd = H * D;
     const int t = col / hd, rem = col - t * hd;
@@ -72,13 +126,28 @@ struct QkvPackSource {
     const int64_t ob = t == 0 ? sb[0] : (t == 1 ? sb[1] : sb[2]);
     const int64_t oh = t == 0 ? sh[0] : (t == 1 ? sh[1] : sh[2]);
     const int64_t os = t == 0 ? ss[0] : (t == 1 ? ss[1] : ss[2]);
-    load8<T>(base + b * ob + h * oh + s * os + d, v);
-    store8<T>(out + r * cols + col, v);
+    return Raw{load_stream8<T>(base + b * ob + h * oh + s * os + d)};
+  }
+  __device__ __forceinline__ void finish(const Raw& raw, int64_t r, int cg, float (&v)[8]) const {
+    T* dst = out + r * cols + cg * 8;
+#pragma unroll
+    for (int i = 0; i < (int)(sizeof(T) * 8 / 16); ++i) stg_stream16(reinterpret_cast<uint4*>(dst) + i, raw.a.q[i]);   // bit copy
+    unpack_raw8<T>(raw.a, v);
   }
 };
 
-template <typename T, bool FUSED, typename Source>
-__global__ void __launch_bounds__(256) colsum_kernel(const Source src, float* __restrict__ partial,
+// rows whose loads a thread puts in flight before the math (DLION_COLSUM_K = 1 | 2 | 4 overrides, for tuning)
+static int colsum_rows_in_flight() {
+  static const int k = [] {
+    const char* v = getenv("DLION_COLSUM_K");
+    const int x = v ? atoi(v) : 4;
+    return x == 1 || x == 2 ? x : 4;
+  }();
+  return k;
+}
+
+template <typename T, bool FUSED, typename Source, int K>
+__global__ void __launch_bounds__(256, K == 2 ? 6 : 4) colsum_kernel(const Source src, float* __restrict__ partial,
                                                      int64_t rows, int cols, unsigned int* __restrict__ tickets,
                                                      T* __restrict__ out, int accumulate) {
   __shared__ float sm[8][32][9];
@@ -90,16 +159,22 @@ __global__ void __launch_bounds__(256) colsum_kernel(const Source src, float* __
   if (live) {
     const int64_t step = (int64_t)gridDim.y * 8;
     int64_t r = (int64_t)blockIdx.y * 8 + rl;
-    for (; r + step < rows; r += 2 * step) {      // two rows in flight per thread
-      float a[8], b[8];
-      src.fetch(r, cg, a);
-      src.fetch(r + step, cg, b);
+    for (; r + (K - 1) * step < rows; r += K * step) {      // K rows' loads in flight per thread, then the math
+      typename Source::Raw raw[K];
 #pragma unroll
-      for (int i = 0; i < 8; ++i) acc[i] += a[i] + b[i];
+      for (int q = 0; q < K; ++q) raw[q] = src.load(r + q * step, cg);
+#pragma unroll
+      for (int q = 0; q < K; ++q) {
+        float a[8];
+        src.finish(raw[q], r + q * step, cg, a);
+#pragma unroll
+        for (int i = 0; i < 8; ++i) acc[i] += a[i];
+      }
     }
-    if (r < rows) {
+    for (; r < rows; r += step) {
       float a[8];
-      src.fetch(r, cg, a);
+      const typename Source::Raw raw = src.load(r, cg);
+      src.finish(raw, r, cg, a);
 #pragma unroll
       for (int i = 0; i < 8; ++i) acc[i] += a[i];
     }
@@ -154,9 +229,19 @@ __global__ void __launch_bounds__(256) colsum_kernel(const Source src, float* __
 
 using namespace dlion;
 
+// expects `grid`, `s`, `partial`, `rows`, `cols` in scope
+#define COLSUM_LAUNCH(FUSED_, SRC_T, SRC, TICKETS, OUT, ACC)                                                          \
+  do {                                                                                                                \
+    const int k_ = colsum_rows_in_flight();                                                                           \
+    if (k_ == 1) colsum_kernel<T, FUSED_, SRC_T, 1><<<grid, 256, 0, s>>>(SRC, partial, rows, cols, TICKETS, OUT, ACC);      \
+    else if (k_ == 2) colsum_kernel<T, FUSED_, SRC_T, 2><<<grid, 256, 0, s>>>(SRC, partial, rows, cols, TICKETS, OUT, ACC); \
+    else colsum_kernel<T, FUSED_, SRC_T, 4><<<grid, 256, 0, s>>>(SRC, partial, rows, cols, TICKETS, OUT, ACC);              \
+  } while (0)
+
 extern "C" int dlion_colsum_parts(int64_t rows, int cols) {
   const int gx = (cols + 255) / 256;
-  int gy = kColsumParts / (gx > 0 ? gx : 1);
+  const int ctas = colsum_rows_in_flight() == 2 ? kNumSMs * 6 : kColsumParts;     // one resident wave
+  int gy = ctas / (gx > 0 ? gx : 1);
   const int64_t max_y = (rows + 7) / 8;
   if (gy > max_y) gy = (int)max_y;
   return gy < 1 ? 1 : gy;
@@ -168,8 +253,7 @@ extern "C" int dlion_colsum(const void* x, int64_t rows, int cols, float* partia
   if (rows == 0) return 0;
   const dim3 grid((cols + 255) / 256, dlion_colsum_parts(rows, cols));
   cudaStream_t s = (cudaStream_t)stream;
-  DISPATCH_DTYPE(dtype, (colsum_kernel<T, false, PlainSource<T>><<<grid, 256, 0, s>>>(PlainSource<T>{(const T*)x, cols},
-                                                                                     partial, rows, cols, nullptr, nullptr, 0)));
+  DISPATCH_DTYPE(dtype, COLSUM_LAUNCH(false, PlainSource<T>, (PlainSource<T>{(const T*)x, cols}), nullptr, (T*)nullptr, 0));
   return DLION_LAUNCH_CHECK("dlion_colsum");
 }
 
@@ -182,9 +266,7 @@ extern "C" int dlion_colsum_fused(const void* x, int64_t rows, int cols, float* 
                   "dlion_colsum_fused: bad pointers");
   const dim3 grid((cols + 255) / 256, dlion_colsum_parts(rows, cols));
   cudaStream_t s = (cudaStream_t)stream;
-  DISPATCH_DTYPE(dtype, (colsum_kernel<T, true, PlainSource<T>><<<grid, 256, 0, s>>>(PlainSource<T>{(const T*)x, cols},
-                                                                                    partial, rows, cols, tickets, (T*)out,
-                                                                                    accumulate)));
+  DISPATCH_DTYPE(dtype, COLSUM_LAUNCH(true, PlainSource<T>, (PlainSource<T>{(const T*)x, cols}), tickets, (T*)out, accumulate));
   return DLION_LAUNCH_CHECK("dlion_colsum_fused");
 }
 
@@ -196,9 +278,8 @@ extern "C" int dlion_gelu_tanh_bwd_colsum(const void* pre, const void* dy, void*
                   "dlion_gelu_tanh_bwd_colsum: bad pointers");
   const dim3 grid((cols + 255) / 256, dlion_colsum_parts(rows, cols));
   cudaStream_t s = (cudaStream_t)stream;
-  DISPATCH_DTYPE(dtype, (colsum_kernel<T, true, GeluBwdSource<T>><<<grid, 256, 0, s>>>(
-                            GeluBwdSource<T>{(const T*)pre, (const T*)dy, (T*)dpre, cols}, partial, rows, cols, tickets,
-                            (T*)out, accumulate)));
+  DISPATCH_DTYPE(dtype, COLSUM_LAUNCH(true, GeluBwdSource<T>, (GeluBwdSource<T>{(const T*)pre, (const T*)dy, (T*)dpre, cols}),
+                                      tickets, (T*)out, accumulate));
   return DLION_LAUNCH_CHECK("dlion_gelu_tanh_bwd_colsum");
 }
 
@@ -226,7 +307,7 @@ extern "C" int dlion_qkv_pack_colsum(const void* dq, const void* dk, const void*
       src.ss[t] = strides_bhs[3 * t + 2];
     }
     src.out = (T*)dqkv; src.S = seq; src.H = heads; src.D = head_dim; src.cols = cols;
-    colsum_kernel<T, true, QkvPackSource<T>><<<grid, 256, 0, s>>>(src, partial, rows, cols, tickets, (T*)out, accumulate);
+    COLSUM_LAUNCH(true, QkvPackSource<T>, src, tickets, (T*)out, accumulate);
   });
   return DLION_LAUNCH_CHECK("dlion_qkv_pack_colsum");
 }
