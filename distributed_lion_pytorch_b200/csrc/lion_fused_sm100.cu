@@ -97,6 +97,7 @@ struct FusedParams {
   const float* clip_sumsq;
   float clip_max_norm;
   int zero_g;
+  uint64_t wait_timeout_ns;     // 0 = poll-count limit only
 };
 
 // ------------------------------------------------------------------ PTX helpers
@@ -169,6 +170,11 @@ __device__ __forceinline__ void multimem_st_v4(uint32_t* mc_ptr, const uint4& v)
                "f"(__uint_as_float(v.y)), "f"(__uint_as_float(v.z)), "f"(__uint_as_float(v.w))
                : "memory");
 }
+__device__ __forceinline__ uint64_t global_timer_ns() {
+  uint64_t t;
+  asm volatile("mov.u64 %0, %%globaltimer;" : "=l"(t));
+  return t;
+}
 __device__ __forceinline__ void fence_acq_rel_sys() { asm volatile("fence.acq_rel.sys;" ::: "memory"); }
 __device__ __forceinline__ void st_release_cta(uint32_t* smem_ptr, uint32_t v) {
   asm volatile("st.release.cta.shared.u32 [%0], %1;" ::"r"(smem_u32(smem_ptr)), "r"(v) : "memory");
@@ -198,7 +204,8 @@ struct Cfg {
   static constexpr int OFF_BARS = OFF_PLANES + kCStages * 5 * PLANE_BYTES;
   static constexpr int NUM_BARS = 2 * kPStages + 3 * kCStages;
   static constexpr int OFF_CTRS = OFF_BARS + NUM_BARS * 8;
-  static constexpr int OFF_ZERO = (OFF_CTRS + 64 + 127) / 128 * 128;   // zero page: source of the g zero-fill
+  static constexpr int OFF_SKIP = OFF_CTRS + 64;                      // [kCStages] u32: tile's vote is void (a wait expired)
+  static constexpr int OFF_ZERO = (OFF_SKIP + kCStages * 4 + 127) / 128 * 128;   // zero page: source of the g zero-fill
   static constexpr int SMEM_TOTAL = OFF_ZERO + kArrayBytes;
 };
 
@@ -244,6 +251,7 @@ __global__ void __launch_bounds__(kFusedThreads, 1) lion_fused_kernel(const __gr
   uint32_t* ctrs = reinterpret_cast<uint32_t*>(smem + C::OFF_CTRS);
   uint32_t* words_done = ctrs;                     // tiles whose packed words are in wring
   uint32_t* sent = ctrs + 1;                       // [kSenders] tiles each sender has pushed out
+  uint32_t* skip = reinterpret_cast<uint32_t*>(smem + C::OFF_SKIP);   // [kCStages]
 
   const int G = P.grid;
   const bool emu = P.emulate_ranks > 0;
@@ -315,7 +323,11 @@ __global__ void __launch_bounds__(kFusedThreads, 1) lion_fused_kernel(const __gr
     const uint64_t* my_flags = P.flags[my_rank];
     const uint32_t* my_arena = P.arena[my_rank] + (int64_t)parity_sel * W * P.arena_words;
     const int64_t spin_limit = P.spin_limit > 0 ? P.spin_limit : kDefaultFlagSpin;
-    bool gave_up = false;
+    const uint64_t deadline = P.wait_timeout_ns ? global_timer_ns() + P.wait_timeout_ns : 0ull;
+    // sticky: once any launch has recorded a stalled exchange, later launches neither wait nor apply votes until
+    // the host has seen the status and cleared it — the host learns of a stall one step late, and must not find a
+    // queue of further launches each spinning through its own time-out
+    bool gave_up = P.status != nullptr && *reinterpret_cast<volatile const int32_t*>(P.status) != 0;
     uint64_t seen = 0;                       // last progress value this lane observed for rank `lane`
     const int thr = P.L / 2 + 1;             // +1 iff 2*cnt > L  <=>  cnt >= floor(L/2)+1
     const bool waits = lane < W && ((P.wait_mask >> lane) & 1u);
@@ -330,7 +342,7 @@ __global__ void __launch_bounds__(kFusedThreads, 1) lion_fused_kernel(const __gr
         // counter is there: everything the sender stored before its release is then visible
         int64_t it = 0;
         while (ld_relaxed_sys(f) < target) {
-          if (++it > spin_limit) {
+          if (++it > spin_limit || (deadline && (it & 63) == 0 && global_timer_ns() > deadline)) {
             report(P.status, 1, cta, lane);
             gave_up = true;
             break;
@@ -384,6 +396,9 @@ __global__ void __launch_bounds__(kFusedThreads, 1) lion_fused_kernel(const __gr
               (P.vote == DLION_VOTE_MAJORITY_ZERO && (P.L & 1) == 0) ? planes_eq(c[w], P.L / 2) : 0u;
         }
       }
+      // a tile whose ballots never (all) arrived is not applied: better an untouched parameter tile, repaired
+      // by resync_replicas(), than an update voted from stale words
+      if (lane == 0) skip[slot] = gave_up ? 1u : 0u;
       __syncwarp();
       if (lane == 0) mbar_arrive(smem_u32(voteC + slot));
     }
@@ -415,6 +430,7 @@ __global__ void __launch_bounds__(kFusedThreads, 1) lion_fused_kernel(const __gr
             multimem_st_v4(P.mc_arena + ((int64_t)(parity_sel * W + my_rank)) * P.arena_words + woff + lane * 4, v);
         } else {
           for (int r = s; r < W; r += kSenders) {
+            if (!((P.wait_mask >> r) & 1u)) continue;   // a rank nobody waits for (declared dead) is not written to
             uint32_t* dst = P.arena[r] + ((int64_t)(parity_sel * W + my_rank)) * P.arena_words + woff;
             if (lane < C::WORDS / 4) reinterpret_cast<uint4*>(dst)[lane] = v;   // one coalesced request per tile
           }
@@ -428,7 +444,8 @@ __global__ void __launch_bounds__(kFusedThreads, 1) lion_fused_kernel(const __gr
         const int r_begin = P.mc_arena != nullptr ? (s == 0 ? 0 : W) : s;
         const int r_step = P.mc_arena != nullptr ? 1 : kSenders;
         for (int r = r_begin; r < W; r += r_step)
-          st_relaxed_sys(P.flags[r] + (int64_t)my_rank * DLION_FUSED_MAX_CTAS + cta, epoch_hi | (uint64_t)done);
+          if ((P.wait_mask >> r) & 1u)
+            st_relaxed_sys(P.flags[r] + (int64_t)my_rank * DLION_FUSED_MAX_CTAS + cta, epoch_hi | (uint64_t)done);
         st_release_cta(sent + s, done);              // ring slots below `done` may be reused
       }
       __syncwarp();
@@ -512,8 +529,9 @@ __global__ void __launch_bounds__(kFusedThreads, 1) lion_fused_kernel(const __gr
       const T* sp = reinterpret_cast<const T*>(cring + slot * kCStageBytes);
       const uint8_t* pl = reinterpret_cast<const uint8_t*>(planes + slot * 5 * C::WORDS);
       const int64_t off = ((int64_t)cta + (int64_t)i * G) * C::TILE;
+      const bool void_vote = skip[slot] != 0u;       // ordered by the voteC mbarrier (uniform over the CTA)
 #pragma unroll
-      for (int u = 0; u < C::UPT_C; ++u) {
+      for (int u = 0; u < C::UPT_C && !void_vote; ++u) {
         const int unit = ct + u * kCThreads;
         float pf[8];
         load8<T>(sp + unit * 8, pf);
@@ -602,10 +620,12 @@ static int launch_fused(const dlion_fused_args* a, cudaStream_t s) {
   for (int r = 0; r < a->world; ++r)
     DLION_CHECK_ARG(P.arena[r] != nullptr && P.flags[r] != nullptr && aligned16(P.arena[r]),
                     "dlion_fused_step: arena/flags pointer of rank %d is null or unaligned", r);
-  P.mc_arena = a->emulate_ranks > 0 ? nullptr : a->mc_arena;
+  // multicast reaches every member of the group: only usable while every rank is awaited (none declared dead)
+  P.mc_arena = (a->emulate_ranks > 0 || P.wait_mask != all) ? nullptr : a->mc_arena;
   P.arena_words = a->arena_words; P.grid = a->grid; P.emulate_ranks = a->emulate_ranks; P.emu_stride = a->emu_stride;
   P.status = a->status; P.spin_limit = a->spin_limit; P.sr_key = a->sr_key;
   P.clip_sumsq = a->clip_sumsq; P.clip_max_norm = a->clip_max_norm; P.zero_g = a->zero_g;
+  P.wait_timeout_ns = a->wait_timeout_us * 1000ull;
   DLION_CHECK_ARG(a->clip_sumsq == nullptr || a->clip_max_norm > 0.f, "dlion_fused_step: clip_max_norm must be positive");
   void* kargs[] = {(void*)&P};
   return check_cuda(cudaLaunchCooperativeKernel((void*)lion_fused_kernel<T>, dim3(a->grid * vr), dim3(kFusedThreads),

@@ -20,6 +20,7 @@ from torch.utils.checkpoint import checkpoint
 
 from ..ops.activation import gelu_tanh
 from ..ops.cross_entropy import linear_cross_entropy, linear_log_probs
+from ..ops.embedding import embed
 from ..ops.linear import fused_linear
 from ..ops.lt_gemm import linear_gelu
 from ..ops.norm import add_layer_norm
@@ -189,8 +190,7 @@ class GPT2LMHeadModel(nn.Module, PreTrainedMixin):
     def hidden_states(self, input_ids, attention_mask=None):
         B, S = input_ids.shape
         t = self.transformer
-        pos = torch.arange(S, device=input_ids.device)
-        h = t.wte(input_ids) + t.wpe(pos)
+        h = embed(input_ids, t.wte.weight, t.wpe.weight)      # wte[ids] + wpe[0..S-1], one pass
         mask = None
         if attention_mask is not None and not bool(attention_mask.all()):
             causal = torch.ones(S, S, dtype=torch.bool, device=h.device).tril()

@@ -16,6 +16,7 @@ import torch.nn.functional as F
 from torch.utils.checkpoint import checkpoint
 
 from ..ops.activation import swiglu
+from ..ops.embedding import embed
 from ..ops.cross_entropy import linear_cross_entropy, linear_log_probs
 from ..ops.linear import fused_linear
 from ..ops.norm import add_rms_norm
@@ -167,7 +168,7 @@ class LlamaForCausalLM(nn.Module, PreTrainedMixin):
     def hidden_states(self, input_ids, attention_mask=None):
         B, S = input_ids.shape
         m = self.model
-        h = m.embed_tokens(input_ids)
+        h = embed(input_ids, m.embed_tokens.weight)
         cos, sin = self._tables(S, h.device)
         mask = None
         if attention_mask is not None and not bool(attention_mask.all()):

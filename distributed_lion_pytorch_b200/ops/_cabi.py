@@ -36,6 +36,7 @@ class FusedArgs(C.Structure):
         ("arena_words", C.c_int64), ("grid", C.c_int), ("emulate_ranks", C.c_int),
         ("emu_stride", C.c_int64), ("status", C.c_void_p), ("spin_limit", C.c_int64), ("sr_key", C.c_uint64),
         ("clip_sumsq", C.c_void_p), ("clip_max_norm", C.c_float), ("zero_g", C.c_int),
+        ("wait_timeout_us", C.c_uint64),
     ]
 
 
@@ -102,6 +103,8 @@ def _declare(L: C.CDLL) -> None:
         "dlion_norm_bwd_dxsum_parts": [i64, i32],
         "dlion_norm_bwd_dxsum": [vp, vp, vp, vp, vp, vp, vp, vp, vp, vp, vp, i64, i32, i32, f32, u64, i32, vp],
         "dlion_norm_bwd_finalize_dxsum": [vp, vp, vp, vp, vp, vp, i32, i32, i32, i32, vp],
+        "dlion_embed_fwd": [vp, vp, vp, vp, i64, i32, i32, i64, i32, vp],
+        "dlion_embed_bwd_sorted": [vp, vp, vp, vp, i64, i32, i64, i32, i32, vp],
         "dlion_gelu_tanh_fwd": [vp, vp, i64, i32, vp],
         "dlion_gelu_tanh_bwd": [vp, vp, vp, i64, i32, vp],
         "dlion_swiglu_fwd": [vp, vp, vp, i64, i32, vp],

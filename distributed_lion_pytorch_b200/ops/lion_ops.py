@@ -107,7 +107,7 @@ def fused_step(p: torch.Tensor, g: torch.Tensor, m: torch.Tensor, *, world: int,
                wait_mask: Optional[int] = None, max_grad_norm: Optional[float] = None, seed: int = 0, step: int = 0,
                elem_base: int = 0, emulate_ranks: int = 0, emu_stride: int = 0, status: Optional[torch.Tensor] = None,
                spin_limit: int = 0, n: Optional[int] = None, mc_arena_ptr: int = 0, sr_key: int = 0,
-               clip=None, zero_g: bool = False) -> None:
+               clip=None, zero_g: bool = False, wait_timeout_us: int = 0) -> None:
     """Launch the fused sign-pack-exchange-vote-update kernel on ``n`` elements of p/g/m.
 
     ``arena_ptrs[r]`` / ``flag_ptrs[r]`` are device addresses of rank r's receive arena and
@@ -137,6 +137,7 @@ def fused_step(p: torch.Tensor, g: torch.Tensor, m: torch.Tensor, *, world: int,
     a.sr_key = int(sr_key) & (2 ** 64 - 1)
     a.clip_sumsq, a.clip_max_norm = _clip_args(clip)
     a.zero_g = int(bool(zero_g))
+    a.wait_timeout_us = int(wait_timeout_us)
     import ctypes as C
     with torch.cuda.device(p.device):
         _cabi.check(_cabi.lib().dlion_fused_step(C.byref(a), _cabi.stream_ptr(p.device)), "fused_step")

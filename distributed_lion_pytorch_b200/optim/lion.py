@@ -379,6 +379,25 @@ class Lion(Optimizer):
             if stray:   # the checkpoint knows parameters we have not bucketed yet: re-plan at next step
                 self._buckets, self._bucket_sig = None, None
 
+    def declare_dead(self, rank: int) -> None:
+        """Call on every surviving rank (same argument) once a peer is known to be gone: its ballots no longer count
+        (the majority threshold / averaging denominator shrink) and — on the fused path — nobody waits for its
+        progress flags any more, so a step costs no spin on flags that will never arrive.  The reference's README
+        advertises robustness to worker drop-out (README.md:2) but ``dist.all_gather`` simply hangs on a missing
+        rank (distributed_lion.py:81).  The ``nccl_1bit`` path is a collective and cannot shed a dead rank."""
+        W = self.world_size
+        if not 0 <= rank < W:
+            raise ValueError(f"rank {rank} outside [0, {W})")
+        full = (1 << W) - 1
+        live = (full if self.live_mask is None else self.live_mask) & ~(1 << rank)
+        wait = (full if self.wait_mask is None else self.wait_mask) & ~(1 << rank)
+        if live == 0:
+            raise ValueError("no live worker left")
+        self.live_mask, self.wait_mask = live, wait
+        ctx = getattr(self._backend, "_ctx", None)
+        if ctx is not None:
+            ctx.clear_status()
+
     def check_health(self) -> None:
         """Raise if the fused exchange kernel recorded a stalled flag wait since the last check
         (synchronises the device; the trainer calls it whenever it logs).  No-op for other back-ends."""

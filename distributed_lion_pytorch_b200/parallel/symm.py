@@ -95,6 +95,14 @@ class FusedExchange:
         self.arena_words = 0
         self.flags = PeerBuffer(self.world * _cabi.FUSED_MAX_CTAS * 8, device, pg)
         self.status = torch.zeros(4, dtype=torch.int32, device=device)
+        # host mirror of the status word: refreshed by a 16-byte async copy behind every step, read WITHOUT a device
+        # sync at the start of the next one (poll_status), so a stalled exchange surfaces one step later, not at the
+        # next logging step
+        self._status_host = torch.zeros(4, dtype=torch.int32).pin_memory()
+        self._status_evt: Optional[torch.cuda.Event] = None
+        # longest a voter waits for one peer's flag (GPU wall clock); generous by default: a peer may legitimately be
+        # seconds late (data loading, a checkpoint being written elsewhere)
+        self.wait_timeout_s = float(os.environ.get("DLION_WAIT_TIMEOUT_S", "60"))
         self._grid = {}
         self._mc_agreed = 0
 
@@ -127,9 +135,11 @@ class FusedExchange:
              sr_key: int = 0, clip=None, zero_g: bool = False, wait_mask=None) -> None:
         tile = lion_ops.fused_tile(b.dtype)
         assert b.numel % tile == 0, "bucket length must be a multiple of the fused tile"
+        self.poll_status()
         chunk = self.chunk_elems - self.chunk_elems % tile
         self._ensure_arena(b.numel)
         grid = self.grid_for(b.dtype)
+        timeout_us = int(self.wait_timeout_s * 1e6) if self.wait_timeout_s > 0 else 0
         for off in range(0, b.numel, chunk):
             n = min(chunk, b.numel - off)
             self.epoch += 1
@@ -139,7 +149,12 @@ class FusedExchange:
                                 grid=grid, lr=lr, wd=wd, beta1=beta1, beta2=beta2, vote=vote, tie=tie,
                                 live_mask=live_mask, max_grad_norm=max_grad_norm, seed=seed, step=step_index,
                                 elem_base=off, status=self.status, mc_arena_ptr=self._mc_ptr(), sr_key=sr_key,
-                                clip=clip, zero_g=zero_g, wait_mask=wait_mask)
+                                clip=clip, zero_g=zero_g, wait_mask=wait_mask, wait_timeout_us=timeout_us,
+                                spin_limit=(1 << 40) if timeout_us else 0)
+        self._status_host.copy_(self.status, non_blocking=True)
+        if self._status_evt is None:
+            self._status_evt = torch.cuda.Event()
+        self._status_evt.record()
 
     def _mc_ptr(self) -> int:
         """NVLS multicast alias of the arena.  Used whenever the fabric exposes one (symmetric memory reports a
@@ -154,13 +169,32 @@ class FusedExchange:
     def uses_multicast(self) -> bool:
         return self._mc_ptr() != 0
 
+    @staticmethod
+    def _raise(st) -> None:
+        what = {1: f"rank {st[2]}'s progress flag never arrived at CTA {st[1]}",
+                2: f"internal pipeline wait expired in CTA {st[1]} (role {st[2]})"}.get(st[0], str(st))
+        raise RuntimeError(f"fused Distributed-Lion kernel reported a stalled exchange: {what}.  The parameter tiles "
+                           "whose ballots were incomplete were left untouched; replicas may now differ — call "
+                           "Lion.resync_replicas() (and Lion.declare_dead(rank) if the peer is gone) before continuing")
+
+    def poll_status(self) -> None:
+        """No device sync: if the status copy issued behind the previous step has landed and says a wait expired,
+        raise now — before another step is launched and before anyone writes a checkpoint."""
+        if self._status_evt is not None and self._status_evt.query():
+            st = self._status_host.tolist()
+            if st[0] != 0:
+                self._raise(st)
+
     def check_status(self) -> None:
         """Host-side health check (synchronises): raises if a flag wait timed out in any launch."""
         st = self.status.tolist()
         if st[0] != 0:
-            what = {1: f"rank {st[2]}'s progress flag never arrived at CTA {st[1]}",
-                    2: f"internal pipeline wait expired in CTA {st[1]} (role {st[2]})"}.get(st[0], str(st))
-            raise RuntimeError(f"fused Distributed-Lion kernel reported a stalled exchange: {what}")
+            self._raise(st)
+
+    def clear_status(self) -> None:
+        self.status.zero_()
+        self._status_host.zero_()
+        self._status_evt = None
 
 
 class EmulatedExchange:

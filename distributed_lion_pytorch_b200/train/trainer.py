@@ -534,6 +534,9 @@ class Trainer:
 
     def _save_checkpoint(self) -> str:
         a = self.args
+        if isinstance(self.optimizer, Lion):
+            # never persist parameters that came out of a stalled sign exchange: raises here, before anything is written
+            self.optimizer.check_health()
         d = os.path.join(a.output_dir, f"{PREFIX_CHECKPOINT_DIR}-{self.state.global_step}")
         if self.is_world_process_zero:
             os.makedirs(d, exist_ok=True)

@@ -113,7 +113,8 @@ int dlion_vote_update_sr(void* p, const void* g, void* m, const uint32_t* gather
  * groups of CTAs, group v acting as rank v on p/g/m + v*emu_stride elements, all arenas /
  * flags living on this device (arena[v], flags[v]).  Used by the one-GPU tests.
  *
- * status (device int32[4], may be NULL): [0]=0 ok / 1 flag-wait timeout, [1]=CTA, [2]=src rank.
+ * status (device int32[4], may be NULL): [0]=0 ok / 1 flag-wait timeout, [1]=CTA, [2]=src rank; tiles whose wait
+ * expired are not applied (see wait_timeout_us).
  * reference: distributed_lion.py:61-96 + the NCCL all_gather it calls at :81. */
 typedef struct {
   void* p;
@@ -153,6 +154,12 @@ typedef struct {
   const float* clip_sumsq;
   float clip_max_norm;
   int zero_g;
+  /* Upper bound, in microseconds of GPU wall clock (%globaltimer), on the time a voter waits for one peer's
+   * progress flag; 0 = only the poll-count limit `spin_limit` applies.  When a wait expires the kernel records it
+   * in `status`, leaves the parameter tiles whose ballots are incomplete UNTOUCHED (momenta are local and still
+   * advance) and runs to completion — a stalled peer can neither hang the GPU nor inject an update voted from
+   * stale words.  (reference: dist.all_gather at distributed_lion.py:81 blocks forever on a missing rank.) */
+  uint64_t wait_timeout_us;
 } dlion_fused_args;
 
 #define DLION_FUSED_MAX_CTAS 1024
@@ -263,6 +270,17 @@ int dlion_gelu_tanh_bwd_colsum(const void* pre, const void* dy, void* dpre, int6
 int dlion_qkv_pack_colsum(const void* dq, const void* dk, const void* dv, const int64_t* strides_bhs, void* dqkv,
                           int batch, int seq, int heads, int head_dim, float* partial, unsigned int* tickets, void* out,
                           int accumulate, int dtype, void* stream);
+
+/* Token + position embedding.  Forward: out[row] = wte[ids[row]] + wpe[row % seq] in one pass (wpe may be NULL).
+ * Backward of the token table: `sorted_ids` are the n token ids sorted ascending (stable) and `perm[k]` is the row of
+ * dh that sorted position k came from; the gradient rows are summed in fp32 in sorted order (deterministic, no
+ * atomics) and written (accumulate = 0: rows of absent tokens are NOT touched — pass a zeroed buffer) or added into
+ * grad (accumulate = 1: grad is the live .grad buffer).
+ * reference: HF GPT2Model wte / wpe and autograd's embedding_dense_backward + AccumulateGrad (async_trainer.py:33). */
+int dlion_embed_fwd(const int64_t* ids, const void* wte, const void* wpe, void* out, int64_t rows, int seq, int hidden,
+                    int64_t vocab, int dtype, void* stream);
+int dlion_embed_bwd_sorted(const void* dh, const int64_t* sorted_ids, const int64_t* perm, void* grad, int64_t n,
+                           int hidden, int64_t vocab, int accumulate, int dtype, void* stream);
 
 /* MLP activations as single passes over n elements (n % 8 == 0): GPT-2's tanh-form GELU and
  * Llama's silu(gate) * up, forward and backward.

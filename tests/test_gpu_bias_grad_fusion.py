@@ -120,3 +120,43 @@ def test_gpt2_block_uses_all_three_handoffs():
     n_layer = m.config.n_layer
     assert lin.HANDOFFS - before == 3 * n_layer, (lin.HANDOFFS - before, n_layer)
     assert all(p.grad is not None and torch.isfinite(p.grad).all() for p in m.parameters())
+
+
+@pytest.mark.parametrize("dtype", [torch.bfloat16, torch.float32])
+@pytest.mark.parametrize("with_pos", [True, False])
+@pytest.mark.parametrize("grads_exist", [True, False])
+def test_embedding_forward_and_sorted_backward(dtype, with_pos, grads_exist):
+    """One-pass wte[ids] + wpe[pos] and the deterministic backward (sorted ids, one CTA per run of equal ids, adds
+    into the existing .grad) against torch.nn.functional.embedding + autograd — with many repeated tokens."""
+    from distributed_lion_pytorch_b200.ops.embedding import embed
+    torch.manual_seed(0)
+    V, H, B, S = 1000, 264, 7, 53
+    wte = torch.nn.Parameter(torch.randn(V, H, device="cuda", dtype=dtype))
+    wpe = torch.nn.Parameter(torch.randn(64, H, device="cuda", dtype=dtype)) if with_pos else None
+    ids = torch.randint(0, 40, (B, S), device="cuda")            # 371 tokens over 40 ids: long runs
+    ids[0, :5] = 999
+    up = torch.randn(B, S, H, device="cuda", dtype=dtype)
+    wte2 = torch.nn.Parameter(wte.detach().clone())
+    wpe2 = torch.nn.Parameter(wpe.detach().clone()) if with_pos else None
+    ref = F.embedding(ids, wte2)
+    if with_pos:
+        ref = ref + wpe2[:S]
+    (ref * up).sum().backward()
+    if grads_exist:
+        wte.grad = torch.full_like(wte, 0.25)
+        if with_pos:
+            wpe.grad = torch.full_like(wpe, -0.5)
+    out = embed(ids, wte, wpe)
+    assert torch.equal(out, ref)
+    (out * up).sum().backward()
+    tol = dict(rtol=2e-2, atol=6e-2) if dtype == torch.bfloat16 else dict(rtol=1e-5, atol=1e-5)
+    assert torch.allclose(wte.grad.float(), wte2.grad.float() + (0.25 if grads_exist else 0.0), **tol)
+    if with_pos:
+        assert torch.allclose(wpe.grad.float(), wpe2.grad.float() + (-0.5 if grads_exist else 0.0), **tol)
+    # deterministic: a second backward on fresh buffers gives identical bits
+    g1 = wte.grad.clone()
+    wte.grad = torch.full_like(wte, 0.25) if grads_exist else None
+    if with_pos:
+        wpe.grad = None
+    (embed(ids, wte, wpe) * up).sum().backward()
+    assert torch.equal(wte.grad, g1)

@@ -200,3 +200,71 @@ def test_fused_small_grid_skewed_arrival_real_gpus(grid):
     outs = run_distributed(_worker_big, world, 1 << 20, 6, grid == 37, grid, True, backend="nccl", timeout=900)
     for o in outs:
         assert o["grid"] == grid and o["bad_step"] < 0 and o["identical"] and o["clean"]
+
+
+# --------------------------------------------------------------------------- a peer that stops stepping
+def _worker_stall(rank, world, tmp):
+    """Rank 1 stops taking optimizer steps after step 3 (its process stays alive, as a hung or very late worker
+    would).  Rank 0 must not hang: its kernel gives up after the wait time-out, leaves the affected parameter tiles
+    untouched, the NEXT step() raises without a device sync, a checkpoint attempt raises instead of writing, and
+    after declare_dead(1) rank 0 keeps training on its own ballots."""
+    import os
+    import time
+    os.environ["DLION_WAIT_TIMEOUT_S"] = "1.0"
+    from distributed_lion import Lion
+    dev = torch.device("cuda", rank)
+    net = _net(0, torch.bfloat16).to(dev)
+    opt = Lion(net.parameters(), lr=1e-3, weight_decay=0.0, comm="fused")
+    g = torch.Generator(device=dev).manual_seed(100 + rank)
+
+    def one_step():
+        x = torch.randn(64, 256, device=dev, generator=g).bfloat16()
+        opt.zero_grad()
+        net(x).float().pow(2).mean().backward()
+        opt.step()
+
+    for _ in range(3):
+        one_step()
+    torch.cuda.synchronize()
+    out = {"rank": rank}
+    if rank == 1:
+        time.sleep(12)                     # "dead": never steps again, but its memory stays mapped
+        return out
+    before = [p.detach().clone() for p in net.parameters()]
+    t0 = time.time()
+    one_step()                             # peers' flags never come: bounded wait inside the kernel
+    raised_at = None
+    for i in range(50):
+        try:
+            one_step()
+        except RuntimeError as e:
+            raised_at, out["msg"] = i, str(e)
+            break
+        time.sleep(0.05)
+    out["seconds_to_raise"] = time.time() - t0
+    out["raised_at"] = raised_at
+    torch.cuda.synchronize()
+    # the stalled step applied nothing to the parameters (every tile's ballots were incomplete)
+    out["untouched"] = all(torch.equal(a, p.detach()) for a, p in zip(before, net.parameters()))
+    try:
+        opt.check_health()
+        out["health_raises"] = False
+    except RuntimeError:
+        out["health_raises"] = True
+    opt.declare_dead(1)
+    for _ in range(3):
+        one_step()
+    torch.cuda.synchronize()
+    opt.check_health()
+    out["moved_after_declare_dead"] = not all(torch.equal(a, p.detach()) for a, p in zip(before, net.parameters()))
+    return out
+
+
+def test_stalled_peer_raises_quickly_and_can_be_declared_dead(tmp_path):
+    if torch.cuda.device_count() < 2:
+        pytest.skip("needs 2 GPUs")
+    outs = run_distributed(_worker_stall, 2, str(tmp_path), backend="nccl", timeout=300)
+    o = outs[0]
+    assert o["raised_at"] is not None and "stalled exchange" in o["msg"], o
+    assert o["seconds_to_raise"] < 5.0, o
+    assert o["untouched"] and o["health_raises"] and o["moved_after_declare_dead"], o
