@@ -142,6 +142,6 @@ def all_reduce_scalar(x: float, op: str = "mean", device: Optional[torch.device]
         return float(x)
     t = torch.tensor([float(x)], dtype=torch.float64 if (device or _DEVICE).type == "cpu" else torch.float32,
                      device=device or _DEVICE)
-    dist.all_reduce(t, op=dist.ReduceOp.MAX if op == "max" else dist.ReduceOp.SUM)
+    dist.all_reduce(t, op={"max": dist.ReduceOp.MAX, "min": dist.ReduceOp.MIN}.get(op, dist.ReduceOp.SUM))
     v = float(t.item())
     return v / dist.get_world_size() if op == "mean" else v

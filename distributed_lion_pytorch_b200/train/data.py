@@ -8,9 +8,11 @@ every path has a synthetic twin that produces tensors of exactly the same shape.
 """
 from __future__ import annotations
 
+import itertools
 import math
 from typing import Callable, Dict, Iterable, Iterator, List, Optional, Sequence
 
+import numpy as np
 import torch
 from torch.utils.data import DataLoader, Dataset, IterableDataset, Sampler
 
@@ -69,6 +71,10 @@ class ByteTokenizer:
             return {"input_ids": self.encode(text)}
         return {"input_ids": [self.encode(t) for t in text]}
 
+    def encode_np(self, text: str) -> np.ndarray:
+        """Tokens as a numpy array without a Python list in between (the bulk tokeniser's fast path)."""
+        return np.frombuffer(text.encode("utf-8"), dtype=np.uint8)
+
     def decode(self, ids) -> str:
         return bytes(i for i in ids if i < 256).decode("utf-8", errors="replace")
 
@@ -109,11 +115,70 @@ class BlockDataset(Dataset):
         return {"input_ids": ids, "labels": ids.clone()}
 
 
-def text_file_dataset(path: str, tokenizer, block_size: int, keep_linebreaks: bool = True) -> BlockDataset:
-    with open(path, encoding="utf-8") as f:
-        lines = f.read().splitlines(keepends=keep_linebreaks)
-    toks = [tokenizer(l)["input_ids"] for l in lines if l.strip()]
-    return BlockDataset(group_texts(toks, block_size))
+def text_file_dataset(path: str, tokenizer, block_size: int, keep_linebreaks: bool = True, *,
+                      num_workers: Optional[int] = None, overwrite_cache: bool = False, cache_dir: Optional[str] = None,
+                      max_blocks: Optional[int] = None):
+    """A local text file as fixed-size token blocks (reference: run_clm.py:342-381 + :463-544).  The file is
+    tokenised once by ``num_workers`` processes into memory-mapped shards under a cache directory
+    (``train/token_cache.py``); later launches, and every rank after rank 0, just open the maps.  Neither the text
+    nor the tokens are ever held in memory as a whole."""
+    from .token_cache import MemmapBlockDataset, tokenize_text_file
+    d = tokenize_text_file(path, tokenizer, num_workers=num_workers, cache_dir=cache_dir,
+                           overwrite_cache=overwrite_cache, keep_linebreaks=keep_linebreaks)
+    return MemmapBlockDataset(d, block_size, max_blocks=max_blocks)
+
+
+class StreamingBlockDataset(IterableDataset):
+    """A stream of raw text examples (``datasets`` streaming mode, or any iterable of dicts / strings) packed into
+    fixed-size token blocks on the fly (reference: run_clm.py:316-341 with ``streaming=True``, then the same
+    tokenize + ``group_texts`` maps applied lazily).
+
+    Sharding happens on the RAW stream, before any tokenisation: with ``shard(rank, world)`` rank r keeps raw examples
+    r, r+W, ... and inside a DataLoader with ``num_workers`` workers each worker keeps every n-th of those — so the
+    tokeniser runs once per example across the whole job, not once per rank."""
+
+    def __init__(self, source, tokenizer, block_size: int, text_key: Optional[str] = "text", skip: int = 0,
+                 take: Optional[int] = None, max_blocks: Optional[int] = None, infinite: bool = False):
+        self.source, self.tok, self.block_size, self.text_key = source, tokenizer, int(block_size), text_key
+        self.skip, self.take, self.max_blocks = int(skip), take, max_blocks
+        # training streams restart when exhausted: every rank must be able to reach --max_steps, and the shards of a
+        # stream are not equally long
+        self.infinite = bool(infinite)
+        self._rank, self._world = 0, 1
+
+    def shard(self, rank: int, world: int) -> "StreamingBlockDataset":
+        self._rank, self._world = int(rank), int(world)
+        return self
+
+    def _raw(self) -> Iterator:
+        it = iter(self.source)
+        stop = None if self.take is None else self.skip + int(self.take)
+        it = itertools.islice(it, self.skip, stop)
+        info = torch.utils.data.get_worker_info()
+        nw, wid = (info.num_workers, info.id) if info is not None else (1, 0)
+        return itertools.islice(it, self._rank * nw + wid, None, self._world * nw)
+
+    def __iter__(self) -> Iterator[Dict[str, torch.Tensor]]:
+        from .token_cache import _encode
+        buf = np.empty(0, dtype=np.int64)
+        produced = 0
+        while True:
+            seen = 0
+            for ex in self._raw():
+                seen += 1
+                text = ex if isinstance(ex, str) else ex[self.text_key]
+                if not text:
+                    continue
+                buf = np.concatenate([buf, np.asarray(_encode(self.tok, text), dtype=np.int64)])
+                while buf.size >= self.block_size:
+                    ids = torch.from_numpy(buf[: self.block_size].copy())
+                    buf = buf[self.block_size:]
+                    yield {"input_ids": ids, "labels": ids.clone()}
+                    produced += 1
+                    if self.max_blocks is not None and produced >= self.max_blocks:
+                        return
+            if not self.infinite or seen == 0:
+                return
 
 
 def prepare_sample_text(example: dict) -> str:
@@ -142,9 +207,22 @@ class ConstantLengthDataset(IterableDataset):
         self.infinite, self.seq_length = infinite, seq_length
         self.max_buffer_size = int(seq_length * chars_per_token * num_of_sequences)
         self.eos = eos_token_id if eos_token_id is not None else getattr(tokenizer, "eos_token_id", 0)
+        self._rank, self._world = 0, 1
+
+    def shard(self, rank: int, world: int) -> "ConstantLengthDataset":
+        """Rank ``rank`` of ``world`` formats, tokenises and packs only every world-th RAW example (accelerate's
+        dataloader sharding, which the reference relies on at sft_llama2.py:171-181, dispatches whole batches
+        instead; either way no example is tokenised more than once per job)."""
+        self._rank, self._world = int(rank), int(world)
+        return self
+
+    def _raw(self) -> Iterator:
+        info = torch.utils.data.get_worker_info()
+        nw, wid = (info.num_workers, info.id) if info is not None else (1, 0)
+        return itertools.islice(iter(self.dataset), self._rank * nw + wid, None, self._world * nw)
 
     def __iter__(self) -> Iterator[Dict[str, torch.Tensor]]:
-        it = iter(self.dataset)
+        it = self._raw()
         more = True
         while more:
             buffer, buflen = [], 0
@@ -155,7 +233,7 @@ class ConstantLengthDataset(IterableDataset):
                     buflen += len(text)
                 except StopIteration:
                     if self.infinite:
-                        it = iter(self.dataset)
+                        it = self._raw()
                     else:
                         more = False
                         break
@@ -210,6 +288,11 @@ class ShardSampler(Sampler):
 def build_loader(dataset, batch_size: int, *, rank: int = 0, world: int = 1, seed: int = 0, shuffle: bool = True,
                  collate_fn=None, num_workers: int = 0, pin_memory: bool = False, drop_last: bool = True):
     collate_fn = collate_fn or default_data_collator
+    if isinstance(dataset, IterableDataset) and callable(getattr(dataset, "shard", None)):
+        # shards its own RAW stream by rank (and by dataloader worker): tokenisation is not repeated on every rank
+        dataset.shard(rank, world)
+        return DataLoader(dataset, batch_size=batch_size, collate_fn=collate_fn, num_workers=num_workers,
+                          pin_memory=pin_memory, drop_last=drop_last, persistent_workers=num_workers > 0), None
     if isinstance(dataset, IterableDataset):
         class _Sharded(IterableDataset):
             def __iter__(self_inner):

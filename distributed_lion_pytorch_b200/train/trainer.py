@@ -105,6 +105,37 @@ class TrainOutput:
     metrics: Dict[str, float]
 
 
+class LossScaler:
+    """Dynamic loss scaling for fp16 training (``--fp16``, or a model held in float16 as dpo_llama2.py:133-139 loads
+    it): the loss is multiplied by ``scale`` before backward, the gradients are divided by it before clipping; a step
+    whose gradients contain inf / nan is skipped and the scale halved, and after ``growth_interval`` clean steps the
+    scale doubles — ``torch.amp.GradScaler``'s policy, restated because GradScaler refuses fp16 *parameters* and
+    knows nothing about flat gradient buckets.  One host sync per optimizer step (the skip decision)."""
+
+    def __init__(self, init_scale: float = 2.0 ** 16, growth_interval: int = 2000, min_scale: float = 1.0):
+        self.scale, self.growth_interval, self.min_scale = float(init_scale), int(growth_interval), float(min_scale)
+        self._good = 0
+        self.skipped = 0
+
+    def unscale_and_check(self, grads: List[torch.Tensor]) -> bool:
+        """Divide ``grads`` by the scale in place; False when any of them is not finite."""
+        if not grads:
+            return True
+        inv = 1.0 / self.scale
+        torch._foreach_mul_(grads, inv)
+        norms = torch._foreach_norm(grads)
+        return bool(torch.isfinite(torch.stack([n.float() for n in norms])).all().item())
+
+    def update(self, ok: bool) -> None:
+        if ok:
+            self._good += 1
+            if self._good >= self.growth_interval:
+                self.scale, self._good = self.scale * 2.0, 0
+        else:
+            self.scale, self._good = max(self.scale * 0.5, self.min_scale), 0
+            self.skipped += 1
+
+
 class Trainer:
     """Synchronous-gradient trainer (the comparison baseline).  See module docstring."""
     sync_gradients = True
@@ -131,6 +162,11 @@ class Trainer:
         self._wandb = None
         self._last_grad_norm = None
         self.optimizer_step_events = None       # set to a list to collect (start, end) CUDA events per step
+        self.loss_scaler: Optional[LossScaler] = None
+        if self.model is not None and self.device.type == "cuda":
+            p0 = next(self.model.parameters(), None)
+            if self.args.fp16 or (p0 is not None and p0.dtype == torch.float16):
+                self.loss_scaler = LossScaler()
         if self.args.gradient_checkpointing and hasattr(self.model, "gradient_checkpointing_enable"):
             self.model.gradient_checkpointing_enable()
 
@@ -193,7 +229,10 @@ class Trainer:
             loss = self.compute_loss(model, inputs)
         ga = self.args.gradient_accumulation_steps
         with self.timer.phase("backward"):
-            (loss / ga if ga > 1 else loss).backward()
+            scaled = loss / ga if ga > 1 else loss
+            if self.loss_scaler is not None:
+                scaled = scaled * self.loss_scaler.scale
+            scaled.backward()
         return loss.detach() / ga
 
     def _flat_grads(self) -> List[torch.Tensor]:
@@ -230,6 +269,25 @@ class Trainer:
                 return bucket_ops.clip_grad_norm_flat_(flats, mg)
         params = [p for p in self.model.parameters() if p.grad is not None]
         return torch.nn.utils.clip_grad_norm_(params, mg)
+
+    def _unscale_or_skip(self) -> bool:
+        """fp16: bring the gradients back to true scale; on overflow drop them, shrink the scale and skip the step.
+        With W > 1 every rank must take the same decision (a rank that skipped alone would desynchronise the sign
+        exchange), so the verdict is reduced over ranks."""
+        flats = self._flat_grads()
+        grads = flats if flats else [p.grad for p in self.model.parameters() if p.grad is not None]
+        ok = self.loss_scaler.unscale_and_check(grads)
+        if rt.is_dist():
+            ok = rt.all_reduce_scalar(1.0 if ok else 0.0, "min", self.device) > 0.5
+        self.loss_scaler.update(ok)
+        if not ok:
+            if isinstance(self.optimizer, Lion):
+                self.optimizer.zero_grad()
+            else:
+                self.optimizer.zero_grad(set_to_none=True)
+            logger.warning("step %d: non-finite gradients, step skipped, loss scale -> %g", self.state.global_step,
+                           self.loss_scaler.scale)
+        return ok
 
     def _lion_param_ids(self) -> set:
         ids = getattr(self, "_lion_ids", None)
@@ -284,6 +342,9 @@ class Trainer:
             total = loss if total is None else total + loss
         with self.timer.phase("grad_sync"):
             self._sync_gradients()
+        if self.loss_scaler is not None and not self._unscale_or_skip():
+            self.state.global_step += 1         # a skipped step still counts (HF semantics); nothing was applied
+            return total
         ev = self.optimizer_step_events
         if ev is not None:                      # bench.py: device time of clip + optimizer + zero_grad
             a, b = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)

@@ -80,19 +80,56 @@ class DataTrainingArguments:
                 raise ValueError("`train_file`/`validation_file` should be a csv, a json or a txt file.")
 
 
-def _hub_dataset(data_args, tokenizer, block_size):
-    """openwebtext & co. through ``datasets`` when it is reachable (it is not on the B200 box)."""
-    from datasets import load_dataset
-    raw = load_dataset(data_args.dataset_name, data_args.dataset_config_name, streaming=data_args.streaming)
+def _text_column(ds) -> str:
+    cols = getattr(ds, "column_names", None)
+    if not cols:                                   # streaming datasets may not know their columns: peek
+        first = next(iter(ds))
+        cols = list(first.keys())
+    return "text" if "text" in cols else cols[0]
+
+
+def _hub_dataset(data_args, tokenizer, block_size, load_dataset=None):
+    """openwebtext & co. through ``datasets`` when it is reachable (it is not on the B200 box).
+    reference: run_clm.py:316-341 (load, carve a validation split when the corpus has none) and :463-544
+    (tokenize + group_texts as cached, multi-process ``map`` calls).
+
+    * ``--streaming``: the splits stay iterable; examples are tokenised and packed on the fly, sharded by rank on the
+      raw stream (``StreamingBlockDataset``).  Without a validation split the first ``max_eval_samples`` (default
+      1000) raw examples become the validation stream and training skips them.
+    * otherwise the text column is tokenised once by ``--preprocessing_num_workers`` processes into memory-mapped
+      token shards (``train/token_cache.py``), cached under the dataset's fingerprint; ``--overwrite_cache`` rebuilds."""
+    if load_dataset is None:
+        from datasets import load_dataset
+    from distributed_lion_pytorch_b200.train.data import StreamingBlockDataset
+    from distributed_lion_pytorch_b200.train.token_cache import MemmapBlockDataset, tokenize_text_iterable
+    name, cfgname = data_args.dataset_name, data_args.dataset_config_name
+    raw = load_dataset(name, cfgname, streaming=data_args.streaming)
+    if data_args.streaming:
+        col = _text_column(raw["train"])
+        if "validation" in raw:
+            train = StreamingBlockDataset(raw["train"], tokenizer, block_size, col, max_blocks=data_args.max_train_samples,
+                                          infinite=True)
+            valid = StreamingBlockDataset(raw["validation"], tokenizer, block_size, col, max_blocks=data_args.max_eval_samples)
+        else:
+            n_val = data_args.max_eval_samples or 1000
+            train = StreamingBlockDataset(raw["train"], tokenizer, block_size, col, skip=n_val,
+                                          max_blocks=data_args.max_train_samples, infinite=True)
+            valid = StreamingBlockDataset(raw["train"], tokenizer, block_size, col, take=n_val,
+                                          max_blocks=data_args.max_eval_samples)
+        return train, valid
     if "validation" not in raw:
         pct = data_args.validation_split_percentage
-        raw = {"validation": load_dataset(data_args.dataset_name, data_args.dataset_config_name, split=f"train[:{pct}%]"),
-               "train": load_dataset(data_args.dataset_name, data_args.dataset_config_name, split=f"train[{pct}%:]")}
-    col = "text" if "text" in raw["train"].column_names else raw["train"].column_names[0]
+        raw = {"validation": load_dataset(name, cfgname, split=f"train[:{pct}%]"),
+               "train": load_dataset(name, cfgname, split=f"train[{pct}%:]")}
     out = {}
-    for split in ("train", "validation"):
-        toks = (tokenizer(t)["input_ids"] for t in raw[split][col])
-        out[split] = BlockDataset(group_texts(toks, block_size))
+    for split, cap in (("train", data_args.max_train_samples), ("validation", data_args.max_eval_samples)):
+        ds = raw[split]
+        col = _text_column(ds)
+        fp = str(getattr(ds, "_fingerprint", "")) or f"{len(ds)}"
+        d = tokenize_text_iterable((ex[col] for ex in ds), tokenizer, f"{name}-{cfgname}-{split}",
+                                   num_workers=data_args.preprocessing_num_workers,
+                                   overwrite_cache=data_args.overwrite_cache, fingerprint=fp)
+        out[split] = MemmapBlockDataset(d, block_size, max_blocks=cap)
     return out["train"], out["validation"]
 
 
@@ -145,14 +182,14 @@ def main(argv=None):
             with main_process_first():            # reference: run_clm.py:474,531
                 train_dataset, eval_dataset = _hub_dataset(data_args, tokenizer, block_size)
         else:
-            train_dataset = text_file_dataset(data_args.train_file, tokenizer, block_size, data_args.keep_linebreaks) \
-                if data_args.train_file else None
-            eval_dataset = text_file_dataset(data_args.validation_file, tokenizer, block_size,
-                                             data_args.keep_linebreaks) if data_args.validation_file else None
-        if data_args.max_train_samples and train_dataset is not None:
-            train_dataset.blocks = train_dataset.blocks[: data_args.max_train_samples]
-        if data_args.max_eval_samples and eval_dataset is not None:
-            eval_dataset.blocks = eval_dataset.blocks[: data_args.max_eval_samples]
+            kw = dict(num_workers=data_args.preprocessing_num_workers, overwrite_cache=data_args.overwrite_cache)
+            with main_process_first():            # rank 0 tokenises into the cache, the others open it
+                train_dataset = text_file_dataset(data_args.train_file, tokenizer, block_size, data_args.keep_linebreaks,
+                                                  max_blocks=data_args.max_train_samples, **kw) \
+                    if data_args.train_file else None
+                eval_dataset = text_file_dataset(data_args.validation_file, tokenizer, block_size,
+                                                 data_args.keep_linebreaks, max_blocks=data_args.max_eval_samples, **kw) \
+                    if data_args.validation_file else None
 
     def preprocess_logits_for_metrics(logits, labels):
         return logits.argmax(dim=-1)
@@ -166,6 +203,8 @@ def main(argv=None):
     optimizers = (None, None)
     if training_args.lion:
         if training_args.max_steps <= 0:
+            if not hasattr(train_dataset, "__len__"):
+                raise ValueError("a streaming dataset has no length: pass --max_steps (as HF's Trainer requires too)")
             per_epoch = len(train_dataset) // (training_args.per_device_train_batch_size * training_args.world_size
                                                * training_args.gradient_accumulation_steps)
             training_args.max_steps = max(int(training_args.num_train_epochs * per_epoch), 1)

@@ -68,3 +68,34 @@ def test_dpo_llama_on_gpu(tmp_path):
         "--eval_steps", "3", "--save_steps", "100", "--output_dir", str(out)])
     assert _launches() - n0 > 50
     assert (out / "final_checkpoint").is_dir()
+
+
+def test_fp16_training_uses_dynamic_loss_scaling(tmp_path):
+    """``--fp16`` / a float16 model (reference: dpo_llama2.py:133-139 loads its models in float16): the trainer scales
+    the loss, unscales the gradients before clipping, skips a step whose gradients overflow and halves the scale."""
+    import torch
+    from distributed_lion import Lion
+    from distributed_lion_pytorch_b200.models import build_model
+    from distributed_lion_pytorch_b200.train import AsyncTrainer, TrainingArguments, get_cosine_schedule_with_warmup
+    dev = torch.device("cuda")
+    torch.manual_seed(0)
+    model = build_model("gpt2-tiny", dtype=torch.float16, device=dev, pretrained=False)
+    opt = Lion(model.parameters(), lr=1e-3, weight_decay=0.0)
+    tr = AsyncTrainer(model=model, args=TrainingArguments(output_dir=str(tmp_path), gradient_accumulation_steps=2, lion=True,
+                                                          async_grad=True, max_grad_norm=1.0),
+                      optimizers=(opt, get_cosine_schedule_with_warmup(opt, 1, 100)))
+    assert tr.loss_scaler is not None and tr.loss_scaler.scale == 2.0 ** 16
+    tr.loss_scaler.scale = 2.0 ** 30          # certain to overflow fp16 gradients at first
+    ids = torch.randint(0, 512, (2, 32), device=dev)
+    batch = {"input_ids": ids, "labels": ids}
+    before = [p.detach().clone() for p in model.parameters()]
+    scales, moved = [], []
+    for _ in range(24):
+        loss = tr.train_step([batch, batch])
+        assert torch.isfinite(loss)
+        scales.append(tr.loss_scaler.scale)
+        moved.append(not all(torch.equal(a, p.detach()) for a, p in zip(before, model.parameters())))
+    # a scale of 2^30 overflows fp16 gradients: those steps are skipped and the scale halves until the gradients fit
+    assert tr.loss_scaler.skipped >= 1 and scales[-1] < 2.0 ** 30
+    assert not moved[0] and moved[-1]                       # skipped steps apply nothing; later steps train
+    assert all(torch.isfinite(p).all() for p in model.parameters())

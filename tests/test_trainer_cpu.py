@@ -296,3 +296,45 @@ def test_trainer_detects_and_repairs_a_diverged_replica(tmp_path):
     assert all(o["err"] is not None and "diverged" in o["err"] and o["step"] == 3 for o in outs)
     outs = run_distributed(_worker_divergence, 2, str(tmp_path / "c"), "off")
     assert all(o["err"] is None and not o["checks"] for o in outs) and not torch.equal(outs[0]["params"], outs[1]["params"])
+
+
+def test_hf_trainer_subclass_wraps_training_step_in_no_sync(monkeypatch):
+    """reference: async_trainer.py:8-34 — the HF ``Trainer`` subclass whose ``training_step`` runs under
+    ``model.no_sync()``.  HF's Trainer cannot be *constructed* on this image (no accelerate), so the class is built
+    and its ``training_step`` is driven on an un-initialised instance with HF's own step stubbed out: the override must
+    enter ``no_sync`` exactly once around the parent call, pass ``num_items_in_batch`` through, and also work for a
+    model that has no ``no_sync`` (one process)."""
+    import transformers
+    from async_trainer import hf_async_trainer_class
+    calls = []
+    monkeypatch.setattr(transformers.Trainer, "training_step",
+                        lambda self, model, inputs, num_items_in_batch=None: calls.append(("step", model.depth, num_items_in_batch)) or 7)
+    cls = hf_async_trainer_class()
+    assert issubclass(cls, transformers.Trainer)
+    tr = object.__new__(cls)
+
+    class _DDPLike:
+        depth = 0
+
+        def no_sync(self):
+            import contextlib
+
+            @contextlib.contextmanager
+            def cm():
+                self.depth += 1
+                calls.append(("enter", self.depth))
+                try:
+                    yield
+                finally:
+                    self.depth -= 1
+                    calls.append(("exit", self.depth))
+            return cm()
+
+    m = _DDPLike()
+    assert tr.training_step(m, {"x": 1}, num_items_in_batch=5) == 7
+    assert calls == [("enter", 1), ("step", 1, 5), ("exit", 0)]          # HF's step ran INSIDE no_sync
+    calls.clear()
+
+    class _Plain:
+        depth = 0
+    assert tr.training_step(_Plain(), {}) == 7 and calls == [("step", 0, None)]
