@@ -257,6 +257,150 @@ static bool try_launch_reg(void* logits, const int64_t* labels, float* loss, con
   return false;
 }
 
+
+// ------------------------------------------------------------------ row-resident variant (16-bit logits)
+// One persistent CTA per SM keeps TWO whole rows in shared memory (a GPT-2 row is 100 KB, a Llama row 64 KB): while
+// the CTA works on row i out of buffer i & 1, the TMA engine (cp.async.bulk, completion counted on an mbarrier)
+// already brings row i + 1 into the other buffer.  Every logit is read from HBM exactly once; both passes (online
+// max / sum of exp, then the gradient) read shared memory; the gradient goes out as coalesced 16-byte stores.
+// Against the streaming kernel above that is 2 passes over HBM instead of 3, with the loads fully overlapped.
+__device__ __forceinline__ uint32_t ce_smem_u32(const void* ptr) { return (uint32_t)__cvta_generic_to_shared(ptr); }
+
+template <typename T, int MODE>
+__global__ void __launch_bounds__(kCEThreads, 1) ce_rowres_kernel(T* __restrict__ logits, const int64_t* __restrict__ labels,
+                                                                  float* __restrict__ loss,
+                                                                  const float* __restrict__ row_scale, int64_t rows,
+                                                                  int vocab, int64_t row_stride, int64_t ignore_index,
+                                                                  float grad_scale) {
+  extern __shared__ __align__(128) uint8_t ce_smem[];
+  __shared__ MaxSum red[32];
+  __shared__ __align__(8) uint64_t full[2];
+  const uint32_t row_bytes = (uint32_t)row_stride * (uint32_t)sizeof(T);
+  const uint32_t buf_bytes = (row_bytes + 127u) & ~127u;
+  const int nvec = vocab >> 3;
+  const int tail0 = nvec << 3;
+  const int padded_vecs = (int)(row_stride >> 3);
+  constexpr float kLog2e = 1.4426950408889634f;
+  if (threadIdx.x == 0) {
+    for (int b = 0; b < 2; ++b)
+      asm volatile("mbarrier.init.shared::cta.b64 [%0], 1;" ::"r"(ce_smem_u32(&full[b])) : "memory");
+    asm volatile("fence.mbarrier_init.release.cluster;" ::: "memory");
+    asm volatile("fence.proxy.async.shared::cta;" ::: "memory");
+  }
+  __syncthreads();
+  auto issue = [&](int64_t row, int b) {      // thread 0 only
+    const uint32_t bar = ce_smem_u32(&full[b]);
+    asm volatile("{\n .reg .b64 st;\n mbarrier.arrive.expect_tx.shared::cta.b64 st, [%0], %1;\n}" ::"r"(bar), "r"(row_bytes) : "memory");
+    asm volatile("cp.async.bulk.shared::cluster.global.mbarrier::complete_tx::bytes [%0], [%1], %2, [%3];" ::"r"(
+                     ce_smem_u32(ce_smem + (size_t)b * buf_bytes)),
+                 "l"(logits + row * row_stride), "r"(row_bytes), "r"(bar)
+                 : "memory");
+  };
+  const int64_t first = blockIdx.x;
+  if (threadIdx.x == 0 && first < rows) issue(first, 0);
+  int it = 0;
+  for (int64_t row = first; row < rows; row += gridDim.x, ++it) {
+    const int b = it & 1;
+    const int64_t next = row + gridDim.x;
+    // buffer b ^ 1 was last read in iteration it - 1, which ended with a block barrier: safe to refill
+    if (threadIdx.x == 0 && next < rows) issue(next, b ^ 1);
+    {   // wait for this row's bytes (phase parity = number of earlier uses of this barrier, mod 2)
+      const uint32_t bar = ce_smem_u32(&full[b]);
+      const uint32_t parity = (uint32_t)((it >> 1) & 1);
+      uint32_t ok = 0;
+      while (!ok)
+        asm volatile("{\n .reg .pred p;\n mbarrier.try_wait.parity.shared::cta.b64 p, [%1], %2;\n selp.u32 %0, 1, 0, p;\n}"
+                     : "=r"(ok) : "r"(bar), "r"(parity) : "memory");
+    }
+    const T* x = reinterpret_cast<const T*>(ce_smem + (size_t)b * buf_bytes);
+    T* gx = logits + row * row_stride;
+    const int64_t label = labels[row];
+    const bool ignored = label == ignore_index || label < 0 || label >= vocab;
+    float scale = grad_scale;
+    if (MODE == 2) scale = row_scale[row];
+    if (ignored) {
+      if (MODE != 2 && threadIdx.x == 0 && loss != nullptr) loss[row] = 0.f;
+      if (MODE != 0) {
+        const float zeros[8] = {0.f, 0.f, 0.f, 0.f, 0.f, 0.f, 0.f, 0.f};
+        for (int j = threadIdx.x; j < padded_vecs; j += kCEThreads) store8<T>(gx + j * 8, zeros);
+      }
+      __syncthreads();
+      continue;   // block-uniform
+    }
+    MaxSum acc{-CUDART_INF_F, 0.f};
+    for (int j = threadIdx.x; j < nvec; j += kCEThreads) {
+      float f[8];
+      load8<T>(x + j * 8, f);
+      float mx = f[0];
+#pragma unroll
+      for (int i = 1; i < 8; ++i) mx = fmaxf(mx, f[i]);
+      const float m = fmaxf(acc.m, mx);
+      const float ms = m * kLog2e;
+      float sacc = acc.s * fast_exp2(fmaf(acc.m, kLog2e, -ms));
+#pragma unroll
+      for (int i = 0; i < 8; ++i) sacc += fast_exp2(fmaf(f[i], kLog2e, -ms));
+      acc = {m, sacc};
+    }
+    if (threadIdx.x < vocab - tail0) {
+      const float f = DT<T>::to_f(x[tail0 + threadIdx.x]);
+      acc = combine(acc, MaxSum{f, 1.f});
+    }
+    const MaxSum tot = block_maxsum(acc, red);
+    const float lse = tot.m + logf(tot.s);
+    if (MODE != 2 && threadIdx.x == 0 && loss != nullptr) loss[row] = lse - DT<T>::to_f(x[label]);
+    if (MODE != 0) {
+      const float inv = scale / tot.s;
+      const float mxs = tot.m * kLog2e;
+      const int label_vec = (int)(label >> 3), label_lane = (int)(label & 7);
+      for (int j = threadIdx.x; j < padded_vecs; j += kCEThreads) {
+        float f[8];
+        load8<T>(x + j * 8, f);
+#pragma unroll
+        for (int i = 0; i < 8; ++i) f[i] = fast_exp2(fmaf(f[i], kLog2e, -mxs)) * inv;
+        if (j >= nvec) {
+#pragma unroll
+          for (int i = 0; i < 8; ++i)
+            if (j * 8 + i >= vocab) f[i] = 0.f;
+        }
+        if (j == label_vec) {
+#pragma unroll
+          for (int i = 0; i < 8; ++i)
+            if (i == label_lane) f[i] -= scale;
+        }
+        store8<T>(gx + j * 8, f);
+      }
+    }
+    __syncthreads();   // everyone is done with buffer b (and with red[]) before it is refilled / reused
+  }
+}
+
+template <typename T, int MODE>
+static bool try_launch_rowres(void* logits, const int64_t* labels, float* loss, const float* row_scale, int64_t rows,
+                              int vocab, int64_t row_stride, int64_t ignore_index, float grad_scale, cudaStream_t s) {
+  if (sizeof(T) != 2) return false;
+  static const bool off = getenv("DLION_CE_STREAMING") != nullptr;      // force the streaming kernel (A/B)
+  if (off) return false;
+  const size_t buf = ((size_t)row_stride * sizeof(T) + 127) & ~(size_t)127;
+  const size_t smem = 2 * buf;
+  if (smem > 220 * 1024 || row_stride * sizeof(T) >= (1u << 20) || rows < 1) return false;
+  static thread_local int configured_dev = -1;
+  static thread_local size_t configured_smem = 0;
+  int dev = 0;
+  if (cudaGetDevice(&dev) != cudaSuccess) return false;
+  if (dev != configured_dev || smem > configured_smem) {
+    if (cudaFuncSetAttribute(ce_rowres_kernel<T, MODE>, cudaFuncAttributeMaxDynamicSharedMemorySize, 220 * 1024) != cudaSuccess) {
+      cudaGetLastError();
+      return false;
+    }
+    configured_dev = dev;
+    configured_smem = 220 * 1024;
+  }
+  const int grid = (int)(rows < kNumSMs ? rows : kNumSMs);
+  ce_rowres_kernel<T, MODE><<<grid, kCEThreads, smem, s>>>((T*)logits, labels, loss, row_scale, rows, vocab, row_stride,
+                                                           ignore_index, grad_scale);
+  return true;
+}
+
 template <int MODE>
 static int launch(void* logits, const int64_t* labels, float* loss, const float* row_scale, int64_t rows, int vocab,
                   int64_t row_stride, int64_t ignore_index, float grad_scale, int dtype, cudaStream_t s) {
@@ -266,7 +410,8 @@ static int launch(void* logits, const int64_t* labels, float* loss, const float*
   const int grid1 = (int)(rows < cap1 ? rows : cap1);
   DISPATCH_DTYPE(dtype, {
     if (!try_launch_reg<T, MODE>(logits, labels, loss, row_scale, rows, vocab, row_stride, ignore_index, grad_scale,
-                                 grid1, s))
+                                 grid1, s) &&
+        !try_launch_rowres<T, MODE>(logits, labels, loss, row_scale, rows, vocab, row_stride, ignore_index, grad_scale, s))
       ce_kernel<T, MODE><<<grid, kCEThreads, 0, s>>>((T*)logits, labels, loss, row_scale, rows, vocab, row_stride,
                                                       ignore_index, grad_scale);
   });

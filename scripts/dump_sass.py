@@ -39,6 +39,9 @@ WANT = {
     "swiglu_fwd_kernel": [("bf16", r"swiglu_fwd_kernelI13__nv_bfloat16")],
     "swiglu_bwd_kernel": [("bf16", r"swiglu_bwd_kernelI13__nv_bfloat16")],
     "rope_kernel": [("bf16", r"rope_kernelI13__nv_bfloat16")],
+    "ce_rowres_kernel": [("bf16_fwd_bwd", r"ce_rowres_kernelI13__nv_bfloat16Li1E")],
+    "embed_fwd_kernel": [("bf16", r"embed_fwd_kernelI13__nv_bfloat16")],
+    "embed_bwd_sorted_kernel": [("bf16", r"embed_bwd_sorted_kernelI13__nv_bfloat16")],
     "ce_kernel": [("bf16_fwd_bwd", r"ce_kernelI13__nv_bfloat16Li1E"), ("bf16_rowscale", r"ce_kernelI13__nv_bfloat16Li2E")],
     "q4_quantize_kernel": [("bf16", r"q4_quantize_kernelI13__nv_bfloat16")],
     "q4_dequantize_kernel": [("bf16", r"q4_dequantize_kernelI13__nv_bfloat16")],
