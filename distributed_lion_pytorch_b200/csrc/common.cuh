@@ -254,6 +254,25 @@ __device__ __forceinline__ void hash_bits8(uint64_t key, int64_t vec, uint32_t (
 #pragma unroll
   for (int i = 0; i < 4; ++i) r[i] = mix32(base + (uint32_t)i * 0x85EBCA6Bu + hi);
 }
+// Dropout fused into the residual add: keep-mask bits for the 8 elements of vector `vec` of the
+// whole [rows, cols] tensor, regenerated (not stored) in the backward from (seed, vec): keep iff a
+// 16-bit uniform >= p * 65536.
+// mix32 (the counter hash) lives in common.cuh
+__device__ __forceinline__ uint32_t keep_mask8(uint64_t seed, int64_t vec, uint32_t thr16) {
+  // four counter-based 32-bit hashes -> eight 16-bit uniforms (Philox4x32-10 here made the norm
+  // kernels issue-bound: ~70 instructions per 8 elements against ~25 for this)
+  const uint32_t lo = (uint32_t)seed, hi = (uint32_t)(seed >> 32);
+  const uint32_t base = mix32((uint32_t)vec * 0x9E3779B9u + lo) ^ mix32((uint32_t)(vec >> 32) + hi);
+  uint32_t mask = 0;
+#pragma unroll
+  for (int i = 0; i < 4; ++i) {
+    const uint32_t w = mix32(base + (uint32_t)i * 0x85EBCA6Bu + hi);
+    mask |= ((w & 0xffffu) >= thr16 ? 1u : 0u) << (2 * i);
+    mask |= ((w >> 16) >= thr16 ? 1u : 0u) << (2 * i + 1);
+  }
+  return mask;
+}
+
 template <typename T>
 struct SrCapable { static constexpr bool value = false; };
 template <>
@@ -348,6 +367,13 @@ __device__ __forceinline__ uint32_t sign_byte(const float (&m)[8], const float (
   }
   return byte;
 }
+
+// norm_tma.cu: TMA tile-ring forward for cols = 256 / 512 / 768 / 1024 (dispatched from dlion_norm_fwd)
+bool norm_tma_ok(int cols);
+template <typename T>
+int launch_norm_fwd_tma(const void* x, const void* res, const void* w, const void* b, void* y, void* sum_out, float* mean,
+                        float* rstd, int64_t rows, int cols, float eps, bool rms, bool drop, float inv_keep, uint32_t thr16,
+                        uint64_t seed, cudaStream_t s);
 
 // direction u for one element given the +1 count among L live workers
 __device__ __forceinline__ float vote_dir(int cnt, int L, int vote) {

@@ -31,24 +31,7 @@ __device__ __forceinline__ float block_allreduce_sum(float v, float* smem) {
   return v;
 }
 
-// Dropout fused into the residual add: keep-mask bits for the 8 elements of vector `vec` of the
-// whole [rows, cols] tensor, regenerated (not stored) in the backward from (seed, vec): keep iff a
-// 16-bit uniform >= p * 65536.
-// mix32 (the counter hash) lives in common.cuh
-__device__ __forceinline__ uint32_t keep_mask8(uint64_t seed, int64_t vec, uint32_t thr16) {
-  // four counter-based 32-bit hashes -> eight 16-bit uniforms (Philox4x32-10 here made the norm
-  // kernels issue-bound: ~70 instructions per 8 elements against ~25 for this)
-  const uint32_t lo = (uint32_t)seed, hi = (uint32_t)(seed >> 32);
-  const uint32_t base = mix32((uint32_t)vec * 0x9E3779B9u + lo) ^ mix32((uint32_t)(vec >> 32) + hi);
-  uint32_t mask = 0;
-#pragma unroll
-  for (int i = 0; i < 4; ++i) {
-    const uint32_t w = mix32(base + (uint32_t)i * 0x85EBCA6Bu + hi);
-    mask |= ((w & 0xffffu) >= thr16 ? 1u : 0u) << (2 * i);
-    mask |= ((w >> 16) >= thr16 ? 1u : 0u) << (2 * i + 1);
-  }
-  return mask;
-}
+// keep_mask8 (the dropout keep-mask of one 8-element vector) lives in common.cuh: norm_tma.cu shares it
 
 // Thread t owns vectors t, t+BLOCK, ... (VPT of them); vector j covers columns [8j, 8j+8).
 template <typename T, int VPT, int BLOCK, bool RMS, bool DROP>
@@ -531,6 +514,10 @@ extern "C" int dlion_norm_fwd(const void* x, const void* residual, const void* w
   if (rows == 0) return 0;
   cudaStream_t s = (cudaStream_t)stream;
   const DropArgs d = make_drop(drop_p, drop_seed);
+  if (norm_tma_ok(cols)) {      // narrow rows: TMA tile ring + warp-per-row kernel (norm_tma.cu)
+    DISPATCH_DTYPE(dtype, return launch_norm_fwd_tma<T>(x, residual, weight, bias, y, sum_out, mean, rstd, rows, cols, eps,
+                                                        rms != 0, d.on, d.inv_keep, d.thr16, d.seed, s));
+  }
   switch (dtype) {
     case DLION_F32: return fwd_t<float>(x, residual, weight, bias, y, sum_out, mean, rstd, rows, cols, eps, rms, d, s);
     case DLION_BF16:

@@ -28,6 +28,7 @@ WANT = {
     "clip_scale_kernel": [("bf16", r"clip_scale_kernelI13__nv_bfloat16")],
     "norm_fwd_kernel": [("bf16_ln768_dropout", r"norm_fwd_kernelI13__nv_bfloat16Li1ELi96ELb0ELb1"),
                         ("bf16_rms4096", r"norm_fwd_kernelI13__nv_bfloat16Li4ELi256ELb1ELb0")],
+    "norm_fwd_tma_kernel": [("bf16_ln768_dropout", r"norm_fwd_tma_kernelI13__nv_bfloat16Li3ELb0ELb1")],
     "norm_bwd_kernel": [("bf16_ln768_dropout_dxsum", r"norm_bwd_kernelI13__nv_bfloat16Li1ELi96ELb0ELi1ELb1ELb1"),
                         ("bf16_rms4096", r"norm_bwd_kernelI13__nv_bfloat16Li4ELi256ELb1ELi1ELb0ELb0")],
     "norm_bwd_finalize_kernel": [("bf16", r"norm_bwd_finalize_kernelI13__nv_bfloat16")],
