@@ -114,8 +114,12 @@ def gather_grads(b: Bucket, *, use_kernel: bool = True, untouched_is_missing: bo
         elif g.is_sparse:
             raise RuntimeError("Lion does not support sparse gradients")
         elif g.data_ptr() == gv.data_ptr() and g.dtype == gv.dtype:
-            if untouched_is_missing and touched is False:
-                missing.append(i)       # aliased, and nothing accumulated into it: "grad is None" upstream
+            if untouched_is_missing and touched is False and not bool(gv.any()):
+                # aliased, no backward pass wrote to it since the last step AND it still holds the zeros of
+                # zero_grad(): "grad is None" upstream.  (A caller who fills .grad by hand — copy_ into the aliased
+                # view — leaves no mark but leaves non-zero values: that parameter HAS a gradient.  The check syncs,
+                # and only runs for parameters without a mark: none in an ordinary training step.)
+                missing.append(i)
             continue
         else:
             src.append(g)

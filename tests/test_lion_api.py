@@ -298,3 +298,21 @@ def test_clip_grad_norm_eager_path_matches_torch():
         o2.step()
     for a, b in zip(m1.parameters(), m2.parameters()):
         assert torch.equal(a, b)
+
+
+def test_gradients_written_by_hand_into_the_aliased_views_are_used():
+    """From the second step on ``p.grad`` aliases the flat bucket.  A caller who fills it without a backward pass
+    (``p.grad.copy_(...)``) leaves no "written" mark; the parameter must still be updated (it is only skipped when its
+    gradient also still holds the zeros of ``zero_grad()``)."""
+    torch.manual_seed(0)
+    p = torch.nn.Parameter(torch.randn(40))
+    q = torch.nn.Parameter(torch.randn(24))
+    opt = Lion([p, q], lr=1e-2, weight_decay=0.0)
+    (p.sum() + q.sum()).backward()                    # step 1: ordinary backward, buckets get built
+    opt.step()
+    opt.zero_grad()
+    before_p, before_q = p.detach().clone(), q.detach().clone()
+    p.grad.copy_(torch.ones(40))                      # step 2: by hand, q gets nothing
+    opt.step()
+    assert not torch.equal(p.detach(), before_p)      # p moved
+    assert torch.equal(q.detach(), before_q)          # q (no gradient this step) is left untouched, as upstream
