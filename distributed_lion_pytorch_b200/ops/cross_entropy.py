@@ -21,7 +21,7 @@ from typing import Optional
 import torch
 import torch.nn.functional as F
 
-from . import _cabi, require_library
+from . import _cabi, lm_head, require_library
 
 IGNORE_INDEX = -100
 _DEFAULT_CHUNK = int(os.environ.get("DLION_CE_CHUNK", "4096"))   # rows of logits alive at a time
@@ -55,6 +55,7 @@ def _compute_dtype(h: torch.Tensor) -> torch.dtype:
     return h.dtype
 
 
+_FUSED_FWD = os.environ.get("DLION_LMHEAD_FUSED_FWD", "0") == "1"   # forward of linear_log_probs WITH grad on the tcgen05 kernel
 _EMULATE = os.environ.get("DLION_EMULATE_KERNELS") == "1"   # CPU stand-ins, to test the autograd plumbing
 
 
@@ -157,6 +158,12 @@ class _LinearLogProbs(torch.autograd.Function):
         V = weight.shape[0]
         cd = _compute_dtype(h)
         hq = h if h.dtype == cd else h.to(cd)
+        ctx.save_for_backward(h, weight, labels)
+        ctx.ignore_index, ctx.chunk, ctx.cd = ignore_index, chunk, cd
+        if _FUSED_FWD and ignore_index < 0 and N > 0 and lm_head.supported(hq, weight, cd):
+            # forward half on the tcgen05 kernel (no logits block, no padded head); backward recomputes blocks below
+            with _no_autocast(h):
+                return lm_head.lm_head_log_probs(hq, weight if weight.dtype == cd else weight.to(cd), labels, want_lse=False)[0]
         wp = _pad_rows(weight if weight.dtype == cd else weight.to(cd))
         losses = torch.empty(N, dtype=torch.float32, device=h.device)
         with _device_guard(h), _no_autocast(h):
@@ -164,8 +171,6 @@ class _LinearLogProbs(torch.autograd.Function):
                 e = min(N, s + chunk)
                 logits = hq[s:e] @ wp.t()
                 _ce_kernel(logits, labels[s:e], losses[s:e], V, ignore_index, False)
-        ctx.save_for_backward(h, weight, labels)
-        ctx.ignore_index, ctx.chunk, ctx.cd = ignore_index, chunk, cd
         return -losses
 
     @staticmethod
@@ -198,9 +203,26 @@ class _LinearLogProbs(torch.autograd.Function):
             None, None, None
 
 
+def _fused_no_grad(h: torch.Tensor, weight: torch.Tensor, labels: torch.Tensor, ignore_index: int):
+    """(hq, wq) when this call needs no gradient and the tcgen05 LM-head kernel (``ops/lm_head.py``) applies:
+    log-probabilities straight out of TMEM, no logits block, no padded copy of the head.  Else None."""
+    if torch.is_grad_enabled() and (h.requires_grad or weight.requires_grad):
+        return None
+    if ignore_index >= 0 or not h.is_cuda or h.shape[0] == 0:
+        return None
+    cd = _compute_dtype(h)
+    if not lm_head.supported(h, weight, cd):
+        return None
+    return (h if h.dtype == cd else h.to(cd)), (weight if weight.dtype == cd else weight.to(cd))
+
+
 def linear_cross_entropy(h: torch.Tensor, weight: torch.Tensor, labels: torch.Tensor,
                          ignore_index: int = IGNORE_INDEX, chunk: Optional[int] = None) -> torch.Tensor:
     """h: [N, H], weight: [V, H], labels: [N] int64 → scalar mean CE over non-ignored rows."""
+    fused = _fused_no_grad(h, weight, labels, ignore_index)
+    if fused is not None:
+        logp, _ = lm_head.lm_head_log_probs(fused[0], fused[1], labels, want_lse=False)
+        return -logp.sum() / (labels != ignore_index).sum().clamp_(min=1).to(torch.float32)
     if _kernel_ok(h):
         return _LinearCE.apply(h.contiguous(), weight, labels.contiguous(), ignore_index, chunk or _DEFAULT_CHUNK)
     # CPU / fallback: still chunked so memory stays bounded
@@ -215,6 +237,9 @@ def linear_cross_entropy(h: torch.Tensor, weight: torch.Tensor, labels: torch.Te
 def linear_log_probs(h: torch.Tensor, weight: torch.Tensor, labels: torch.Tensor,
                      ignore_index: int = IGNORE_INDEX, chunk: Optional[int] = None) -> torch.Tensor:
     """Per-token log p(label) as fp32 [N]; ignored positions give 0."""
+    fused = _fused_no_grad(h, weight, labels, ignore_index)
+    if fused is not None:
+        return lm_head.lm_head_log_probs(fused[0], fused[1], labels, want_lse=False)[0]
     if _kernel_ok(h):
         return _LinearLogProbs.apply(h.contiguous(), weight, labels.contiguous(), ignore_index,
                                      chunk or _DEFAULT_CHUNK)

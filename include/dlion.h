@@ -24,7 +24,7 @@
 extern "C" {
 #endif
 
-#define DLION_VERSION 101
+#define DLION_VERSION 102
 
 typedef enum { DLION_F32 = 0, DLION_BF16 = 1, DLION_F16 = 2 } dlion_dtype;
 
@@ -309,6 +309,19 @@ int dlion_ce_fwd_bwd(void* logits, const int64_t* labels, float* loss, int64_t r
 /* per-row backward scale variant used by DPO: logits <- (softmax - onehot) * row_scale[row] */
 int dlion_ce_bwd_rowscale(void* logits, const int64_t* labels, const float* row_scale, int64_t rows,
                           int vocab, int64_t row_stride, int64_t ignore_index, int dtype, void* stream);
+
+/* N5, no-grad side — vocabulary projection fused with log-sum-exp on the tcgen05 tensor cores (TMA-fed, TMEM
+ * accumulators): lse[r] = log sum_v exp(h[r] . w[v]) and logp[r] = h[r] . w[labels[r]] - lse[r] (0 where the label is
+ * outside [0, vocab), e.g. -100) without a [rows, vocab] logits tensor in HBM.  h [rows, hidden] and w [vocab, hidden]
+ * are bf16 / fp16, row-major with row strides ld_h / ld_w elements (multiples of 8), 16-byte aligned.  logp or lse may
+ * be NULL; labels may be NULL when logp is.  `workspace` holds dlion_lmhead_plan()'s number of floats; `status`
+ * (device int, may be NULL) receives a code before the kernel traps if one of its bounded pipeline waits expires.
+ * reference: HF ForCausalLM evaluation loss (run_clm.py:626-639); TRL DPOTrainer reference-model log-probs
+ * (dpo_llama2.py:219-231). */
+int dlion_lmhead_plan(int rows, int vocab, int* splits, int64_t* workspace_floats);
+int dlion_lmhead_logprobs(const void* h, int64_t ld_h, const void* w, int64_t ld_w, const int64_t* labels, float* logp,
+                          float* lse, float* workspace, int64_t workspace_floats, int* status, int rows, int vocab,
+                          int hidden, int dtype, void* stream);
 
 /* Blockwise 4-bit weight codec for frozen LoRA base weights (bitsandbytes layout: element 2i in
  * the high nibble of byte i, one fp32 absmax per `blocksize` elements, 16-entry code book given
