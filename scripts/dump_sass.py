@@ -44,6 +44,8 @@ WANT = {
     "embed_fwd_kernel": [("bf16", r"embed_fwd_kernelI13__nv_bfloat16")],
     "embed_bwd_sorted_kernel": [("bf16", r"embed_bwd_sorted_kernelI13__nv_bfloat16")],
     "ce_kernel": [("bf16_fwd_bwd", r"ce_kernelI13__nv_bfloat16Li1E"), ("bf16_rowscale", r"ce_kernelI13__nv_bfloat16Li2E")],
+    "lmhead_lse_kernel": [("tcgen05", r"lmhead_lse_kernel")],
+    "lmhead_merge_kernel": [("fp32", r"lmhead_merge_kernel")],
     "q4_quantize_kernel": [("bf16", r"q4_quantize_kernelI13__nv_bfloat16")],
     "q4_dequantize_kernel": [("bf16", r"q4_dequantize_kernelI13__nv_bfloat16")],
 }
@@ -87,7 +89,7 @@ def main():
     if missing:
         raise SystemExit("no SASS found for: " + ", ".join(missing))
     for name in sorted(funcs):
-        if "dlion" not in name or "13__nv_bfloat16" not in name and "lion_fused_kernelIfE" not in name:
+        if "dlion" not in name or ("13__nv_bfloat16" not in name and "lion_fused_kernelIfE" not in name and "lmhead" not in name):
             continue
         cnt = collections.Counter()
         n = 0
@@ -105,7 +107,9 @@ def main():
         "the stamp of the library built from the current `csrc/`.  Per kernel (bf16 instantiations; the fused kernel also\n"
         "fp32): total instructions and the memory / barrier / conversion mnemonics.  `UBLKCP.S.G` / `UBLKCP.G.S` =\n"
         "cp.async.bulk (TMA 1-D) global→shared / shared→global, `SYNCS.*` = mbarrier ops, `*.STRONG.SYS` = system-scope\n"
-        "accesses to peer-visible memory, `MEMBAR.*.SYS` = fence.acq_rel.sys, `F2FP.*.PACK_AB` = packed bf16 rounding.\n"
+        "accesses to peer-visible memory, `MEMBAR.*.SYS` = fence.acq_rel.sys, `F2FP.*.PACK_AB` = packed bf16 rounding;\n"
+        "`UTMALDG.2D` = cp.async.bulk.tensor.2d (TMA tile load), `UTCHMMA` = tcgen05.mma kind::f16, `UTCBAR` = tcgen05.commit,\n"
+        "`LDTM` = tcgen05.ld (TMEM to registers), `UTCATOMSWS` = tcgen05.alloc / dealloc (the LM-head kernel).\n"
         "Full listings of the kernels on the training path are the `*.sass` files beside this one.\n\n"
         + "\n".join(lines) + "\n")
     print(f"wrote {len(list(OUT.glob('*.sass')))} listings + SUMMARY.md for stamp {stamp[:16]}…")
