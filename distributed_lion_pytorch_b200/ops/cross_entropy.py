@@ -55,7 +55,7 @@ def _compute_dtype(h: torch.Tensor) -> torch.dtype:
     return h.dtype
 
 
-_FUSED_FWD = os.environ.get("DLION_LMHEAD_FUSED_FWD", "0") == "1"   # forward of linear_log_probs WITH grad on the tcgen05 kernel
+_FUSED_FWD = os.environ.get("DLION_LMHEAD_FUSED_FWD", "1") == "1"   # forward of linear_log_probs WITH grad on the tcgen05 kernel
 _EMULATE = os.environ.get("DLION_EMULATE_KERNELS") == "1"   # CPU stand-ins, to test the autograd plumbing
 
 
