@@ -25,14 +25,11 @@
 // reference: HF `ForCausalLM` loss inside Trainer.compute_loss (run_clm.py:588-639, evaluation at :626-639)
 // and TRL DPOTrainer's per-token log-probs of the frozen reference model (dpo_llama2.py:219-231) — upstream
 // both materialise fp32 [batch, seq, vocab] logits.
-#include <cuda.h>
-
-#include <mutex>
-
-#include "common.cuh"
+#include "tc05.cuh"
 
 namespace dlion {
 namespace lm {
+using namespace tc;
 
 constexpr int BM = 128;               // rows per tile (= TMEM lanes, = UMMA M)
 constexpr int BN = 256;               // vocabulary entries per tile (= UMMA N, = TMEM columns per accumulator)
@@ -45,104 +42,6 @@ constexpr int kStageBytes = kABytes + kBBytes;
 constexpr int kThreads = 192;
 constexpr int kTmemCols = 512;
 constexpr int kSmemBytes = kStages * kStageBytes + 1024 /* alignment slack */ + 256 /* barriers */;
-constexpr float kLog2e = 1.4426950408889634f;
-constexpr uint64_t kWaitNs = 10ull * 1000 * 1000 * 1000;
-
-__device__ __forceinline__ uint32_t smem_u32(const void* p) { return (uint32_t)__cvta_generic_to_shared(p); }
-__device__ __forceinline__ uint64_t timer_ns() {
-  uint64_t t;
-  asm volatile("mov.u64 %0, %%globaltimer;" : "=l"(t));
-  return t;
-}
-__device__ __forceinline__ void mbar_init(uint64_t* bar, uint32_t count) {
-  asm volatile("mbarrier.init.shared::cta.b64 [%0], %1;" ::"r"(smem_u32(bar)), "r"(count) : "memory");
-}
-__device__ __forceinline__ void mbar_arrive(uint64_t* bar) {
-  asm volatile("{\n .reg .b64 st;\n mbarrier.arrive.shared::cta.b64 st, [%0];\n}" ::"r"(smem_u32(bar)) : "memory");
-}
-__device__ __forceinline__ void mbar_expect_tx(uint64_t* bar, uint32_t bytes) {
-  asm volatile("{\n .reg .b64 st;\n mbarrier.arrive.expect_tx.shared::cta.b64 st, [%0], %1;\n}" ::"r"(smem_u32(bar)),
-               "r"(bytes)
-               : "memory");
-}
-__device__ __forceinline__ bool mbar_try(uint64_t* bar, uint32_t parity) {
-  uint32_t ok;
-  asm volatile("{\n .reg .pred p;\n mbarrier.try_wait.parity.shared::cta.b64 p, [%1], %2;\n selp.u32 %0, 1, 0, p;\n}"
-               : "=r"(ok)
-               : "r"(smem_u32(bar)), "r"(parity)
-               : "memory");
-  return ok != 0;
-}
-// bounded wait: a fault in the pipeline protocol ends in a trap (the launch fails), never in a hung GPU
-__device__ __forceinline__ void mbar_wait(uint64_t* bar, uint32_t parity, int* status, int code) {
-  if (mbar_try(bar, parity)) return;
-  const uint64_t t0 = timer_ns();
-  uint32_t n = 0;
-  while (!mbar_try(bar, parity)) {
-    if ((++n & 1023u) == 0 && timer_ns() - t0 > kWaitNs) {
-      if (status != nullptr) atomicExch(status, code);
-      __threadfence_system();
-      asm volatile("trap;");
-    }
-  }
-}
-// 2-D tiled TMA load (tensor map over this GPU's memory; no multicast): box lands at `dst`, bytes on `bar`
-__device__ __forceinline__ void tma_load_2d(void* dst, const CUtensorMap* map, int c_inner, int c_outer, uint64_t* bar) {
-  asm volatile("cp.async.bulk.tensor.2d.shared::cluster.global.mbarrier::complete_tx::bytes [%0], [%1, {%3, %4}], [%2];" ::"r"(
-                   smem_u32(dst)),
-               "l"(reinterpret_cast<uint64_t>(map)), "r"(smem_u32(bar)), "r"(c_inner), "r"(c_outer)
-               : "memory");
-}
-__device__ __forceinline__ void tma_prefetch_desc(const CUtensorMap* map) {
-  asm volatile("prefetch.tensormap [%0];" ::"l"(reinterpret_cast<uint64_t>(map)) : "memory");
-}
-__device__ __forceinline__ void tc_fence_before() { asm volatile("tcgen05.fence::before_thread_sync;" ::: "memory"); }
-__device__ __forceinline__ void tc_fence_after() { asm volatile("tcgen05.fence::after_thread_sync;" ::: "memory"); }
-// D[tmem] (+)= A[smem] · B[smem]^T, both operands K-major, issued by ONE thread for the CTA
-__device__ __forceinline__ void umma_f16(uint32_t tmem_d, uint64_t desc_a, uint64_t desc_b, uint32_t idesc, uint32_t accumulate) {
-  asm volatile(
-      "{\n .reg .pred p;\n setp.ne.b32 p, %4, 0;\n tcgen05.mma.cta_group::1.kind::f16 [%0], %1, %2, %3, p;\n}" ::"r"(tmem_d),
-      "l"(desc_a), "l"(desc_b), "r"(idesc), "r"(accumulate)
-      : "memory");
-}
-// arrive on `bar` once every tcgen05.mma issued so far by this thread has completed (implies fence::before_thread_sync)
-__device__ __forceinline__ void umma_commit(uint64_t* bar) {
-  asm volatile("tcgen05.commit.cta_group::1.mbarrier::arrive::one.shared::cluster.b64 [%0];" ::"r"(smem_u32(bar)) : "memory");
-}
-// shared-memory matrix descriptor, K-major operand in the canonical 128-byte-swizzle layout TMA writes:
-// rows 128 B apart, groups of 8 rows 1024 B apart (stride byte offset), version 1 (sm_100), layout type 2
-__device__ __forceinline__ uint64_t smem_desc_sw128(uint32_t addr) {
-  return (uint64_t)((addr & 0x3FFFFu) >> 4) | (1ull << 16) | ((uint64_t)(1024 >> 4) << 32) | (1ull << 46) | (2ull << 61);
-}
-// instruction descriptor: fp32 accumulate, A and B of format `fmt` (0 = f16, 1 = bf16), both K-major, M 128, N 256
-__host__ __device__ constexpr uint32_t instr_desc(uint32_t fmt) {
-  return (1u << 4) | (fmt << 7) | (fmt << 10) | ((uint32_t)(BN >> 3) << 17) | ((uint32_t)(BM >> 4) << 24);
-}
-__device__ __forceinline__ float ex2(float x) {
-  float y;
-  asm("ex2.approx.ftz.f32 %0, %1;" : "=f"(y) : "f"(x));
-  return y;
-}
-// 32 consecutive TMEM columns of this thread's lane -> 32 registers
-__device__ __forceinline__ void tmem_ld32(uint32_t taddr, float (&v)[32]) {
-  uint32_t r[32];
-  asm volatile(
-      "tcgen05.ld.sync.aligned.32x32b.x32.b32 {%0, %1, %2, %3, %4, %5, %6, %7, %8, %9, %10, %11, %12, %13, %14, %15, %16, "
-      "%17, %18, %19, %20, %21, %22, %23, %24, %25, %26, %27, %28, %29, %30, %31}, [%32];"
-      : "=r"(r[0]), "=r"(r[1]), "=r"(r[2]), "=r"(r[3]), "=r"(r[4]), "=r"(r[5]), "=r"(r[6]), "=r"(r[7]), "=r"(r[8]),
-        "=r"(r[9]), "=r"(r[10]), "=r"(r[11]), "=r"(r[12]), "=r"(r[13]), "=r"(r[14]), "=r"(r[15]), "=r"(r[16]),
-        "=r"(r[17]), "=r"(r[18]), "=r"(r[19]), "=r"(r[20]), "=r"(r[21]), "=r"(r[22]), "=r"(r[23]), "=r"(r[24]),
-        "=r"(r[25]), "=r"(r[26]), "=r"(r[27]), "=r"(r[28]), "=r"(r[29]), "=r"(r[30]), "=r"(r[31])
-      : "r"(taddr)
-      : "memory");
-  // the registers are named as in/out operands so that no use of them can be scheduled above the wait
-  asm volatile("tcgen05.wait::ld.sync.aligned;"
-               : "+r"(r[0]), "+r"(r[1]), "+r"(r[2]), "+r"(r[3]), "+r"(r[4]), "+r"(r[5]), "+r"(r[6]), "+r"(r[7]), "+r"(r[8]), "+r"(r[9]), "+r"(r[10]), "+r"(r[11]), "+r"(r[12]), "+r"(r[13]), "+r"(r[14]), "+r"(r[15]), "+r"(r[16]), "+r"(r[17]), "+r"(r[18]), "+r"(r[19]), "+r"(r[20]), "+r"(r[21]), "+r"(r[22]), "+r"(r[23]), "+r"(r[24]), "+r"(r[25]), "+r"(r[26]), "+r"(r[27]), "+r"(r[28]), "+r"(r[29]), "+r"(r[30]), "+r"(r[31])
-               :
-               : "memory");
-#pragma unroll
-  for (int i = 0; i < 32; ++i) v[i] = __uint_as_float(r[i]);
-}
 
 // online (max, sum exp) over 32 logits of one row; with MASK only the first `valid` of them exist
 template <bool MASK>
@@ -360,37 +259,6 @@ __global__ void __launch_bounds__(256) lmhead_merge_kernel(const float* __restri
   }
 }
 
-// ---- host side -------------------------------------------------------------------------------------------
-typedef CUresult (*EncodeTiledFn)(CUtensorMap*, CUtensorMapDataType, cuuint32_t, void*, const cuuint64_t*, const cuuint64_t*,
-                                  const cuuint32_t*, const cuuint32_t*, CUtensorMapInterleave, CUtensorMapSwizzle,
-                                  CUtensorMapL2promotion, CUtensorMapFloatOOBfill);
-
-static EncodeTiledFn encode_fn() {
-  static EncodeTiledFn fn = nullptr;
-  static std::once_flag once;
-  std::call_once(once, [] {
-    void* ptr = nullptr;
-    cudaDriverEntryPointQueryResult q;
-    if (cudaGetDriverEntryPoint("cuTensorMapEncodeTiled", &ptr, cudaEnableDefault, &q) == cudaSuccess &&
-        q == cudaDriverEntryPointSuccess)
-      fn = reinterpret_cast<EncodeTiledFn>(ptr);
-  });
-  return fn;
-}
-
-// [outer, inner] 16-bit matrix, `ld` elements between rows, box [box_outer, 64], 128-byte swizzle, zero fill
-static bool make_map(CUtensorMap* map, const void* base, int64_t inner, int64_t outer, int64_t ld, int box_outer, int dtype) {
-  EncodeTiledFn fn = encode_fn();
-  if (fn == nullptr) return false;
-  const cuuint64_t dims[2] = {(cuuint64_t)inner, (cuuint64_t)outer};
-  const cuuint64_t strides[1] = {(cuuint64_t)ld * 2};
-  const cuuint32_t box[2] = {(cuuint32_t)BK, (cuuint32_t)box_outer};
-  const cuuint32_t estr[2] = {1, 1};
-  const CUtensorMapDataType dt = dtype == DLION_BF16 ? CU_TENSOR_MAP_DATA_TYPE_BFLOAT16 : CU_TENSOR_MAP_DATA_TYPE_FLOAT16;
-  return fn(map, dt, 2, const_cast<void*>(base), dims, strides, box, estr, CU_TENSOR_MAP_INTERLEAVE_NONE,
-            CU_TENSOR_MAP_SWIZZLE_128B, CU_TENSOR_MAP_L2_PROMOTION_L2_256B, CU_TENSOR_MAP_FLOAT_OOB_FILL_NONE) == CUDA_SUCCESS;
-}
-
 // number of vocabulary splits: minimise (waves of units over the SMs) x (tiles per unit)
 static int plan_splits(int m_tiles, int n_tiles, int ctas) {
   int best = 1;
@@ -437,7 +305,7 @@ extern "C" int dlion_lmhead_logprobs(const void* h, int64_t ld_h, const void* w,
   p.splits = lm::plan_splits(p.m_tiles, p.n_tiles, kNumSMs);
   DLION_CHECK_ARG(workspace_floats >= (int64_t)(2 * p.splits + 1) * rows, "dlion_lmhead_logprobs: workspace too small (see dlion_lmhead_plan)");
   CUtensorMap map_h, map_w;
-  if (!lm::make_map(&map_h, h, hidden, rows, ld_h, lm::BM, dtype) || !lm::make_map(&map_w, w, hidden, vocab, ld_w, lm::BN, dtype)) {
+  if (!tc::make_map(&map_h, h, hidden, rows, ld_h, lm::BM, dtype) || !tc::make_map(&map_w, w, hidden, vocab, ld_w, lm::BN, dtype)) {
     set_error("dlion_lmhead_logprobs: cuTensorMapEncodeTiled unavailable or refused the layout");
     return DLION_E_UNSUPPORTED;
   }
@@ -449,7 +317,7 @@ extern "C" int dlion_lmhead_logprobs(const void* h, int64_t ld_h, const void* w,
   p.rows = rows;
   p.vocab = vocab;
   p.hidden = hidden;
-  p.idesc = lm::instr_desc(dtype == DLION_BF16 ? 1u : 0u);
+  p.idesc = tc::instr_desc(dtype == DLION_BF16 ? 1u : 0u, lm::BM, lm::BN);
   static std::once_flag attr_once;
   static cudaError_t attr_err = cudaSuccess;
   std::call_once(attr_once, [] {

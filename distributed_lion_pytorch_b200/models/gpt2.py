@@ -23,6 +23,7 @@ from ..ops.cross_entropy import linear_cross_entropy, linear_log_probs
 from ..ops.embedding import embed
 from ..ops.linear import fused_linear
 from ..ops.lt_gemm import linear_gelu
+from ..ops.mlp import gelu_mlp
 from ..ops.norm import add_layer_norm
 from ..ops.qkv import split_qkv
 from .common import CausalLMOutput, ConfigBase, PreTrainedMixin, shift_labels
@@ -118,6 +119,11 @@ class GPT2MLP(nn.Module):
 
     def forward(self, x):
         if self.act in ("gelu_new", "gelu_pytorch_tanh"):
+            # one autograd node: GELU in the c_fc GEMM's epilogue forward; backward = tcgen05 dgrad GEMM with the GELU
+            # backward and c_fc's bias gradient in ITS epilogue (ops/mlp.py, csrc/gemm_dgelu_sm100.cu)
+            y = gelu_mlp(x, self.c_fc.weight, self.c_fc.bias, self.c_proj.weight, self.c_proj.bias)
+            if y is not None:
+                return y
             h = linear_gelu(x, self.c_fc.weight, self.c_fc.bias)        # GEMM with the GELU in its epilogue
             if h is None:
                 h = gelu_tanh(self.c_fc(x))

@@ -24,7 +24,7 @@
 extern "C" {
 #endif
 
-#define DLION_VERSION 102
+#define DLION_VERSION 103
 
 typedef enum { DLION_F32 = 0, DLION_BF16 = 1, DLION_F16 = 2 } dlion_dtype;
 
@@ -322,6 +322,17 @@ int dlion_lmhead_plan(int rows, int vocab, int* splits, int64_t* workspace_float
 int dlion_lmhead_logprobs(const void* h, int64_t ld_h, const void* w, int64_t ld_w, const int64_t* labels, float* logp,
                           float* lse, float* workspace, int64_t workspace_floats, int* status, int rows, int vocab,
                           int hidden, int dtype, void* stream);
+
+/* Data-gradient GEMM of an MLP down-projection with the tanh-GELU backward and the up-projection's bias gradient in
+ * its epilogue (tcgen05 / TMEM / 2-D TMA kernel): dpre[m, n] = (dy[m, k] . w[n, k]^T) * gelu_tanh'(pre[m, n]);
+ * part[m_tile, n] (fp32, dlion_dgrad_dgelu_parts(m) x n) receives the column sums of dpre per 128-row tile, which
+ * dlion_dgrad_dgelu_bias_finalize folds (fixed order) into `out[n]` (+= with accumulate).  bf16 / fp16, row-major,
+ * row strides in elements (multiples of 8), 16-byte aligned; dpre may not alias pre.
+ * reference: HF GPT2MLP backward under autograd (Conv1D -> NewGELUActivation -> Conv1D), async_trainer.py:33. */
+int dlion_dgrad_dgelu_parts(int64_t m);
+int dlion_dgrad_dgelu(const void* dy, int64_t ld_dy, const void* w, int64_t ld_w, const void* pre, int64_t ld_pre, void* dpre,
+                      int64_t ld_dpre, float* part, int* status, int m, int n, int k, int dtype, void* stream);
+int dlion_dgrad_dgelu_bias_finalize(const float* part, void* out, int m_tiles, int n, int accumulate, int dtype, void* stream);
 
 /* Blockwise 4-bit weight codec for frozen LoRA base weights (bitsandbytes layout: element 2i in
  * the high nibble of byte i, one fp32 absmax per `blocksize` elements, 16-entry code book given
