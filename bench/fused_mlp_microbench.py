@@ -24,7 +24,8 @@ def timed(fn, iters, flush):
     ts = []
     for _ in range(iters):
         flush.zero_()
-        a, b = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
+        torch.cuda._sleep(400_000)          # ~0.2 ms of GPU spin: the host queues the launches behind it, so the events
+        a, b = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)   # bracket GPU time only
         a.record()
         fn()
         b.record()
@@ -63,8 +64,9 @@ def main():
         t_fused = timed(lambda: mlp.dgrad_dgelu(dy, w, pre, bias_grad_out=bias_grad, accumulate=True), a.iters, flush)
         t_split = timed(split, a.iters, flush)
         t_gemm = timed(lambda: dy @ w.t(), a.iters, flush)
+        t_fused_nobias = timed(lambda: mlp.dgrad_dgelu(dy, w, pre, want_bias_grad=False), a.iters, flush)
         flops = 2.0 * m * n * k
-        row = {"shape": name, "m": m, "n": n, "k": k, "fused_us": round(t_fused, 1), "gemm_plus_kernel_us": round(t_split, 1),
+        row = {"shape": name, "m": m, "n": n, "k": k, "fused_us": round(t_fused, 1), "fused_kernel_only_us": round(t_fused_nobias, 1), "gemm_plus_kernel_us": round(t_split, 1),
                "cublas_gemm_only_us": round(t_gemm, 1), "fused_tflops": round(flops / t_fused / 1e6, 1),
                "speedup": round(t_split / t_fused, 3), "hbm_bytes_min": 2 * (m * k + n * k + 2 * m * n)}
         rows.append(row)

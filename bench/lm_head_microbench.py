@@ -25,7 +25,8 @@ def timed(fn, iters, flush):
     ts = []
     for _ in range(iters):
         flush.zero_()
-        a, b = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
+        torch.cuda._sleep(400_000)          # ~0.2 ms of GPU spin: the host queues the launches behind it, so the events
+        a, b = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)   # bracket GPU time only
         a.record()
         fn()
         b.record()

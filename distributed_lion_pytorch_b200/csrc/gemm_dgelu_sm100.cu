@@ -9,16 +9,18 @@
 // one-pass activation-backward/column-sum kernel 79 + 67 us; here the product never leaves the SM before the
 // activation backward has been applied: fp32 accumulators in TMEM -> registers -> ⊙ gelu'(pre) -> bf16 -> HBM once.
 //
-// One persistent CTA per SM, ten warps:
-//   warp 0 (one lane)   TMA producer of the operand ring: [128 x 64] of dy and [256 x 64] of w per k-step, 3 stages
+// One persistent CTA per SM, nineteen warps:
+//   warp 0 (one lane)   TMA producer of the operand ring: [128 x 64] of dy and [256 x 64] of w per k-step, 4 stages
+//                       (192 KB in flight per SM: the loads are L2 hits at ~1.6 us round trip under this load)
 //   warp 1 (one lane)   `tcgen05.mma.cta_group::1.kind::f16` (M 128, N 256, K 16) into one of two TMEM accumulators
-//   warps 2-9           epilogue, thread = (row, 32-column group).  The [128 x 256] tile is walked in four boxes of
-//                       64 columns; a box of `pre` arrives by TMA in a 4-deep staging ring (128-byte swizzle, 16 KB),
-//                       the thread multiplies its 32 accumulator values (`tcgen05.ld`) by gelu'(pre), writes bf16
-//                       back IN PLACE, and one elected thread sends the box to HBM with a TMA store and re-arms the
-//                       buffer freed by the store before (prefetch distance: three boxes).  Column sums are reduced
-//                       inside the warp by recursive halving (31 shuffles per 32 x 32 patch), the four row quarters
-//                       are folded through 8 KB of shared memory at the end of the tile: deterministic, no atomics.
+//   warps 2-17          epilogue = 4 row quarters x 4 column groups, thread = one row.  The [128 x 256] tile is walked in
+//                       eight boxes of 32 columns; a box of `pre` arrives by TMA in a 4-deep staging ring (64-byte
+//                       swizzle, 8 KB), the thread multiplies its 32 accumulator values (`tcgen05.ld.32x32b.x32`) by
+//                       gelu'(pre), writes bf16 back IN PLACE and its warp arrives on the box's mbarrier; column sums
+//                       are reduced inside the warp by recursive halving (31 shuffles per 32 x 32 patch) and stored per
+//                       32-row quarter — deterministic, no atomics, no block barrier anywhere in the loop
+//   warp 18 (one lane)  store warp: sends each finished box to HBM with a TMA store and re-arms the buffer freed by the
+//                       store before with the `pre` box three boxes ahead
 // All tensor maps cover buffers of THIS GPU only; no load uses cluster multicast.  Waits are bounded (tc05.cuh).
 // reference: HF GPT2MLP backward under autograd (Conv1D -> NewGELUActivation -> Conv1D), reached from
 // accelerator.backward (async_trainer.py:33): a GEMM, ~8 elementwise kernels and a column reduction upstream.
@@ -29,31 +31,43 @@ namespace gd {
 using namespace tc;
 
 constexpr int BM = 128, BN = 256, BK = 64, UK = 16;
-constexpr int kStages = 3;
+constexpr int kStages = 4;
 constexpr int kABytes = BM * BK * 2, kBBytes = BN * BK * 2, kStageBytes = kABytes + kBBytes;
-constexpr int kBoxCols = 64, kBoxes = BN / kBoxCols, kBoxBytes = BM * kBoxCols * 2;   // 16 KB
+constexpr int kBoxCols = 32, kBoxes = BN / kBoxCols, kBoxBytes = BM * kBoxCols * 2;   // [128 x 32] = 8 KB, 64-byte swizzle
 constexpr int kStaging = 4;
-constexpr int kEpiWarps = 8, kEpiThreads = kEpiWarps * 32, kThreads = 64 + kEpiThreads;
-constexpr int kColPartFloats = 2 * 4 * BN;                                          // [tile parity][row quarter][column]
+constexpr int kEpiWarps = 16, kGroups = kEpiWarps / 4;   // 4 row quarters x kGroups column groups
+constexpr int kStoreWarp = 2 + kEpiWarps, kThreads = (kStoreWarp + 1) * 32;
 constexpr int kTmemCols = 512;
-constexpr int kSmemBytes = kStages * kStageBytes + kStaging * kBoxBytes + kColPartFloats * 4 + 256 + 1024;
+constexpr int kSmemBytes = kStages * kStageBytes + kStaging * kBoxBytes + 256 + 1024;
 
 struct Params {
-  float* part;        // [m_tiles, n] column sums per row tile
+  float* part;        // [m_tiles * 4, n] column sums per 32-row quarter of a row tile
   int* status;
+  long long* prof;     // optional [grid][16] cycle counters per wait site (bench/diagnostics), or nullptr
   int m, n, k;
   int m_tiles, n_tiles;
   uint32_t idesc;
 };
 
-// gelu_tanh'(x) = s (1 + x (1 - s) (2k + 6kc x^2)),  s = (1 + tanh(k (x + c x^3))) / 2
+// gelu_tanh'(x) = s (1 + x (1 - s) (2k + 6kc x^2)),  s = (1 + tanh(u)) / 2 = sigmoid(2u),  u = k (x + c x^3)
+// MODE 0: s through tanh.approx (MUFU.TANH);  MODE 1: s = rcp(1 + ex2(-2u log2 e)) (MUFU.EX2 + MUFU.RCP);
+// MODE 2: no activation at all (timing floor of the pipeline, wrong numbers — bench only)
+template <int MODE>
 __device__ __forceinline__ float dgelu(float x) {
   constexpr float kK = 0.7978845608028654f, kC = 0.044715f;
+  if constexpr (MODE == 2) return x;
   const float x2 = x * x;
-  const float u = x * fmaf(kK * kC, x2, kK);
-  float t;
-  asm("tanh.approx.f32 %0, %1;" : "=f"(t) : "f"(u));
-  const float s = fmaf(0.5f, t, 0.5f);
+  float s;
+  if constexpr (MODE == 0) {
+    const float u = x * fmaf(kK * kC, x2, kK);
+    float t;
+    asm("tanh.approx.f32 %0, %1;" : "=f"(t) : "f"(u));
+    s = fmaf(0.5f, t, 0.5f);
+  } else {
+    constexpr float kA = -2.0f * kK * kLog2e;
+    const float e = ex2(x * fmaf(kA * kC, x2, kA));
+    asm("rcp.approx.ftz.f32 %0, %1;" : "=f"(s) : "f"(1.0f + e));
+  }
   const float w = x * fmaf(6.0f * kK * kC, x2, 2.0f * kK);
   return fmaf(s, w * (1.0f - s), s);
 }
@@ -97,24 +111,38 @@ __device__ __forceinline__ float colsum32(float (&v)[32], int lane) {
   return v[0];
 }
 
-template <typename T>
+// cycles spent in one wait, added to slot `slot` of this CTA's counters (only when profiling is on)
+#define GD_TIMED(slot, stmt)                                  \
+  do {                                                        \
+    if (p.prof != nullptr) {                                  \
+      const long long t0_ = clock64();                        \
+      stmt;                                                   \
+      prof_acc[slot] += clock64() - t0_;                      \
+    } else {                                                  \
+      stmt;                                                   \
+    }                                                         \
+  } while (0)
+
+template <typename T, int MODE>
 __global__ void __launch_bounds__(kThreads, 1)
 dgrad_dgelu_kernel(const __grid_constant__ CUtensorMap map_a, const __grid_constant__ CUtensorMap map_b,
                    const __grid_constant__ CUtensorMap map_aux, const __grid_constant__ CUtensorMap map_out, const Params p) {
   extern __shared__ uint8_t smem_raw[];
   uint8_t* smem = reinterpret_cast<uint8_t*>((reinterpret_cast<uintptr_t>(smem_raw) + 1023) & ~uintptr_t(1023));
-  uint8_t* staging = smem + kStages * kStageBytes;                               // 4 x [128 x 64] boxes, swizzled
-  float* colpart = reinterpret_cast<float*>(staging + kStaging * kBoxBytes);
-  uint64_t* full = reinterpret_cast<uint64_t*>(colpart + kColPartFloats);
+  uint8_t* staging = smem + kStages * kStageBytes;                               // 4 x [128 x 32] boxes, swizzled
+  uint64_t* full = reinterpret_cast<uint64_t*>(staging + kStaging * kBoxBytes);
   uint64_t* empty = full + kStages;
   uint64_t* acc_full = empty + kStages;
   uint64_t* acc_empty = acc_full + 2;
   uint64_t* aux_full = acc_empty + 2;
-  uint32_t* tmem_slot = reinterpret_cast<uint32_t*>(aux_full + kStaging);
+  uint64_t* box_done = aux_full + kStaging;                                      // epilogue warps -> store warp
+  uint32_t* tmem_slot = reinterpret_cast<uint32_t*>(box_done + kStaging);
 
   const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
   const int k_blocks = (p.k + BK - 1) / BK;
   const int total = p.m_tiles * p.n_tiles;
+  long long prof_acc[8] = {0, 0, 0, 0, 0, 0, 0, 0};
+  const long long prof_t0 = clock64();
 
   if (warp == 0 && lane == 0) {
     tma_prefetch_desc(&map_a);
@@ -129,7 +157,10 @@ dgrad_dgelu_kernel(const __grid_constant__ CUtensorMap map_a, const __grid_const
       mbar_init(acc_full + a, 1);
       mbar_init(acc_empty + a, kEpiWarps);
     }
-    for (int b = 0; b < kStaging; ++b) mbar_init(aux_full + b, 1);
+    for (int b = 0; b < kStaging; ++b) {
+      mbar_init(aux_full + b, 1);
+      mbar_init(box_done + b, 4);                 // the four row-quarter warps of one column group
+    }
     asm volatile("fence.mbarrier_init.release.cluster;" ::: "memory");
     asm volatile("fence.proxy.async.shared::cta;" ::: "memory");
   }
@@ -151,7 +182,7 @@ dgrad_dgelu_kernel(const __grid_constant__ CUtensorMap map_a, const __grid_const
       for (int t = blockIdx.x; t < total; t += gridDim.x) {
         const int mt = t / p.n_tiles, nt = t - mt * p.n_tiles;
         for (int kb = 0; kb < k_blocks; ++kb) {
-          mbar_wait(empty + stage, phase ^ 1, p.status, 1);
+          GD_TIMED(0, mbar_wait(empty + stage, phase ^ 1, p.status, 1));
           uint8_t* a = smem + stage * kStageBytes;
           mbar_expect_tx(full + stage, kStageBytes);
           tma_load_2d(a, &map_a, kb * BK, mt * BM, full + stage);
@@ -169,11 +200,11 @@ dgrad_dgelu_kernel(const __grid_constant__ CUtensorMap map_a, const __grid_const
       int stage = 0, acc = 0;
       uint32_t phase = 0, acc_phase = 0;
       for (int t = blockIdx.x; t < total; t += gridDim.x) {
-        mbar_wait(acc_empty + acc, acc_phase ^ 1, p.status, 2);
+        GD_TIMED(1, mbar_wait(acc_empty + acc, acc_phase ^ 1, p.status, 2));
         tc_fence_after();
         const uint32_t d = tmem_base + (uint32_t)(acc * BN);
         for (int kb = 0; kb < k_blocks; ++kb) {
-          mbar_wait(full + stage, phase, p.status, 3);
+          GD_TIMED(2, mbar_wait(full + stage, phase, p.status, 3));
           tc_fence_after();
           const uint32_t a_addr = smem_u32(smem + stage * kStageBytes);
           const uint64_t da = smem_desc_sw128(a_addr), db = smem_desc_sw128(a_addr + kABytes);
@@ -193,84 +224,97 @@ dgrad_dgelu_kernel(const __grid_constant__ CUtensorMap map_a, const __grid_const
         }
       }
     }
-  } else {
-    // ================================ epilogue: 8 warps ================================
-    const int ew = warp - 2;                       // 0..7
-    const int quarter = warp & 3;                  // TMEM lanes 32 * (warp % 4) .. + 31 are this warp's
-    const int g = ew >> 2;                         // which 32 of a box's 64 columns
-    const int row_in_tile = quarter * 32 + lane;
-    const int et = threadIdx.x - 64;               // 0..255
-    const bool elected = et == 0;
-    const uint32_t lane_base = tmem_base + ((uint32_t)(quarter * 32) << 16);
-    // box jj of this CTA's sequence: `pre` box -> staging buffer jj % 4
-    auto issue_aux = [&](int jj) {
-      const int t = blockIdx.x + (jj / kBoxes) * gridDim.x;
-      if (t >= total) return;
-      const int mt = t / p.n_tiles, nt = t - mt * p.n_tiles, b = jj % kBoxes, buf = jj % kStaging;
-      mbar_expect_tx(aux_full + buf, kBoxBytes);
-      tma_load_2d(staging + buf * kBoxBytes, &map_aux, nt * BN + b * kBoxCols, mt * BM, aux_full + buf);
-    };
-    if (elected) {
+  } else if (warp == kStoreWarp) {
+    // ================================ store warp: finished boxes out, `pre` boxes in ================================
+    if (lane == 0) {
+      // box jj of this CTA's sequence (8 per tile): `pre` box -> staging buffer jj % 4
+      auto issue_aux = [&](int jj) {
+        const int t = blockIdx.x + (jj / kBoxes) * gridDim.x;
+        if (t >= total) return;
+        const int mt = t / p.n_tiles, nt = t - mt * p.n_tiles, b = jj % kBoxes, buf = jj % kStaging;
+        mbar_expect_tx(aux_full + buf, kBoxBytes);
+        tma_load_2d(staging + buf * kBoxBytes, &map_aux, nt * BN + b * kBoxCols, mt * BM, aux_full + buf);
+      };
       issue_aux(0);
       issue_aux(1);
       issue_aux(2);
+      int j = 0;
+      for (int t = blockIdx.x; t < total; t += gridDim.x) {
+        const int mt = t / p.n_tiles, nt = t - mt * p.n_tiles;
+        for (int b = 0; b < kBoxes; ++b, ++j) {
+          const int buf = j % kStaging;
+          GD_TIMED(3, mbar_wait(box_done + buf, (uint32_t)((j / kStaging) & 1), p.status, 6));   // its four warps have written it
+          tma_store_2d(&map_out, staging + buf * kBoxBytes, nt * BN + b * kBoxCols, mt * BM);
+          tma_store_commit();
+          GD_TIMED(4, tma_store_wait_read<1>());   // the store before this one has drained its buffer ...
+          issue_aux(j + 3);                        // ... which is the one box j + 3 lands in
+        }
+      }
+      tma_store_wait_all();
     }
-    int acc = 0, j = 0, parity = 0;
+  } else {
+    // ================================ epilogue: 16 warps = 4 row quarters x 4 column groups ================================
+    const int quarter = warp & 3;                  // TMEM lanes 32 * (warp % 4) .. + 31 are this warp's
+    const int g = (warp - 2) >> 2;                 // column group: boxes g, g + kGroups, ... of every tile
+    const int row_in_tile = quarter * 32 + lane;
+    const int swz = (row_in_tile >> 1) & 3;        // 64-byte swizzle: 16-byte chunk index ^= address bits 7-8
+    const uint32_t lane_base = tmem_base + ((uint32_t)(quarter * 32) << 16);
+    int acc = 0, tile_i = 0;
     uint32_t acc_phase = 0;
-    for (int t = blockIdx.x; t < total; t += gridDim.x, parity ^= 1) {
+    for (int t = blockIdx.x; t < total; t += gridDim.x, ++tile_i) {
       const int mt = t / p.n_tiles, nt = t - mt * p.n_tiles;
-      float* cp = colpart + parity * (4 * BN);
-      mbar_wait(acc_full + acc, acc_phase, p.status, 4);
+      float* prow = p.part + (int64_t)(mt * 4 + quarter) * p.n;
+      GD_TIMED(5, mbar_wait(acc_full + acc, acc_phase, p.status, 4));
       tc_fence_after();
 #pragma unroll 1
-      for (int b = 0; b < kBoxes; ++b, ++j) {
-        const int buf = j % kStaging;
-        mbar_wait(aux_full + buf, (uint32_t)((j / kStaging) & 1), p.status, 5);
+      for (int b = g; b < kBoxes; b += kGroups) {
+        const int j = tile_i * kBoxes + b, buf = j % kStaging;
+        GD_TIMED(6, mbar_wait(aux_full + buf, (uint32_t)((j / kStaging) & 1), p.status, 5));
         float v[32];
-        tmem_ld32(lane_base + (uint32_t)(acc * BN + b * kBoxCols + g * 32), v);
-        if (b == kBoxes - 1) {                     // last read of this accumulator: hand it back to the MMA warp
+        tmem_ld32(lane_base + (uint32_t)(acc * BN + b * kBoxCols), v);
+        if (b + kGroups >= kBoxes) {                     // last read of this accumulator: hand it back to the MMA warp
           tc_fence_before();
           __syncwarp();
           if (lane == 0) mbar_arrive(acc_empty + acc);
         }
-        uint8_t* rowp = staging + buf * kBoxBytes + row_in_tile * 128;
+        uint8_t* rowp = staging + buf * kBoxBytes + row_in_tile * 64;
 #pragma unroll
         for (int c = 0; c < 4; ++c) {
-          uint4* ptr = reinterpret_cast<uint4*>(rowp + (((g * 4 + c) ^ (row_in_tile & 7)) << 4));
+          uint4* ptr = reinterpret_cast<uint4*>(rowp + ((c ^ swz) << 4));
           const uint4 x = *ptr;
           const uint32_t xin[4] = {x.x, x.y, x.z, x.w};
           uint32_t xo[4];
 #pragma unroll
           for (int e = 0; e < 4; ++e) {
             const float2 f = unpack2<T>(xin[e]);
-            float d0 = v[c * 8 + 2 * e] * dgelu(f.x), d1 = v[c * 8 + 2 * e + 1] * dgelu(f.y);
+            float d0 = v[c * 8 + 2 * e] * dgelu<MODE>(f.x), d1 = v[c * 8 + 2 * e + 1] * dgelu<MODE>(f.y);
             xo[e] = pack2<T>(d0, d1);
             v[c * 8 + 2 * e] = d0;
             v[c * 8 + 2 * e + 1] = d1;
           }
           *ptr = make_uint4(xo[0], xo[1], xo[2], xo[3]);
         }
-        cp[quarter * BN + b * kBoxCols + g * 32 + lane] = colsum32(v, lane);
-        fence_async_smem();
-        asm volatile("bar.sync 1, %0;" ::"n"(kEpiThreads) : "memory");
-        if (elected) {
-          tma_store_2d(&map_out, staging + buf * kBoxBytes, nt * BN + b * kBoxCols, mt * BM);
-          tma_store_commit();
-          tma_store_wait_read<1>();                // the store before this one has drained its buffer ...
-          issue_aux(j + 3);                        // ... which is the one box j + 3 lands in
-        }
+        fence_async_smem();                        // this thread's writes -> visible to the TMA store
+        __syncwarp();
+        if (lane == 0) mbar_arrive(box_done + buf);
+        const float cs = colsum32(v, lane);        // this quarter's 32 rows, column b * 32 + lane
+        const int col = nt * BN + b * kBoxCols + lane;
+        if (col < p.n) prow[col] = cs;
       }
-      // all four row quarters of this tile's column sums are in shared memory (barrier of the last box)
-      const int col = nt * BN + et;
-      if (col < p.n) p.part[(int64_t)mt * p.n + col] = (cp[et] + cp[BN + et]) + (cp[2 * BN + et] + cp[3 * BN + et]);
       if (++acc == 2) {
         acc = 0;
         acc_phase ^= 1;
       }
     }
-    if (elected) tma_store_wait_all();
   }
 
+  if (p.prof != nullptr && lane == 0 && (warp <= 2 || warp == kStoreWarp)) {
+    // slots: 0 producer/empty, 1 mma/acc_empty, 2 mma/full, 3 store/box_done, 4 store/wait_read, 5 epi/acc_full, 6 epi/aux_full
+    long long* out = p.prof + (int64_t)blockIdx.x * 16;
+    for (int i = 0; i < 7; ++i)
+      if (prof_acc[i] != 0) out[i] = prof_acc[i];
+    if (warp == 2) out[8] = clock64() - prof_t0;       // this epilogue warp's whole loop
+  }
   tc_fence_before();
   __syncthreads();
   tc_fence_after();
@@ -280,20 +324,31 @@ dgrad_dgelu_kernel(const __grid_constant__ CUtensorMap map_a, const __grid_const
   }
 }
 
-// bias gradient = sum over the row tiles of the per-tile column sums (fixed order: deterministic)
+// bias gradient = sum over the partial rows (fixed order: deterministic).  32 columns x 32 row groups per CTA: every
+// load of a thread is independent of the others, so the ~20 rows it owns are in flight together.
 template <typename T>
-__global__ void __launch_bounds__(256) dgelu_bias_finalize_kernel(const float* __restrict__ part, T* __restrict__ out, int m_tiles,
-                                                                  int n, int accumulate) {
-  __shared__ float red[4][64];
-  const int tx = threadIdx.x & 63, ty = threadIdx.x >> 6;
-  const int col = blockIdx.x * 64 + tx;
-  float s = 0.f;
-  if (col < n)
-    for (int mt = ty; mt < m_tiles; mt += 4) s += part[(int64_t)mt * n + col];
-  red[ty][tx] = s;
+__global__ void __launch_bounds__(1024) dgelu_bias_finalize_kernel(const float* __restrict__ part, T* __restrict__ out, int rows,
+                                                                   int n, int accumulate) {
+  __shared__ float red[32][33];
+  const int tx = threadIdx.x & 31, ty = threadIdx.x >> 5;
+  const int col = blockIdx.x * 32 + tx;
+  float s0 = 0.f, s1 = 0.f, s2 = 0.f, s3 = 0.f;
+  if (col < n) {
+    int r = ty;
+    for (; r + 96 < rows; r += 128) {
+      s0 += __ldg(part + (int64_t)r * n + col);
+      s1 += __ldg(part + (int64_t)(r + 32) * n + col);
+      s2 += __ldg(part + (int64_t)(r + 64) * n + col);
+      s3 += __ldg(part + (int64_t)(r + 96) * n + col);
+    }
+    for (; r < rows; r += 32) s0 += __ldg(part + (int64_t)r * n + col);
+  }
+  red[ty][tx] = (s0 + s1) + (s2 + s3);
   __syncthreads();
   if (ty == 0 && col < n) {
-    float r = (red[0][tx] + red[1][tx]) + (red[2][tx] + red[3][tx]);
+    float r = 0.f;
+#pragma unroll
+    for (int i = 0; i < 32; ++i) r += red[i][tx];
     if (accumulate) r += DT<T>::to_f(out[col]);
     out[col] = DT<T>::from_f(r);
   }
@@ -304,21 +359,40 @@ __global__ void __launch_bounds__(256) dgelu_bias_finalize_kernel(const float* _
 
 using namespace dlion;
 
-extern "C" int dlion_dgrad_dgelu_parts(int64_t m) { return (int)((m + gd::BM - 1) / gd::BM); }
+static long long* g_dgelu_prof = nullptr;
+/* diagnostics: device buffer of 148 x 16 int64 that the next launches fill with per-wait-site cycle counts (NULL = off) */
+extern "C" int dlion_dgrad_dgelu_set_profile(long long* buf) {
+  g_dgelu_prof = buf;
+  return 0;
+}
 
-template <typename T>
-static int launch_dgrad_dgelu(const CUtensorMap& ma, const CUtensorMap& mb, const CUtensorMap& mx, const CUtensorMap& mo,
-                              const gd::Params& p, cudaStream_t s) {
+extern "C" int dlion_dgrad_dgelu_parts(int64_t m) { return (int)((m + gd::BM - 1) / gd::BM) * 4; }
+
+template <typename T, int MODE>
+static int launch_dgrad_dgelu_mode(const CUtensorMap& ma, const CUtensorMap& mb, const CUtensorMap& mx, const CUtensorMap& mo,
+                                   const gd::Params& p, cudaStream_t s) {
   static std::once_flag once;
   static cudaError_t attr_err = cudaSuccess;
   std::call_once(once, [] {
-    attr_err = cudaFuncSetAttribute(gd::dgrad_dgelu_kernel<T>, cudaFuncAttributeMaxDynamicSharedMemorySize, gd::kSmemBytes);
+    attr_err = cudaFuncSetAttribute(gd::dgrad_dgelu_kernel<T, MODE>, cudaFuncAttributeMaxDynamicSharedMemorySize, gd::kSmemBytes);
   });
   if (attr_err != cudaSuccess) return check_cuda(attr_err, "dlion_dgrad_dgelu: shared-memory attribute");
   const int total = p.m_tiles * p.n_tiles;
   const int grid = total < kNumSMs ? total : kNumSMs;
-  gd::dgrad_dgelu_kernel<T><<<grid, gd::kThreads, gd::kSmemBytes, s>>>(ma, mb, mx, mo, p);
+  gd::dgrad_dgelu_kernel<T, MODE><<<grid, gd::kThreads, gd::kSmemBytes, s>>>(ma, mb, mx, mo, p);
   return DLION_LAUNCH_CHECK("dlion_dgrad_dgelu");
+}
+
+template <typename T>
+static int launch_dgrad_dgelu(const CUtensorMap& ma, const CUtensorMap& mb, const CUtensorMap& mx, const CUtensorMap& mo,
+                              const gd::Params& p, cudaStream_t s) {
+  static const int mode = [] {
+    const char* e = getenv("DLION_DGELU_MODE");      // A/B switch of the microbenchmark
+    return e != nullptr ? atoi(e) : 0;
+  }();
+  if (mode == 1) return launch_dgrad_dgelu_mode<T, 1>(ma, mb, mx, mo, p, s);
+  if (mode == 2) return launch_dgrad_dgelu_mode<T, 2>(ma, mb, mx, mo, p, s);
+  return launch_dgrad_dgelu_mode<T, 0>(ma, mb, mx, mo, p, s);
 }
 
 extern "C" int dlion_dgrad_dgelu(const void* dy, int64_t ld_dy, const void* w, int64_t ld_w, const void* pre, int64_t ld_pre,
@@ -334,6 +408,7 @@ extern "C" int dlion_dgrad_dgelu(const void* dy, int64_t ld_dy, const void* w, i
   gd::Params p{};
   p.part = part;
   p.status = status;
+  p.prof = g_dgelu_prof;
   p.m = m;
   p.n = n;
   p.k = k;
@@ -342,7 +417,8 @@ extern "C" int dlion_dgrad_dgelu(const void* dy, int64_t ld_dy, const void* w, i
   p.idesc = tc::instr_desc(dtype == DLION_BF16 ? 1u : 0u, gd::BM, gd::BN);
   CUtensorMap ma, mb, mx, mo;
   if (!tc::make_map(&ma, dy, k, m, ld_dy, gd::BM, dtype) || !tc::make_map(&mb, w, k, n, ld_w, gd::BN, dtype) ||
-      !tc::make_map(&mx, pre, n, m, ld_pre, gd::BM, dtype) || !tc::make_map(&mo, dpre, n, m, ld_dpre, gd::BM, dtype)) {
+      !tc::make_map(&mx, pre, n, m, ld_pre, gd::BM, dtype, gd::kBoxCols) ||
+      !tc::make_map(&mo, dpre, n, m, ld_dpre, gd::BM, dtype, gd::kBoxCols)) {
     set_error("dlion_dgrad_dgelu: cuTensorMapEncodeTiled unavailable or refused the layout");
     return DLION_E_UNSUPPORTED;
   }
@@ -355,6 +431,6 @@ extern "C" int dlion_dgrad_dgelu_bias_finalize(const float* part, void* out, int
                                                void* stream) {
   DLION_CHECK_ARG(part != nullptr && out != nullptr && m_tiles > 0 && n > 0, "dlion_dgrad_dgelu_bias_finalize: bad arguments");
   cudaStream_t s = (cudaStream_t)stream;
-  DISPATCH_DTYPE(dtype, gd::dgelu_bias_finalize_kernel<T><<<(n + 63) / 64, 256, 0, s>>>(part, (T*)out, m_tiles, n, accumulate));
+  DISPATCH_DTYPE(dtype, gd::dgelu_bias_finalize_kernel<T><<<(n + 31) / 32, 1024, 0, s>>>(part, (T*)out, m_tiles, n, accumulate));
   return DLION_LAUNCH_CHECK("dlion_dgrad_dgelu_bias_finalize");
 }

@@ -144,18 +144,20 @@ inline EncodeTiledFn encode_fn() {
   return fn;
 }
 
-// [outer, inner] 16-bit matrix, `ld` elements between rows, box [box_outer, 64 elements = 128 B], 128-byte swizzle,
+// [outer, inner] 16-bit matrix, `ld` elements between rows, box [box_outer, box_inner]: 64 elements = 128 B rows with
+// the 128-byte swizzle, or 32 elements = 64 B rows with the 64-byte swizzle;
 // out-of-bounds elements read as zero / are not written
-inline bool make_map(CUtensorMap* map, const void* base, int64_t inner, int64_t outer, int64_t ld, int box_outer, int dtype) {
+inline bool make_map(CUtensorMap* map, const void* base, int64_t inner, int64_t outer, int64_t ld, int box_outer, int dtype,
+                     int box_inner = 64) {
   EncodeTiledFn fn = encode_fn();
   if (fn == nullptr) return false;
   const cuuint64_t dims[2] = {(cuuint64_t)inner, (cuuint64_t)outer};
   const cuuint64_t strides[1] = {(cuuint64_t)ld * 2};
-  const cuuint32_t box[2] = {64u, (cuuint32_t)box_outer};
+  const cuuint32_t box[2] = {(cuuint32_t)box_inner, (cuuint32_t)box_outer};
   const cuuint32_t estr[2] = {1, 1};
   const CUtensorMapDataType dt = dtype == DLION_BF16 ? CU_TENSOR_MAP_DATA_TYPE_BFLOAT16 : CU_TENSOR_MAP_DATA_TYPE_FLOAT16;
   return fn(map, dt, 2, const_cast<void*>(base), dims, strides, box, estr, CU_TENSOR_MAP_INTERLEAVE_NONE,
-            CU_TENSOR_MAP_SWIZZLE_128B, CU_TENSOR_MAP_L2_PROMOTION_L2_256B, CU_TENSOR_MAP_FLOAT_OOB_FILL_NONE) == CUDA_SUCCESS;
+            box_inner == 64 ? CU_TENSOR_MAP_SWIZZLE_128B : CU_TENSOR_MAP_SWIZZLE_64B, CU_TENSOR_MAP_L2_PROMOTION_L2_256B, CU_TENSOR_MAP_FLOAT_OOB_FILL_NONE) == CUDA_SUCCESS;
 }
 
 }  // namespace tc

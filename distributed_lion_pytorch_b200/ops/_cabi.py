@@ -115,6 +115,7 @@ def _declare(L: C.CDLL) -> None:
         "dlion_lmhead_plan": [i32, i32, C.POINTER(i32), C.POINTER(i64)],
         "dlion_lmhead_logprobs": [vp, i64, vp, i64, vp, vp, vp, vp, i64, vp, i32, i32, i32, i32, vp],
         "dlion_dgrad_dgelu_parts": [i64],
+        "dlion_dgrad_dgelu_set_profile": [vp],
         "dlion_dgrad_dgelu": [vp, i64, vp, i64, vp, i64, vp, i64, vp, vp, i32, i32, i32, i32, vp],
         "dlion_dgrad_dgelu_bias_finalize": [vp, vp, i32, i32, i32, i32, vp],
         "dlion_lt_available": [],

@@ -330,6 +330,7 @@ int dlion_lmhead_logprobs(const void* h, int64_t ld_h, const void* w, int64_t ld
  * row strides in elements (multiples of 8), 16-byte aligned; dpre may not alias pre.
  * reference: HF GPT2MLP backward under autograd (Conv1D -> NewGELUActivation -> Conv1D), async_trainer.py:33. */
 int dlion_dgrad_dgelu_parts(int64_t m);
+int dlion_dgrad_dgelu_set_profile(long long* buf);   /* diagnostics: 148 x 16 int64 device counters, NULL = off */
 int dlion_dgrad_dgelu(const void* dy, int64_t ld_dy, const void* w, int64_t ld_w, const void* pre, int64_t ld_pre, void* dpre,
                       int64_t ld_dpre, float* part, int* status, int m, int n, int k, int dtype, void* stream);
 int dlion_dgrad_dgelu_bias_finalize(const float* part, void* out, int m_tiles, int n, int accumulate, int dtype, void* stream);
