@@ -125,6 +125,7 @@ def test_gpt2_model_uses_the_fused_mlp_and_agrees_with_the_unfused_one(monkeypat
     torch.manual_seed(0)
     model = build_model("gpt2-tiny", dtype=torch.bfloat16, device="cuda").eval()      # eval: no dropout noise
     ids = torch.randint(0, 512, (4, 64), device="cuda")
+    from distributed_lion_pytorch_b200.ops import mlp
     calls = {"n": 0}
     real = lt_gemm._LinearGelu.apply
 
@@ -132,7 +133,8 @@ def test_gpt2_model_uses_the_fused_mlp_and_agrees_with_the_unfused_one(monkeypat
         calls["n"] += 1
         return real(*a)
     monkeypatch.setattr(lt_gemm._LinearGelu, "apply", staticmethod(counting))
-    loss_f = model(ids, labels=ids).loss
+    monkeypatch.setattr(mlp, "_ENABLED", False)        # the one-node MLP (ops/mlp.py, tested in test_gpu_fused_mlp.py) off:
+    loss_f = model(ids, labels=ids).loss               # this test is about the GELU-epilogue GEMM underneath it
     loss_f.backward()
     assert calls["n"] == model.config.n_layer
     g_f = {n: p.grad.float().clone() for n, p in model.named_parameters()}
