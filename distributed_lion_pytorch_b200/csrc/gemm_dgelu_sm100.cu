@@ -26,6 +26,10 @@
 // accelerator.backward (async_trainer.py:33): a GEMM, ~8 elementwise kernels and a column reduction upstream.
 #include "tc05.cuh"
 
+#ifndef DLION_DGELU_PAIR_DEFAULT
+#define DLION_DGELU_PAIR_DEFAULT false
+#endif
+
 namespace dlion {
 namespace gd {
 using namespace tc;
@@ -324,6 +328,213 @@ dgrad_dgelu_kernel(const __grid_constant__ CUtensorMap map_a, const __grid_const
   }
 }
 
+// ------------------------------------------------------------------------------------------------------------------
+// CTA-pair variant (cta_group::2): two CTAs of a cluster share one [256 x 256] tile.  Each loads its own 128 rows of dy
+// and HALF of the w tile (128 of the 256 rows), one M 256 x N 256 x K 16 `tcgen05.mma.cta_group::2` issued by the leader
+// reads both halves: 8 KB of operands from each CTA's shared memory per MMA instead of 12 KB, and 32 KB instead of 48 KB
+// of TMA traffic per k-step and CTA — the shared-memory bandwidth the epilogue's staging traffic needs.  Each CTA's TMEM
+// receives its 128 rows of the accumulator; the epilogue and the store warp are those of the single-CTA kernel.
+constexpr int kPairStages = 6;
+constexpr int kPairStageBytes = kABytes + kABytes;                                  // [128 x 64] of dy + [128 x 64] of w
+constexpr int kPairSmemBytes = kPairStages * kPairStageBytes + kStaging * kBoxBytes + 512 + 1024;
+
+template <typename T>
+__global__ void __cluster_dims__(2, 1, 1) __launch_bounds__(kThreads, 1)
+dgrad_dgelu_pair_kernel(const __grid_constant__ CUtensorMap map_a, const __grid_constant__ CUtensorMap map_b,
+                        const __grid_constant__ CUtensorMap map_aux, const __grid_constant__ CUtensorMap map_out, const Params p) {
+  extern __shared__ uint8_t smem_raw[];
+  uint8_t* smem = reinterpret_cast<uint8_t*>((reinterpret_cast<uintptr_t>(smem_raw) + 1023) & ~uintptr_t(1023));
+  uint8_t* staging = smem + kPairStages * kPairStageBytes;
+  uint64_t* full = reinterpret_cast<uint64_t*>(staging + kStaging * kBoxBytes);   // used in the leader only
+  uint64_t* empty = full + kPairStages;                                            // one set per CTA (multicast commit)
+  uint64_t* acc_full = empty + kPairStages;                                        // one set per CTA (multicast commit)
+  uint64_t* acc_empty = acc_full + 2;                                              // leader only: 2 x 16 warps arrive
+  uint64_t* aux_full = acc_empty + 2;
+  uint64_t* box_done = aux_full + kStaging;
+  uint32_t* tmem_slot = reinterpret_cast<uint32_t*>(box_done + kStaging);
+
+  const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
+  const uint32_t rank = cluster_ctarank();           // 0 = leader
+  const int cluster_id = blockIdx.x >> 1, n_clusters = gridDim.x >> 1;
+  const int k_blocks = (p.k + BK - 1) / BK;
+  const int pair_m_tiles = (p.m_tiles + 1) >> 1;
+  const int total = pair_m_tiles * p.n_tiles;        // [256 x 256] tiles
+
+  if (warp == 0 && lane == 0) {
+    tma_prefetch_desc(&map_a);
+    tma_prefetch_desc(&map_b);
+    tma_prefetch_desc(&map_aux);
+    tma_prefetch_desc(&map_out);
+    for (int s = 0; s < kPairStages; ++s) {
+      mbar_init(full + s, 1);
+      mbar_init(empty + s, 1);
+    }
+    for (int a = 0; a < 2; ++a) {
+      mbar_init(acc_full + a, 1);
+      mbar_init(acc_empty + a, 2 * kEpiWarps);
+    }
+    for (int b = 0; b < kStaging; ++b) {
+      mbar_init(aux_full + b, 1);
+      mbar_init(box_done + b, 4);
+    }
+    asm volatile("fence.mbarrier_init.release.cluster;" ::: "memory");
+    asm volatile("fence.proxy.async.shared::cta;" ::: "memory");
+  }
+  if (warp == 1) {                                   // the same warp in both CTAs
+    asm volatile("tcgen05.alloc.cta_group::2.sync.aligned.shared::cta.b32 [%0], %1;" ::"r"(smem_u32(tmem_slot)), "r"(kTmemCols)
+                 : "memory");
+    asm volatile("tcgen05.relinquish_alloc_permit.cta_group::2.sync.aligned;" ::: "memory");
+  }
+  tc_fence_before();
+  cluster_sync_all();                                // both CTAs' barriers exist before anything arrives on them remotely
+  tc_fence_after();
+  const uint32_t tmem_base = *tmem_slot;
+
+  if (warp == 0) {
+    // ================================ operand producer (both CTAs) ================================
+    if (lane == 0) {
+      int stage = 0;
+      uint32_t phase = 0;
+      for (int t = cluster_id; t < total; t += n_clusters) {
+        const int pm = t / p.n_tiles, nt = t - pm * p.n_tiles;
+        const int row0 = pm * 2 * BM + (int)rank * BM, wrow0 = nt * BN + (int)rank * (BN / 2);
+        for (int kb = 0; kb < k_blocks; ++kb) {
+          mbar_wait(empty + stage, phase ^ 1, p.status, 1);
+          uint8_t* a = smem + stage * kPairStageBytes;
+          if (rank == 0) mbar_expect_tx(full + stage, 2 * kPairStageBytes);        // both CTAs' bytes land on this barrier
+          tma_load_2d_pair(a, &map_a, kb * BK, row0, full + stage);
+          tma_load_2d_pair(a + kABytes, &map_b, kb * BK, wrow0, full + stage);
+          if (++stage == kPairStages) {
+            stage = 0;
+            phase ^= 1;
+          }
+        }
+      }
+    }
+  } else if (warp == 1) {
+    // ================================ MMA issuer (leader CTA only) ================================
+    if (lane == 0 && rank == 0) {
+      int stage = 0, acc = 0;
+      uint32_t phase = 0, acc_phase = 0;
+      for (int t = cluster_id; t < total; t += n_clusters) {
+        mbar_wait_cluster(acc_empty + acc, acc_phase ^ 1, p.status, 2);            // both CTAs' epilogues have drained it
+        tc_fence_after();
+        const uint32_t d = tmem_base + (uint32_t)(acc * BN);
+        for (int kb = 0; kb < k_blocks; ++kb) {
+          mbar_wait_cluster(full + stage, phase, p.status, 3);
+          tc_fence_after();
+          const uint32_t a_addr = smem_u32(smem + stage * kPairStageBytes);
+          const uint64_t da = smem_desc_sw128(a_addr), db = smem_desc_sw128(a_addr + kABytes);
+#pragma unroll
+          for (int k = 0; k < BK / UK; ++k)
+            umma_f16_pair(d, da + (uint64_t)(k * 2), db + (uint64_t)(k * 2), p.idesc, (uint32_t)((kb | k) != 0));
+          umma_commit_pair(empty + stage);           // frees the stage in both CTAs
+          if (++stage == kPairStages) {
+            stage = 0;
+            phase ^= 1;
+          }
+        }
+        umma_commit_pair(acc_full + acc);            // accumulator complete, both CTAs' epilogues
+        if (++acc == 2) {
+          acc = 0;
+          acc_phase ^= 1;
+        }
+      }
+    }
+  } else if (warp == kStoreWarp) {
+    // ================================ store warp: finished boxes out, `pre` boxes in ================================
+    if (lane == 0) {
+      // box jj of this CTA's sequence (8 per tile): `pre` box -> staging buffer jj % 4
+      auto issue_aux = [&](int jj) {
+        const int t = cluster_id + (jj / kBoxes) * n_clusters;
+        if (t >= total) return;
+        const int pm = t / p.n_tiles, nt = t - pm * p.n_tiles, mt = pm * 2 + (int)rank, b = jj % kBoxes, buf = jj % kStaging;
+        mbar_expect_tx(aux_full + buf, kBoxBytes);
+        tma_load_2d(staging + buf * kBoxBytes, &map_aux, nt * BN + b * kBoxCols, mt * BM, aux_full + buf);
+      };
+      issue_aux(0);
+      issue_aux(1);
+      issue_aux(2);
+      int j = 0;
+      for (int t = cluster_id; t < total; t += n_clusters) {
+        const int pm = t / p.n_tiles, nt = t - pm * p.n_tiles, mt = pm * 2 + (int)rank;
+        for (int b = 0; b < kBoxes; ++b, ++j) {
+          const int buf = j % kStaging;
+          mbar_wait(box_done + buf, (uint32_t)((j / kStaging) & 1), p.status, 6);   // its four warps have written it
+          tma_store_2d(&map_out, staging + buf * kBoxBytes, nt * BN + b * kBoxCols, mt * BM);
+          tma_store_commit();
+          tma_store_wait_read<1>();   // the store before this one has drained its buffer ...
+          issue_aux(j + 3);                        // ... which is the one box j + 3 lands in
+        }
+      }
+      tma_store_wait_all();
+    }
+  } else {
+    // ================================ epilogue: 16 warps = 4 row quarters x 4 column groups ================================
+    const int quarter = warp & 3;                  // TMEM lanes 32 * (warp % 4) .. + 31 are this warp's
+    const int g = (warp - 2) >> 2;                 // column group: boxes g, g + kGroups, ... of every tile
+    const int row_in_tile = quarter * 32 + lane;
+    const int swz = (row_in_tile >> 1) & 3;        // 64-byte swizzle: 16-byte chunk index ^= address bits 7-8
+    const uint32_t lane_base = tmem_base + ((uint32_t)(quarter * 32) << 16);
+    int acc = 0, tile_i = 0;
+    uint32_t acc_phase = 0;
+    for (int t = cluster_id; t < total; t += n_clusters, ++tile_i) {
+      const int pm = t / p.n_tiles, nt = t - pm * p.n_tiles, mt = pm * 2 + (int)rank;
+      float* prow = p.part + (int64_t)(mt * 4 + quarter) * p.n;
+      mbar_wait(acc_full + acc, acc_phase, p.status, 4);
+      tc_fence_after();
+#pragma unroll 1
+      for (int b = g; b < kBoxes; b += kGroups) {
+        const int j = tile_i * kBoxes + b, buf = j % kStaging;
+        mbar_wait(aux_full + buf, (uint32_t)((j / kStaging) & 1), p.status, 5);
+        float v[32];
+        tmem_ld32(lane_base + (uint32_t)(acc * BN + b * kBoxCols), v);
+        if (b + kGroups >= kBoxes) {                     // last read of this accumulator: hand it back to the MMA warp
+          tc_fence_before();
+          __syncwarp();
+          if (lane == 0) mbar_arrive_cluster(acc_empty + acc, 0);   // the leader's barrier counts both CTAs
+        }
+        uint8_t* rowp = staging + buf * kBoxBytes + row_in_tile * 64;
+#pragma unroll
+        for (int c = 0; c < 4; ++c) {
+          uint4* ptr = reinterpret_cast<uint4*>(rowp + ((c ^ swz) << 4));
+          const uint4 x = *ptr;
+          const uint32_t xin[4] = {x.x, x.y, x.z, x.w};
+          uint32_t xo[4];
+#pragma unroll
+          for (int e = 0; e < 4; ++e) {
+            const float2 f = unpack2<T>(xin[e]);
+            float d0 = v[c * 8 + 2 * e] * dgelu<0>(f.x), d1 = v[c * 8 + 2 * e + 1] * dgelu<0>(f.y);
+            xo[e] = pack2<T>(d0, d1);
+            v[c * 8 + 2 * e] = d0;
+            v[c * 8 + 2 * e + 1] = d1;
+          }
+          *ptr = make_uint4(xo[0], xo[1], xo[2], xo[3]);
+        }
+        fence_async_smem();                        // this thread's writes -> visible to the TMA store
+        __syncwarp();
+        if (lane == 0) mbar_arrive(box_done + buf);
+        const float cs = colsum32(v, lane);        // this quarter's 32 rows, column b * 32 + lane
+        const int col = nt * BN + b * kBoxCols + lane;
+        if (col < p.n) prow[col] = cs;
+      }
+      if (++acc == 2) {
+        acc = 0;
+        acc_phase ^= 1;
+      }
+    }
+  }
+
+  __syncwarp();                                      // lanes that had no role wait here for their warp's working lane
+  tc_fence_before();
+  cluster_sync_all();                                // nobody leaves while its pair may still read its shared memory / TMEM
+  tc_fence_after();
+  if (warp == 1) {
+    __syncwarp();
+    asm volatile("tcgen05.dealloc.cta_group::2.sync.aligned.b32 %0, %1;" ::"r"(tmem_base), "r"(kTmemCols) : "memory");
+  }
+}
+
 // bias gradient = sum over the partial rows (fixed order: deterministic).  32 columns x 32 row groups per CTA: every
 // load of a thread is independent of the others, so the ~20 rows it owns are in flight together.
 template <typename T>
@@ -366,7 +577,19 @@ extern "C" int dlion_dgrad_dgelu_set_profile(long long* buf) {
   return 0;
 }
 
-extern "C" int dlion_dgrad_dgelu_parts(int64_t m) { return (int)((m + gd::BM - 1) / gd::BM) * 4; }
+// CTA-pair kernel (cta_group::2) unless switched off; read once
+static bool use_pair() {
+  static const bool on = [] {
+    const char* e = getenv("DLION_DGELU_PAIR");
+    return e == nullptr ? DLION_DGELU_PAIR_DEFAULT : atoi(e) != 0;
+  }();
+  return on;
+}
+
+extern "C" int dlion_dgrad_dgelu_parts(int64_t m) {
+  if (use_pair()) return (int)((m + 2 * gd::BM - 1) / (2 * gd::BM)) * 8;      // both halves of every [256 x 256] tile write
+  return (int)((m + gd::BM - 1) / gd::BM) * 4;
+}
 
 template <typename T, int MODE>
 static int launch_dgrad_dgelu_mode(const CUtensorMap& ma, const CUtensorMap& mb, const CUtensorMap& mx, const CUtensorMap& mo,
@@ -381,6 +604,21 @@ static int launch_dgrad_dgelu_mode(const CUtensorMap& ma, const CUtensorMap& mb,
   const int grid = total < kNumSMs ? total : kNumSMs;
   gd::dgrad_dgelu_kernel<T, MODE><<<grid, gd::kThreads, gd::kSmemBytes, s>>>(ma, mb, mx, mo, p);
   return DLION_LAUNCH_CHECK("dlion_dgrad_dgelu");
+}
+
+template <typename T>
+static int launch_dgrad_dgelu_pair(const CUtensorMap& ma, const CUtensorMap& mb, const CUtensorMap& mx, const CUtensorMap& mo,
+                                   const gd::Params& p, cudaStream_t s) {
+  static std::once_flag once;
+  static cudaError_t attr_err = cudaSuccess;
+  std::call_once(once, [] {
+    attr_err = cudaFuncSetAttribute(gd::dgrad_dgelu_pair_kernel<T>, cudaFuncAttributeMaxDynamicSharedMemorySize, gd::kPairSmemBytes);
+  });
+  if (attr_err != cudaSuccess) return check_cuda(attr_err, "dlion_dgrad_dgelu: shared-memory attribute (pair)");
+  const int total = ((p.m_tiles + 1) / 2) * p.n_tiles;
+  const int grid = 2 * total < kNumSMs ? 2 * total : (kNumSMs & ~1);
+  gd::dgrad_dgelu_pair_kernel<T><<<grid, gd::kThreads, gd::kPairSmemBytes, s>>>(ma, mb, mx, mo, p);
+  return DLION_LAUNCH_CHECK("dlion_dgrad_dgelu (pair)");
 }
 
 template <typename T>
@@ -414,15 +652,20 @@ extern "C" int dlion_dgrad_dgelu(const void* dy, int64_t ld_dy, const void* w, i
   p.k = k;
   p.m_tiles = (m + gd::BM - 1) / gd::BM;
   p.n_tiles = (n + gd::BN - 1) / gd::BN;
-  p.idesc = tc::instr_desc(dtype == DLION_BF16 ? 1u : 0u, gd::BM, gd::BN);
+  const bool pair = use_pair();
+  p.idesc = tc::instr_desc(dtype == DLION_BF16 ? 1u : 0u, pair ? 2 * gd::BM : gd::BM, gd::BN);
   CUtensorMap ma, mb, mx, mo;
-  if (!tc::make_map(&ma, dy, k, m, ld_dy, gd::BM, dtype) || !tc::make_map(&mb, w, k, n, ld_w, gd::BN, dtype) ||
+  if (!tc::make_map(&ma, dy, k, m, ld_dy, gd::BM, dtype) || !tc::make_map(&mb, w, k, n, ld_w, pair ? gd::BN / 2 : gd::BN, dtype) ||
       !tc::make_map(&mx, pre, n, m, ld_pre, gd::BM, dtype, gd::kBoxCols) ||
       !tc::make_map(&mo, dpre, n, m, ld_dpre, gd::BM, dtype, gd::kBoxCols)) {
     set_error("dlion_dgrad_dgelu: cuTensorMapEncodeTiled unavailable or refused the layout");
     return DLION_E_UNSUPPORTED;
   }
   cudaStream_t s = (cudaStream_t)stream;
+  if (pair) {
+    if (dtype == DLION_BF16) return launch_dgrad_dgelu_pair<__nv_bfloat16>(ma, mb, mx, mo, p, s);
+    return launch_dgrad_dgelu_pair<__half>(ma, mb, mx, mo, p, s);
+  }
   if (dtype == DLION_BF16) return launch_dgrad_dgelu<__nv_bfloat16>(ma, mb, mx, mo, p, s);
   return launch_dgrad_dgelu<__half>(ma, mb, mx, mo, p, s);
 }

@@ -89,3 +89,30 @@ def test_gpt2_block_uses_the_fused_mlp_and_matches_the_unfused_path(monkeypatch)
     for n, p in model.named_parameters():
         ref = p.grad.float()
         assert (fused[n] - ref).abs().max().item() <= 3e-2 * ref.abs().max().item() + 1e-4, n
+
+
+def test_cta_pair_variant_matches_reference_in_a_subprocess():
+    """The cta_group::2 build of the same kernel (two CTAs of a cluster share a [256 x 256] tile; opt-in with
+    DLION_DGELU_PAIR=1, read once per process) gives the same numbers as the fp32 reference."""
+    import os
+    import subprocess
+    import sys
+    code = r'''
+import torch, torch.nn.functional as F
+from distributed_lion_pytorch_b200.ops.mlp import dgrad_dgelu
+for m, n, k in ((300, 520, 72), (4096, 3072, 768)):
+    g = torch.Generator(device="cuda").manual_seed(m)
+    dy = (torch.randn(m, k, device="cuda", generator=g) * 0.5).to(torch.bfloat16)
+    w = (torch.randn(n, k, device="cuda", generator=g) * k ** -0.5).to(torch.bfloat16)
+    pre = (torch.randn(m, n, device="cuda", generator=g) * 1.5).to(torch.bfloat16)
+    dpre, db = dgrad_dgelu(dy, w, pre)
+    x = pre.float().requires_grad_(True)
+    F.gelu(x, approximate="tanh").backward(dy.float() @ w.float().t())
+    torch.testing.assert_close(dpre.float(), x.grad, atol=2e-2, rtol=2e-2)
+    torch.testing.assert_close(db.float(), dpre.float().sum(0), atol=0.2, rtol=1e-2)
+print("pair ok")
+'''
+    root = os.path.dirname(os.path.dirname(os.path.abspath(__file__)))
+    env = dict(os.environ, DLION_DGELU_PAIR="1", PYTHONPATH=root + os.pathsep + os.environ.get("PYTHONPATH", ""))
+    r = subprocess.run([sys.executable, "-c", code], env=env, capture_output=True, text=True, timeout=300, cwd=root)
+    assert r.returncode == 0 and "pair ok" in r.stdout, r.stdout + r.stderr
