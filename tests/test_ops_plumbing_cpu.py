@@ -100,3 +100,25 @@ def test_linear_cross_entropy_under_autocast_with_fp32_master_weights(emulate):
         out = m(ids, labels=ids)
     out.loss.backward()
     assert all(p.grad is not None and p.grad.dtype == torch.float32 for p in m.parameters())
+
+
+def test_tensor_core_ops_decline_on_cpu_and_callers_fall_back():
+    """The tcgen05 kernels (LM head, MLP backward) are CUDA-only: on CPU their entry points say "not applicable" and the
+    callers run the plain paths with the same results (ops/lm_head.py, ops/mlp.py)."""
+    import torch.nn.functional as F
+    from distributed_lion_pytorch_b200.ops import cross_entropy as ce, lm_head, mlp
+    torch.manual_seed(0)
+    h = torch.randn(37, 32)
+    w = torch.randn(101, 32)
+    labels = torch.randint(0, 101, (37,))
+    labels[::5] = -100
+    assert not lm_head.supported(h, w) and not lm_head.supported(h.bfloat16(), w.bfloat16())
+    assert ce._fused_no_grad(h, w, labels, -100) is None
+    with torch.no_grad():
+        loss = ce.linear_cross_entropy(h, w, labels)
+        lp = ce.linear_log_probs(h, w, labels)
+    ref = F.cross_entropy(h @ w.t(), labels, ignore_index=-100)
+    torch.testing.assert_close(loss, ref, atol=1e-5, rtol=1e-5)
+    torch.testing.assert_close(-lp.sum() / (labels != -100).sum(), ref, atol=1e-5, rtol=1e-5)
+    x = torch.randn(2, 5, 16, requires_grad=True)
+    assert mlp.gelu_mlp(x, torch.randn(16, 64), torch.zeros(64), torch.randn(64, 16), torch.zeros(16)) is None
