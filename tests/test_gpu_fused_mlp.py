@@ -93,7 +93,7 @@ def test_gpt2_block_uses_the_fused_mlp_and_matches_the_unfused_path(monkeypatch)
 
 def test_cta_pair_variant_matches_reference_in_a_subprocess():
     """The cta_group::2 build of the same kernel (two CTAs of a cluster share a [256 x 256] tile; opt-in with
-    DLION_DGELU_PAIR=1, read once per process) gives the same numbers as the fp32 reference."""
+    DLION_DGELU_VARIANT=pair, read once per process) gives the same numbers as the fp32 reference."""
     import os
     import subprocess
     import sys
@@ -113,6 +113,6 @@ for m, n, k in ((300, 520, 72), (4096, 3072, 768)):
 print("pair ok")
 '''
     root = os.path.dirname(os.path.dirname(os.path.abspath(__file__)))
-    env = dict(os.environ, DLION_DGELU_PAIR="1", PYTHONPATH=root + os.pathsep + os.environ.get("PYTHONPATH", ""))
+    env = dict(os.environ, DLION_DGELU_VARIANT="pair", PYTHONPATH=root + os.pathsep + os.environ.get("PYTHONPATH", ""))
     r = subprocess.run([sys.executable, "-c", code], env=env, capture_output=True, text=True, timeout=300, cwd=root)
     assert r.returncode == 0 and "pair ok" in r.stdout, r.stdout + r.stderr
