@@ -535,240 +535,6 @@ dgrad_dgelu_pair_kernel(const __grid_constant__ CUtensorMap map_a, const __grid_
   }
 }
 
-// ------------------------------------------------------------------------------------------------------------------
-// Register-prefetch build: the epilogue no longer stages `pre` through shared memory.  Thread = row, so a
-// thread's share of a box is 64 contiguous bytes of one row of `pre`: four 16-byte loads straight into registers,
-// issued TWO boxes ahead of their use (three rotating register sets), which hides a DRAM round trip without any ring
-// in shared memory; shared memory then only carries the OUTPUT boxes to the TMA store (4 x 8 KB, freed as soon as the
-// store has read them).  In the staged build above the four column groups consume the four staging buffers at the same
-// time, so every round of four boxes pays a full TMA round trip (measured: 38 % of an epilogue warp's loop).
-constexpr int kRegEpiWarps = 8, kRegGroups = kRegEpiWarps / 4;
-constexpr int kRegStoreWarp = 2 + kRegEpiWarps, kRegThreads = (kRegStoreWarp + 1) * 32;
-constexpr int kRegBoxesPerWarp = kBoxes / kRegGroups;                               // per tile
-
-struct PreRegs {
-  uint4 c[4];
-};
-
-// this thread's 32 values of `pre` for one box (zeros outside the matrix)
-template <typename T>
-__device__ __forceinline__ void load_pre(PreRegs& r, const T* __restrict__ pre, int64_t ld, int row, int col0, int m, int n) {
-#pragma unroll
-  for (int c = 0; c < 4; ++c) {
-    r.c[c] = make_uint4(0u, 0u, 0u, 0u);
-    if (row < m && col0 + c * 8 < n) {
-      const T* ptr = pre + (int64_t)row * ld + col0 + c * 8;
-      asm volatile("ld.global.nc.L1::no_allocate.v4.u32 {%0, %1, %2, %3}, [%4];"
-                   : "=r"(r.c[c].x), "=r"(r.c[c].y), "=r"(r.c[c].z), "=r"(r.c[c].w)
-                   : "l"(ptr));
-    }
-  }
-}
-
-template <typename T>
-__global__ void __launch_bounds__(kRegThreads, 1)
-dgrad_dgelu_reg_kernel(const __grid_constant__ CUtensorMap map_a, const __grid_constant__ CUtensorMap map_b,
-                       const __grid_constant__ CUtensorMap map_out, const T* __restrict__ pre, int64_t ld_pre, const Params p) {
-  extern __shared__ uint8_t smem_raw[];
-  uint8_t* smem = reinterpret_cast<uint8_t*>((reinterpret_cast<uintptr_t>(smem_raw) + 1023) & ~uintptr_t(1023));
-  uint8_t* staging = smem + kStages * kStageBytes;                               // 4 x [128 x 32] OUTPUT boxes, swizzled
-  uint64_t* full = reinterpret_cast<uint64_t*>(staging + kStaging * kBoxBytes);
-  uint64_t* empty = full + kStages;
-  uint64_t* acc_full = empty + kStages;
-  uint64_t* acc_empty = acc_full + 2;
-  uint64_t* box_done = acc_empty + 2;                                            // epilogue warps -> store warp
-  uint64_t* box_free = box_done + kStaging;                                      // store warp -> epilogue warps
-  uint32_t* tmem_slot = reinterpret_cast<uint32_t*>(box_free + kStaging);
-
-  const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
-  const int k_blocks = (p.k + BK - 1) / BK;
-  const int total = p.m_tiles * p.n_tiles;
-
-  if (warp == 0 && lane == 0) {
-    tma_prefetch_desc(&map_a);
-    tma_prefetch_desc(&map_b);
-    tma_prefetch_desc(&map_out);
-    for (int s = 0; s < kStages; ++s) {
-      mbar_init(full + s, 1);
-      mbar_init(empty + s, 1);
-    }
-    for (int a = 0; a < 2; ++a) {
-      mbar_init(acc_full + a, 1);
-      mbar_init(acc_empty + a, kRegEpiWarps);
-    }
-    for (int b = 0; b < kStaging; ++b) {
-      mbar_init(box_done + b, 4);                 // the four row-quarter warps of one column group
-      mbar_init(box_free + b, 1);
-    }
-    asm volatile("fence.mbarrier_init.release.cluster;" ::: "memory");
-    asm volatile("fence.proxy.async.shared::cta;" ::: "memory");
-  }
-  if (warp == 1) {
-    asm volatile("tcgen05.alloc.cta_group::1.sync.aligned.shared::cta.b32 [%0], %1;" ::"r"(smem_u32(tmem_slot)), "r"(kTmemCols)
-                 : "memory");
-    asm volatile("tcgen05.relinquish_alloc_permit.cta_group::1.sync.aligned;" ::: "memory");
-  }
-  tc_fence_before();
-  __syncthreads();
-  tc_fence_after();
-  const uint32_t tmem_base = *tmem_slot;
-
-  if (warp == 0) {
-    // ================================ operand producer ================================
-    if (lane == 0) {
-      int stage = 0;
-      uint32_t phase = 0;
-      for (int t = blockIdx.x; t < total; t += gridDim.x) {
-        const int mt = t / p.n_tiles, nt = t - mt * p.n_tiles;
-        for (int kb = 0; kb < k_blocks; ++kb) {
-          mbar_wait(empty + stage, phase ^ 1, p.status, 1);
-          uint8_t* a = smem + stage * kStageBytes;
-          mbar_expect_tx(full + stage, kStageBytes);
-          tma_load_2d(a, &map_a, kb * BK, mt * BM, full + stage);
-          tma_load_2d(a + kABytes, &map_b, kb * BK, nt * BN, full + stage);
-          if (++stage == kStages) {
-            stage = 0;
-            phase ^= 1;
-          }
-        }
-      }
-    }
-  } else if (warp == 1) {
-    // ================================ MMA issuer ================================
-    if (lane == 0) {
-      int stage = 0, acc = 0;
-      uint32_t phase = 0, acc_phase = 0;
-      for (int t = blockIdx.x; t < total; t += gridDim.x) {
-        mbar_wait(acc_empty + acc, acc_phase ^ 1, p.status, 2);
-        tc_fence_after();
-        const uint32_t d = tmem_base + (uint32_t)(acc * BN);
-        for (int kb = 0; kb < k_blocks; ++kb) {
-          mbar_wait(full + stage, phase, p.status, 3);
-          tc_fence_after();
-          const uint32_t a_addr = smem_u32(smem + stage * kStageBytes);
-          const uint64_t da = smem_desc_sw128(a_addr), db = smem_desc_sw128(a_addr + kABytes);
-#pragma unroll
-          for (int k = 0; k < BK / UK; ++k)
-            umma_f16(d, da + (uint64_t)(k * 2), db + (uint64_t)(k * 2), p.idesc, (uint32_t)((kb | k) != 0));
-          umma_commit(empty + stage);
-          if (++stage == kStages) {
-            stage = 0;
-            phase ^= 1;
-          }
-        }
-        umma_commit(acc_full + acc);
-        if (++acc == 2) {
-          acc = 0;
-          acc_phase ^= 1;
-        }
-      }
-    }
-  } else if (warp == kRegStoreWarp) {
-    // ================================ store warp: finished output boxes -> HBM ================================
-    if (lane == 0) {
-      int j = 0;
-      for (int t = blockIdx.x; t < total; t += gridDim.x) {
-        const int mt = t / p.n_tiles, nt = t - mt * p.n_tiles;
-        for (int b = 0; b < kBoxes; ++b, ++j) {
-          const int buf = j % kStaging;
-          mbar_wait(box_done + buf, (uint32_t)((j / kStaging) & 1), p.status, 6);
-          tma_store_2d(&map_out, staging + buf * kBoxBytes, nt * BN + b * kBoxCols, mt * BM);
-          tma_store_commit();
-          tma_store_wait_read<0>();                // the store has read the box out of shared memory
-          mbar_arrive(box_free + buf);             // its writers may refill the buffer
-        }
-      }
-      tma_store_wait_all();
-    }
-  } else {
-    // ================================ epilogue: 8 warps = 4 row quarters x 2 column groups ================================
-    const int quarter = warp & 3;                  // TMEM lanes 32 * (warp % 4) .. + 31 are this warp's
-    const int g = (warp - 2) >> 2;                 // column group: boxes g, g + 2, g + 4, g + 6 of every tile
-    const int row_in_tile = quarter * 32 + lane;
-    const int swz = (row_in_tile >> 1) & 3;        // 64-byte swizzle: 16-byte chunk index ^= address bits 7-8
-    const uint32_t lane_base = tmem_base + ((uint32_t)(quarter * 32) << 16);
-    const int my_tiles = (total - (int)blockIdx.x + (int)gridDim.x - 1) / (int)gridDim.x;
-    const int S = my_tiles * kRegBoxesPerWarp;     // this warp's boxes, in order
-    int acc = 0;
-    uint32_t acc_phase = 0;
-
-    auto prefetch = [&](PreRegs& r, int s) {
-      if (s >= S) return;
-      const int i = s / kRegBoxesPerWarp, k = s - i * kRegBoxesPerWarp;
-      const int t = blockIdx.x + i * gridDim.x, mt = t / p.n_tiles, nt = t - mt * p.n_tiles;
-      load_pre<T>(r, pre, ld_pre, mt * BM + row_in_tile, nt * BN + (g + kRegGroups * k) * kBoxCols, p.m, p.n);
-    };
-    auto process = [&](const PreRegs& r, int s) {
-      const int i = s / kRegBoxesPerWarp, k = s - i * kRegBoxesPerWarp, b = g + kRegGroups * k;
-      const int t = blockIdx.x + i * gridDim.x, mt = t / p.n_tiles, nt = t - mt * p.n_tiles;
-      if (k == 0) {
-        mbar_wait(acc_full + acc, acc_phase, p.status, 4);
-        tc_fence_after();
-      }
-      float v[32];
-      tmem_ld32(lane_base + (uint32_t)(acc * BN + b * kBoxCols), v);
-      if (k == kRegBoxesPerWarp - 1) {             // last read of this accumulator: hand it back to the MMA warp
-        tc_fence_before();
-        __syncwarp();
-        if (lane == 0) mbar_arrive(acc_empty + acc);
-        if (++acc == 2) {
-          acc = 0;
-          acc_phase ^= 1;
-        }
-      }
-      uint4 out[4];
-#pragma unroll
-      for (int c = 0; c < 4; ++c) {
-        const uint32_t xin[4] = {r.c[c].x, r.c[c].y, r.c[c].z, r.c[c].w};
-        uint32_t xo[4];
-#pragma unroll
-        for (int e = 0; e < 4; ++e) {
-          const float2 f = unpack2<T>(xin[e]);
-          float d0 = v[c * 8 + 2 * e] * dgelu<0>(f.x), d1 = v[c * 8 + 2 * e + 1] * dgelu<0>(f.y);
-          xo[e] = pack2<T>(d0, d1);
-          v[c * 8 + 2 * e] = d0;
-          v[c * 8 + 2 * e + 1] = d1;
-        }
-        out[c] = make_uint4(xo[0], xo[1], xo[2], xo[3]);
-      }
-      const int j = i * kBoxes + b, buf = j % kStaging;
-      mbar_wait(box_free + buf, (uint32_t)(((j / kStaging) & 1) ^ 1), p.status, 5);   // the store of its last use has read it
-      uint8_t* rowp = staging + buf * kBoxBytes + row_in_tile * 64;
-#pragma unroll
-      for (int c = 0; c < 4; ++c) *reinterpret_cast<uint4*>(rowp + ((c ^ swz) << 4)) = out[c];
-      fence_async_smem();                          // this thread's writes -> visible to the TMA store
-      __syncwarp();
-      if (lane == 0) mbar_arrive(box_done + buf);
-      const float cs = colsum32(v, lane);          // this quarter's 32 rows, column b * 32 + lane
-      const int col = nt * BN + b * kBoxCols + lane;
-      if (col < p.n) p.part[(int64_t)(mt * 4 + quarter) * p.n + col] = cs;
-    };
-
-    PreRegs r0 = {}, r1 = {}, r2 = {};
-    prefetch(r0, 0);
-    prefetch(r1, 1);
-    for (int s = 0; s < S; s += 3) {               // three register sets in rotation: loads run two boxes ahead
-      prefetch(r2, s + 2);
-      process(r0, s);
-      if (s + 1 >= S) break;
-      prefetch(r0, s + 3);
-      process(r1, s + 1);
-      if (s + 2 >= S) break;
-      prefetch(r1, s + 4);
-      process(r2, s + 2);
-    }
-  }
-
-  __syncwarp();
-  tc_fence_before();
-  __syncthreads();
-  tc_fence_after();
-  if (warp == 1) {
-    __syncwarp();
-    asm volatile("tcgen05.dealloc.cta_group::1.sync.aligned.b32 %0, %1;" ::"r"(tmem_base), "r"(kTmemCols) : "memory");
-  }
-}
-
 // bias gradient = sum over the partial rows (fixed order: deterministic).  32 columns x 32 row groups per CTA: every
 // load of a thread is independent of the others, so the ~20 rows it owns are in flight together.
 template <typename T>
@@ -811,15 +577,13 @@ extern "C" int dlion_dgrad_dgelu_set_profile(long long* buf) {
   return 0;
 }
 
-// which build of the kernel runs: 0 = staged (`pre` through a shared-memory ring), 1 = CTA pair (cta_group::2),
-// 2 = register prefetch.  DLION_DGELU_VARIANT=staged|pair|reg, read once per process.
+// which build of the kernel runs: 0 = single CTA (default), 1 = CTA pair (cta_group::2).
+// DLION_DGELU_VARIANT=staged|pair, read once per process.
 static int variant() {
   static const int v = [] {
     const char* e = getenv("DLION_DGELU_VARIANT");
     if (e == nullptr) return DLION_DGELU_VARIANT_DEFAULT;
-    if (e[0] == 'p') return 1;
-    if (e[0] == 'r') return 2;
-    return 0;
+    return e[0] == 'p' ? 1 : 0;
   }();
   return v;
 }
@@ -843,21 +607,6 @@ static int launch_dgrad_dgelu_mode(const CUtensorMap& ma, const CUtensorMap& mb,
   const int grid = total < kNumSMs ? total : kNumSMs;
   gd::dgrad_dgelu_kernel<T, MODE><<<grid, gd::kThreads, gd::kSmemBytes, s>>>(ma, mb, mx, mo, p);
   return DLION_LAUNCH_CHECK("dlion_dgrad_dgelu");
-}
-
-template <typename T>
-static int launch_dgrad_dgelu_reg(const CUtensorMap& ma, const CUtensorMap& mb, const CUtensorMap& mo, const void* pre, int64_t ld_pre,
-                                  const gd::Params& p, cudaStream_t s) {
-  static std::once_flag once;
-  static cudaError_t attr_err = cudaSuccess;
-  std::call_once(once, [] {
-    attr_err = cudaFuncSetAttribute(gd::dgrad_dgelu_reg_kernel<T>, cudaFuncAttributeMaxDynamicSharedMemorySize, gd::kSmemBytes);
-  });
-  if (attr_err != cudaSuccess) return check_cuda(attr_err, "dlion_dgrad_dgelu: shared-memory attribute (reg)");
-  const int total = p.m_tiles * p.n_tiles;
-  const int grid = total < kNumSMs ? total : kNumSMs;
-  gd::dgrad_dgelu_reg_kernel<T><<<grid, gd::kRegThreads, gd::kSmemBytes, s>>>(ma, mb, mo, (const T*)pre, ld_pre, p);
-  return DLION_LAUNCH_CHECK("dlion_dgrad_dgelu (reg)");
 }
 
 template <typename T>
@@ -916,10 +665,6 @@ extern "C" int dlion_dgrad_dgelu(const void* dy, int64_t ld_dy, const void* w, i
     return DLION_E_UNSUPPORTED;
   }
   cudaStream_t s = (cudaStream_t)stream;
-  if (variant() == 2) {
-    if (dtype == DLION_BF16) return launch_dgrad_dgelu_reg<__nv_bfloat16>(ma, mb, mo, pre, ld_pre, p, s);
-    return launch_dgrad_dgelu_reg<__half>(ma, mb, mo, pre, ld_pre, p, s);
-  }
   if (pair) {
     if (dtype == DLION_BF16) return launch_dgrad_dgelu_pair<__nv_bfloat16>(ma, mb, mx, mo, p, s);
     return launch_dgrad_dgelu_pair<__half>(ma, mb, mx, mo, p, s);

@@ -48,7 +48,6 @@ WANT = {
     "lmhead_merge_kernel": [("fp32", r"lmhead_merge_kernel")],
     "dgrad_dgelu_kernel": [("bf16_tcgen05", r"dgrad_dgelu_kernelI13__nv_bfloat16")],
     "dgrad_dgelu_pair_kernel": [("bf16_cta_group2", r"dgrad_dgelu_pair_kernelI13__nv_bfloat16")],
-    "dgrad_dgelu_reg_kernel": [("bf16_register_prefetch", r"dgrad_dgelu_reg_kernelI13__nv_bfloat16")],
     "dgelu_bias_finalize_kernel": [("bf16", r"dgelu_bias_finalize_kernelI13__nv_bfloat16")],
     "q4_quantize_kernel": [("bf16", r"q4_quantize_kernelI13__nv_bfloat16")],
     "q4_dequantize_kernel": [("bf16", r"q4_dequantize_kernelI13__nv_bfloat16")],

@@ -2,10 +2,10 @@
 # final check of HEAD on one B200: the register-prefetch build of the MLP-backward kernel (test + microbench, all three
 # builds), then the standing verify script, the evaluation-forward microbench and an ncu capture of the default build
 mkdir -p gpurun_out
-for v in reg staged; do
+for v in pair staged; do
   echo "== variant $v"
   DLION_DGELU_VARIANT=$v timeout 120 python -m pytest tests/test_gpu_fused_mlp.py -x -q -m gpu -k "dgrad or node" 2>&1 | tail -2
-  DLION_DGELU_VARIANT=$v timeout 60 python bench/fused_mlp_microbench.py --iters 10 --out gpurun_out/fused_mlp_mb_$v.json 2>&1 | head -3 | cut -c1-260
+  DLION_DGELU_VARIANT=$v timeout 60 python bench/fused_mlp_microbench.py --iters 10 --out gpurun_out/fused_mlp_mb_$v.json 2>&1 | cut -c1-260 | head -3
 done
 bash scripts/gpu_verify.sh 2>/dev/null | grep -v "^+"
 timeout 120 python bench/eval_loss_microbench.py > gpurun_out/eval_loss_mb.json 2> gpurun_out/eval_loss_mb.err; tail -1 gpurun_out/eval_loss_mb.json; tail -2 gpurun_out/eval_loss_mb.err
