@@ -35,14 +35,13 @@ namespace gd {
 using namespace tc;
 
 constexpr int BM = 128, BN = 256, BK = 64, UK = 16;
-constexpr int kStages = 4;
 constexpr int kABytes = BM * BK * 2, kBBytes = BN * BK * 2, kStageBytes = kABytes + kBBytes;
 constexpr int kBoxCols = 32, kBoxes = BN / kBoxCols, kBoxBytes = BM * kBoxCols * 2;   // [128 x 32] = 8 KB, 64-byte swizzle
 constexpr int kStaging = 4;
 constexpr int kEpiWarps = 16, kGroups = kEpiWarps / 4;   // 4 row quarters x kGroups column groups
 constexpr int kStoreWarp = 2 + kEpiWarps, kThreads = (kStoreWarp + 1) * 32;
 constexpr int kTmemCols = 512;
-constexpr int kSmemBytes = kStages * kStageBytes + kStaging * kBoxBytes + 256 + 1024;
+constexpr int smem_bytes(int stages, int nbuf) { return stages * kStageBytes + nbuf * kBoxBytes + 512 + 1024; }
 
 struct Params {
   float* part;        // [m_tiles * 4, n] column sums per 32-row quarter of a row tile
@@ -127,20 +126,21 @@ __device__ __forceinline__ float colsum32(float (&v)[32], int lane) {
     }                                                         \
   } while (0)
 
-template <typename T, int MODE>
+// STAGES operand stages of 48 KB and NBUF staging boxes of 8 KB: <4, 4> or, with a whole tile of `pre` boxes in flight, <3, 8>
+template <typename T, int MODE, int STAGES, int NBUF>
 __global__ void __launch_bounds__(kThreads, 1)
 dgrad_dgelu_kernel(const __grid_constant__ CUtensorMap map_a, const __grid_constant__ CUtensorMap map_b,
                    const __grid_constant__ CUtensorMap map_aux, const __grid_constant__ CUtensorMap map_out, const Params p) {
   extern __shared__ uint8_t smem_raw[];
   uint8_t* smem = reinterpret_cast<uint8_t*>((reinterpret_cast<uintptr_t>(smem_raw) + 1023) & ~uintptr_t(1023));
-  uint8_t* staging = smem + kStages * kStageBytes;                               // 4 x [128 x 32] boxes, swizzled
-  uint64_t* full = reinterpret_cast<uint64_t*>(staging + kStaging * kBoxBytes);
-  uint64_t* empty = full + kStages;
-  uint64_t* acc_full = empty + kStages;
+  uint8_t* staging = smem + STAGES * kStageBytes;                               // NBUF x [128 x 32] boxes, swizzled
+  uint64_t* full = reinterpret_cast<uint64_t*>(staging + NBUF * kBoxBytes);
+  uint64_t* empty = full + STAGES;
+  uint64_t* acc_full = empty + STAGES;
   uint64_t* acc_empty = acc_full + 2;
   uint64_t* aux_full = acc_empty + 2;
-  uint64_t* box_done = aux_full + kStaging;                                      // epilogue warps -> store warp
-  uint32_t* tmem_slot = reinterpret_cast<uint32_t*>(box_done + kStaging);
+  uint64_t* box_done = aux_full + NBUF;                                      // epilogue warps -> store warp
+  uint32_t* tmem_slot = reinterpret_cast<uint32_t*>(box_done + NBUF);
 
   const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
   const int k_blocks = (p.k + BK - 1) / BK;
@@ -153,7 +153,7 @@ dgrad_dgelu_kernel(const __grid_constant__ CUtensorMap map_a, const __grid_const
     tma_prefetch_desc(&map_b);
     tma_prefetch_desc(&map_aux);
     tma_prefetch_desc(&map_out);
-    for (int s = 0; s < kStages; ++s) {
+    for (int s = 0; s < STAGES; ++s) {
       mbar_init(full + s, 1);
       mbar_init(empty + s, 1);
     }
@@ -161,7 +161,7 @@ dgrad_dgelu_kernel(const __grid_constant__ CUtensorMap map_a, const __grid_const
       mbar_init(acc_full + a, 1);
       mbar_init(acc_empty + a, kEpiWarps);
     }
-    for (int b = 0; b < kStaging; ++b) {
+    for (int b = 0; b < NBUF; ++b) {
       mbar_init(aux_full + b, 1);
       mbar_init(box_done + b, 4);                 // the four row-quarter warps of one column group
     }
@@ -191,7 +191,7 @@ dgrad_dgelu_kernel(const __grid_constant__ CUtensorMap map_a, const __grid_const
           mbar_expect_tx(full + stage, kStageBytes);
           tma_load_2d(a, &map_a, kb * BK, mt * BM, full + stage);
           tma_load_2d(a + kABytes, &map_b, kb * BK, nt * BN, full + stage);
-          if (++stage == kStages) {
+          if (++stage == STAGES) {
             stage = 0;
             phase ^= 1;
           }
@@ -216,7 +216,7 @@ dgrad_dgelu_kernel(const __grid_constant__ CUtensorMap map_a, const __grid_const
           for (int k = 0; k < BK / UK; ++k)
             umma_f16(d, da + (uint64_t)(k * 2), db + (uint64_t)(k * 2), p.idesc, (uint32_t)((kb | k) != 0));
           umma_commit(empty + stage);
-          if (++stage == kStages) {
+          if (++stage == STAGES) {
             stage = 0;
             phase ^= 1;
           }
@@ -235,23 +235,21 @@ dgrad_dgelu_kernel(const __grid_constant__ CUtensorMap map_a, const __grid_const
       auto issue_aux = [&](int jj) {
         const int t = blockIdx.x + (jj / kBoxes) * gridDim.x;
         if (t >= total) return;
-        const int mt = t / p.n_tiles, nt = t - mt * p.n_tiles, b = jj % kBoxes, buf = jj % kStaging;
+        const int mt = t / p.n_tiles, nt = t - mt * p.n_tiles, b = jj % kBoxes, buf = jj % NBUF;
         mbar_expect_tx(aux_full + buf, kBoxBytes);
         tma_load_2d(staging + buf * kBoxBytes, &map_aux, nt * BN + b * kBoxCols, mt * BM, aux_full + buf);
       };
-      issue_aux(0);
-      issue_aux(1);
-      issue_aux(2);
+      for (int jj = 0; jj < NBUF - 1; ++jj) issue_aux(jj);
       int j = 0;
       for (int t = blockIdx.x; t < total; t += gridDim.x) {
         const int mt = t / p.n_tiles, nt = t - mt * p.n_tiles;
         for (int b = 0; b < kBoxes; ++b, ++j) {
-          const int buf = j % kStaging;
-          GD_TIMED(3, mbar_wait(box_done + buf, (uint32_t)((j / kStaging) & 1), p.status, 6));   // its four warps have written it
+          const int buf = j % NBUF;
+          GD_TIMED(3, mbar_wait(box_done + buf, (uint32_t)((j / NBUF) & 1), p.status, 6));   // its four warps have written it
           tma_store_2d(&map_out, staging + buf * kBoxBytes, nt * BN + b * kBoxCols, mt * BM);
           tma_store_commit();
           GD_TIMED(4, tma_store_wait_read<1>());   // the store before this one has drained its buffer ...
-          issue_aux(j + 3);                        // ... which is the one box j + 3 lands in
+          issue_aux(j + NBUF - 1);                 // ... which is the one box j + NBUF - 1 lands in
         }
       }
       tma_store_wait_all();
@@ -272,8 +270,8 @@ dgrad_dgelu_kernel(const __grid_constant__ CUtensorMap map_a, const __grid_const
       tc_fence_after();
 #pragma unroll 1
       for (int b = g; b < kBoxes; b += kGroups) {
-        const int j = tile_i * kBoxes + b, buf = j % kStaging;
-        GD_TIMED(6, mbar_wait(aux_full + buf, (uint32_t)((j / kStaging) & 1), p.status, 5));
+        const int j = tile_i * kBoxes + b, buf = j % NBUF;
+        GD_TIMED(6, mbar_wait(aux_full + buf, (uint32_t)((j / NBUF) & 1), p.status, 5));
         float v[32];
         tmem_ld32(lane_base + (uint32_t)(acc * BN + b * kBoxCols), v);
         if (b + kGroups >= kBoxes) {                     // last read of this accumulator: hand it back to the MMA warp
@@ -577,13 +575,14 @@ extern "C" int dlion_dgrad_dgelu_set_profile(long long* buf) {
   return 0;
 }
 
-// which build of the kernel runs: 0 = single CTA (default), 1 = CTA pair (cta_group::2).
-// DLION_DGELU_VARIANT=staged|pair, read once per process.
+// which build of the kernel runs: 0 = single CTA, 4 operand stages + 4 staging boxes; 1 = CTA pair (cta_group::2);
+// 2 = single CTA, 3 operand stages + 8 staging boxes (a whole tile of `pre` in flight).
+// DLION_DGELU_VARIANT=staged|pair|deep, read once per process.
 static int variant() {
   static const int v = [] {
     const char* e = getenv("DLION_DGELU_VARIANT");
     if (e == nullptr) return DLION_DGELU_VARIANT_DEFAULT;
-    return e[0] == 'p' ? 1 : 0;
+    return e[0] == 'p' ? 1 : (e[0] == 'd' ? 2 : 0);
   }();
   return v;
 }
@@ -594,18 +593,19 @@ extern "C" int dlion_dgrad_dgelu_parts(int64_t m) {
   return (int)((m + gd::BM - 1) / gd::BM) * 4;
 }
 
-template <typename T, int MODE>
+template <typename T, int MODE, int STAGES, int NBUF>
 static int launch_dgrad_dgelu_mode(const CUtensorMap& ma, const CUtensorMap& mb, const CUtensorMap& mx, const CUtensorMap& mo,
                                    const gd::Params& p, cudaStream_t s) {
+  constexpr int kSmem = gd::smem_bytes(STAGES, NBUF);
   static std::once_flag once;
   static cudaError_t attr_err = cudaSuccess;
   std::call_once(once, [] {
-    attr_err = cudaFuncSetAttribute(gd::dgrad_dgelu_kernel<T, MODE>, cudaFuncAttributeMaxDynamicSharedMemorySize, gd::kSmemBytes);
+    attr_err = cudaFuncSetAttribute(gd::dgrad_dgelu_kernel<T, MODE, STAGES, NBUF>, cudaFuncAttributeMaxDynamicSharedMemorySize, kSmem);
   });
   if (attr_err != cudaSuccess) return check_cuda(attr_err, "dlion_dgrad_dgelu: shared-memory attribute");
   const int total = p.m_tiles * p.n_tiles;
   const int grid = total < kNumSMs ? total : kNumSMs;
-  gd::dgrad_dgelu_kernel<T, MODE><<<grid, gd::kThreads, gd::kSmemBytes, s>>>(ma, mb, mx, mo, p);
+  gd::dgrad_dgelu_kernel<T, MODE, STAGES, NBUF><<<grid, gd::kThreads, kSmem, s>>>(ma, mb, mx, mo, p);
   return DLION_LAUNCH_CHECK("dlion_dgrad_dgelu");
 }
 
@@ -626,14 +626,15 @@ static int launch_dgrad_dgelu_pair(const CUtensorMap& ma, const CUtensorMap& mb,
 
 template <typename T>
 static int launch_dgrad_dgelu(const CUtensorMap& ma, const CUtensorMap& mb, const CUtensorMap& mx, const CUtensorMap& mo,
-                              const gd::Params& p, cudaStream_t s) {
+                              const gd::Params& p, cudaStream_t s, bool deep) {
   static const int mode = [] {
     const char* e = getenv("DLION_DGELU_MODE");      // A/B switch of the microbenchmark
     return e != nullptr ? atoi(e) : 0;
   }();
-  if (mode == 1) return launch_dgrad_dgelu_mode<T, 1>(ma, mb, mx, mo, p, s);
-  if (mode == 2) return launch_dgrad_dgelu_mode<T, 2>(ma, mb, mx, mo, p, s);
-  return launch_dgrad_dgelu_mode<T, 0>(ma, mb, mx, mo, p, s);
+  if (deep) return launch_dgrad_dgelu_mode<T, 0, 3, 8>(ma, mb, mx, mo, p, s);
+  if (mode == 1) return launch_dgrad_dgelu_mode<T, 1, 4, 4>(ma, mb, mx, mo, p, s);
+  if (mode == 2) return launch_dgrad_dgelu_mode<T, 2, 4, 4>(ma, mb, mx, mo, p, s);
+  return launch_dgrad_dgelu_mode<T, 0, 4, 4>(ma, mb, mx, mo, p, s);
 }
 
 extern "C" int dlion_dgrad_dgelu(const void* dy, int64_t ld_dy, const void* w, int64_t ld_w, const void* pre, int64_t ld_pre,
@@ -669,8 +670,8 @@ extern "C" int dlion_dgrad_dgelu(const void* dy, int64_t ld_dy, const void* w, i
     if (dtype == DLION_BF16) return launch_dgrad_dgelu_pair<__nv_bfloat16>(ma, mb, mx, mo, p, s);
     return launch_dgrad_dgelu_pair<__half>(ma, mb, mx, mo, p, s);
   }
-  if (dtype == DLION_BF16) return launch_dgrad_dgelu<__nv_bfloat16>(ma, mb, mx, mo, p, s);
-  return launch_dgrad_dgelu<__half>(ma, mb, mx, mo, p, s);
+  if (dtype == DLION_BF16) return launch_dgrad_dgelu<__nv_bfloat16>(ma, mb, mx, mo, p, s, variant() == 2);
+  return launch_dgrad_dgelu<__half>(ma, mb, mx, mo, p, s, variant() == 2);
 }
 
 extern "C" int dlion_dgrad_dgelu_bias_finalize(const float* part, void* out, int m_tiles, int n, int accumulate, int dtype,
