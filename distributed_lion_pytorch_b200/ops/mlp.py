@@ -22,6 +22,7 @@ import torch
 from . import _cabi, lt_gemm, mark_grad_written, require_library
 
 _ENABLED = os.environ.get("DLION_FUSED_MLP", "1") == "1"
+_EMULATE = os.environ.get("DLION_EMULATE_KERNELS") == "1"   # CPU stand-ins, to test the autograd plumbing
 _STATUS: Dict[int, torch.Tensor] = {}
 
 
@@ -36,7 +37,19 @@ def dgrad_dgelu(dy: torch.Tensor, w: torch.Tensor, pre: torch.Tensor, bias_grad_
                 accumulate: bool = False, want_bias_grad: bool = True):
     """``dpre = (dy @ w.T) * gelu_tanh'(pre)`` with ``w`` [n, k]; returns ``(dpre, db)`` where ``db`` is the column sum
     of ``dpre`` in ``pre.dtype`` (written / accumulated into ``bias_grad_out`` when given; ``None`` if not wanted)."""
-    assert dy.is_cuda and dy.dtype == w.dtype == pre.dtype and dy.dtype in (torch.bfloat16, torch.float16)
+    if not dy.is_cuda:                       # torch stand-in with the kernel's contract (CPU tests of the plumbing)
+        x = pre.float()
+        kk, cc = 0.7978845608028654, 0.044715
+        sg = 0.5 * (1.0 + torch.tanh(kk * (x + cc * x * x * x)))
+        dpre = ((dy.float() @ w.float().t()) * (sg + sg * (1.0 - sg) * x * (2 * kk + 6 * kk * cc * x * x))).to(pre.dtype)
+        if not want_bias_grad:
+            return dpre, None
+        sums = dpre.float().sum(0)
+        if bias_grad_out is None:
+            return dpre, sums.to(pre.dtype)
+        bias_grad_out.copy_((sums + bias_grad_out.float()) if accumulate else sums)
+        return dpre, bias_grad_out
+    assert dy.dtype == w.dtype == pre.dtype and dy.dtype in (torch.bfloat16, torch.float16)
     m, k = dy.shape
     n = w.shape[0]
     assert w.shape[1] == k and pre.shape == (m, n)
@@ -72,7 +85,7 @@ class _GeluMLP(torch.autograd.Function):
         inner = w_fc.shape[1]
         pre = torch.empty(x2.shape[0], inner, dtype=x.dtype, device=x.device)
         act = torch.empty_like(pre)
-        if not lt_gemm.gemm(x2, w_fc, act, epilogue=lt_gemm.GELU_AUX_BIAS, bias=b_fc, aux=pre):
+        if not (x.is_cuda and lt_gemm.gemm(x2, w_fc, act, epilogue=lt_gemm.GELU_AUX_BIAS, bias=b_fc, aux=pre)):
             from .activation import gelu_tanh
             torch.addmm(b_fc, x2, w_fc, out=pre)
             act = gelu_tanh(pre)
@@ -123,15 +136,20 @@ def gelu_mlp(x: torch.Tensor, w_fc: torch.Tensor, b_fc: torch.Tensor, w_proj: to
              b_proj: torch.Tensor) -> Optional[torch.Tensor]:
     """``gelu_tanh(x @ w_fc + b_fc) @ w_proj + b_proj`` (HF Conv1D weights, [in, out]) as one autograd node, or ``None``
     when the fused backward does not apply (CPU, fp32, autograd off, odd shapes, library missing, switched off)."""
-    if not (_ENABLED and x.is_cuda and torch.is_grad_enabled() and require_library() and lt_gemm.available()):
+    if not (_ENABLED and torch.is_grad_enabled()):
         return None
-    if b_fc is None or b_proj is None or x.dtype not in (torch.bfloat16, torch.float16):
+    if x.is_cuda:
+        if not (require_library() and lt_gemm.available()) or x.dtype not in (torch.bfloat16, torch.float16):
+            return None
+    elif not _EMULATE:
+        return None
+    if b_fc is None or b_proj is None:
         return None
     if not (x.dtype == w_fc.dtype == b_fc.dtype == w_proj.dtype == b_proj.dtype):
         return None
     inner, out = w_proj.shape
     if w_fc.shape[1] != inner or inner % 8 or out % 8 or w_fc.shape[0] % 8 or not (_ok16(w_fc) and _ok16(w_proj)) \
-            or not w_fc.is_contiguous() or b_fc.data_ptr() % 16:
+            or not w_fc.is_contiguous() or (x.is_cuda and b_fc.data_ptr() % 16):
         return None
     if not (x.requires_grad or w_fc.requires_grad or w_proj.requires_grad):
         return None

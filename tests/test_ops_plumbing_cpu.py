@@ -122,3 +122,76 @@ def test_tensor_core_ops_decline_on_cpu_and_callers_fall_back():
     torch.testing.assert_close(-lp.sum() / (labels != -100).sum(), ref, atol=1e-5, rtol=1e-5)
     x = torch.randn(2, 5, 16, requires_grad=True)
     assert mlp.gelu_mlp(x, torch.randn(16, 64), torch.zeros(64), torch.randn(64, 16), torch.zeros(16)) is None
+
+
+def test_fused_mlp_node_plumbing_on_cpu(monkeypatch):
+    """The one-node GPT-2 MLP (ops/mlp.py) with torch stand-ins for its kernels: gradients equal plain autograd's, a
+    second backward accumulates into the live gradients and marks them written, and the down-projection's bias gradient
+    arrives through the producer hand-off when the incoming gradient carries it (reference: HF GPT2MLP under autograd,
+    async_trainer.py:33)."""
+    import torch.nn.functional as F
+    from distributed_lion_pytorch_b200.ops import linear, mlp
+    monkeypatch.setattr(mlp, "_EMULATE", True)
+    torch.manual_seed(0)
+    E, I = 16, 64
+    x = torch.randn(3, 5, E, requires_grad=True)
+    w_fc = torch.nn.Parameter(torch.randn(E, I) * E ** -0.5)
+    b_fc = torch.nn.Parameter(torch.randn(I) * 0.1)
+    w_pr = torch.nn.Parameter(torch.randn(I, E) * I ** -0.5)
+    b_pr = torch.nn.Parameter(torch.randn(E) * 0.1)
+    dy = torch.randn(3, 5, E)
+    y = mlp.gelu_mlp(x, w_fc, b_fc, w_pr, b_pr)
+    assert y is not None
+    y.backward(dy)
+    got = [t.grad.clone() for t in (x, w_fc, b_fc, w_pr, b_pr)]
+    ref_in = [t.detach().clone().requires_grad_(True) for t in (x, w_fc, b_fc, w_pr, b_pr)]
+    yr = F.gelu(ref_in[0] @ ref_in[1] + ref_in[2], approximate="tanh") @ ref_in[3] + ref_in[4]
+    yr.backward(dy)
+    torch.testing.assert_close(y, yr, atol=1e-5, rtol=1e-5)
+    for a, r in zip(got, ref_in):
+        torch.testing.assert_close(a, r.grad, atol=1e-4, rtol=1e-4)
+    # steady state: gradients exist, the node adds into them itself (autograd gets None) and marks them
+    for t in (w_fc, b_fc, w_pr, b_pr):
+        t._dlion_touched = False
+    mlp.gelu_mlp(x, w_fc, b_fc, w_pr, b_pr).backward(dy)
+    for t, a in zip((x, w_fc, b_fc, w_pr, b_pr), got):
+        torch.testing.assert_close(t.grad, 2 * a, atol=2e-4, rtol=1e-4)
+    assert all(getattr(t, "_dlion_touched", False) for t in (w_fc, b_fc, w_pr, b_pr))
+    # bias hand-off: the producer of dy attached the column sums for b_proj -> no pass over dy, the sums are used as is
+    before = linear.HANDOFFS
+    y3 = mlp.gelu_mlp(x, w_fc, b_fc, w_pr, b_pr)
+    g = dy.clone()
+    fake = torch.full((E,), 7.0)
+    linear.attach_column_sums(g, b_pr, fake)
+    old = b_pr.grad.clone()
+    y3.backward(g)
+    assert linear.HANDOFFS == before + 1
+    torch.testing.assert_close(b_pr.grad, old + fake)
+    # switched off / no bias / autograd off: the caller gets None and runs the plain modules
+    monkeypatch.setattr(mlp, "_ENABLED", False)
+    assert mlp.gelu_mlp(x, w_fc, b_fc, w_pr, b_pr) is None
+    monkeypatch.setattr(mlp, "_ENABLED", True)
+    assert mlp.gelu_mlp(x, w_fc, None, w_pr, b_pr) is None
+    with torch.no_grad():
+        assert mlp.gelu_mlp(x, w_fc, b_fc, w_pr, b_pr) is None
+
+
+def test_gpt2_with_the_fused_mlp_node_equals_the_plain_modules_on_cpu(monkeypatch):
+    from distributed_lion_pytorch_b200.models import build_model
+    from distributed_lion_pytorch_b200.ops import mlp
+    torch.manual_seed(0)
+    model = build_model("gpt2-tiny", dtype=torch.float32, device="cpu", pretrained=False).eval()
+    ids = torch.randint(0, 512, (2, 32))
+    monkeypatch.setattr(mlp, "_EMULATE", True)
+    calls = []
+    real = mlp.dgrad_dgelu
+    monkeypatch.setattr(mlp, "dgrad_dgelu", lambda *a, **k: calls.append(1) or real(*a, **k))
+    model(ids, labels=ids).loss.backward()
+    assert len(calls) == model.config.n_layer
+    fused = {n: p.grad.clone() for n, p in model.named_parameters()}
+    model.zero_grad(set_to_none=True)
+    monkeypatch.setattr(mlp, "_EMULATE", False)
+    model(ids, labels=ids).loss.backward()
+    assert len(calls) == model.config.n_layer
+    for n, p in model.named_parameters():
+        torch.testing.assert_close(fused[n], p.grad, atol=1e-5, rtol=1e-4, msg=n)
