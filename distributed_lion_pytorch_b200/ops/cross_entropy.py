@@ -208,7 +208,7 @@ def _fused_no_grad(h: torch.Tensor, weight: torch.Tensor, labels: torch.Tensor, 
     log-probabilities straight out of TMEM, no logits block, no padded copy of the head.  Else None."""
     if torch.is_grad_enabled() and (h.requires_grad or weight.requires_grad):
         return None
-    if ignore_index >= 0 or not h.is_cuda or h.shape[0] == 0:
+    if ignore_index >= 0 or h.shape[0] == 0 or not (h.is_cuda or lm_head._EMULATE):
         return None
     cd = _compute_dtype(h)
     if not lm_head.supported(h, weight, cd):

@@ -21,6 +21,7 @@ import torch
 from . import _cabi, require_library
 
 _STATUS: Dict[int, torch.Tensor] = {}
+_EMULATE = os.environ.get("DLION_EMULATE_KERNELS") == "1"   # CPU stand-in, to test the dispatch around the kernel
 
 
 def enabled() -> bool:
@@ -30,6 +31,8 @@ def enabled() -> bool:
 def supported(h: torch.Tensor, weight: torch.Tensor, dtype: Optional[torch.dtype] = None) -> bool:
     """16-bit CUDA operands, hidden a multiple of 8, library present and the path not switched off."""
     dt = dtype or h.dtype
+    if _EMULATE and not h.is_cuda:
+        return enabled() and h.dim() == 2 and weight.dim() == 2 and h.shape[1] == weight.shape[1] and h.shape[0] > 0
     return (h.is_cuda and weight.is_cuda and enabled() and dt in (torch.bfloat16, torch.float16)
             and h.dim() == 2 and weight.dim() == 2 and h.shape[1] == weight.shape[1] and h.shape[1] % 8 == 0
             and h.shape[0] > 0 and require_library())
@@ -51,6 +54,14 @@ def _rowmajor16(t: torch.Tensor) -> torch.Tensor:
 def lm_head_log_probs(h: torch.Tensor, weight: torch.Tensor, labels: Optional[torch.Tensor],
                       want_lse: bool = True) -> Tuple[Optional[torch.Tensor], Optional[torch.Tensor]]:
     """h [N, H], weight [V, H] (same 16-bit dtype, CUDA), labels [N] int64 or None → (logp | None, lse | None)."""
+    if not h.is_cuda:                        # torch stand-in with the kernel's contract: fp32 logits, never stored
+        logits = h.detach().float() @ weight.detach().float().t()
+        lse = torch.logsumexp(logits, dim=-1)
+        if labels is None:
+            return None, lse
+        valid = (labels >= 0) & (labels < weight.shape[0])
+        picked = logits.gather(1, labels.clamp(0, weight.shape[0] - 1)[:, None]).squeeze(1)
+        return torch.where(valid, picked - lse, torch.zeros_like(lse)), (lse if want_lse else None)
     assert h.dtype == weight.dtype and h.dtype in (torch.bfloat16, torch.float16), (h.dtype, weight.dtype)
     h, weight = _rowmajor16(h.detach()), _rowmajor16(weight.detach())
     N, H = h.shape

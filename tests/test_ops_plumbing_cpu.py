@@ -195,3 +195,39 @@ def test_gpt2_with_the_fused_mlp_node_equals_the_plain_modules_on_cpu(monkeypatc
     assert len(calls) == model.config.n_layer
     for n, p in model.named_parameters():
         torch.testing.assert_close(fused[n], p.grad, atol=1e-5, rtol=1e-4, msg=n)
+
+
+def test_lm_head_dispatch_on_cpu(monkeypatch):
+    """Who gets the logits-free LM-head kernel (ops/lm_head.py): calls that need no gradient — evaluation loss, frozen
+    reference model, no_grad log-probs — and nobody else; with a CPU stand-in for the kernel the dispatch is testable
+    here (reference: run_clm.py:626-639 evaluation, dpo_llama2.py:219-231 reference log-probs)."""
+    import torch.nn.functional as F
+    from distributed_lion_pytorch_b200.ops import cross_entropy as ce, lm_head
+    monkeypatch.setattr(lm_head, "_EMULATE", True)
+    torch.manual_seed(0)
+    h = torch.randn(37, 32)
+    w = torch.nn.Parameter(torch.randn(101, 32))
+    labels = torch.randint(0, 101, (37,))
+    labels[::5] = -100
+    calls = []
+    real = lm_head.lm_head_log_probs
+    monkeypatch.setattr(lm_head, "lm_head_log_probs", lambda *a, **k: calls.append(1) or real(*a, **k))
+    ref = F.cross_entropy(h @ w.detach().t(), labels, ignore_index=-100)
+    ref_lp = -F.cross_entropy(h @ w.detach().t(), labels, ignore_index=-100, reduction="none")
+    with torch.no_grad():                                  # evaluation: fused
+        torch.testing.assert_close(ce.linear_cross_entropy(h, w, labels), ref, atol=1e-5, rtol=1e-5)
+        torch.testing.assert_close(ce.linear_log_probs(h, w, labels), ref_lp, atol=1e-5, rtol=1e-5)
+    assert len(calls) == 2
+    frozen = w.detach()                                    # frozen reference model with grad mode on: fused
+    torch.testing.assert_close(ce.linear_log_probs(h, frozen, labels), ref_lp, atol=1e-5, rtol=1e-5)
+    assert len(calls) == 3
+    loss = ce.linear_cross_entropy(h, w, labels)           # training: not the no-grad kernel, and a gradient comes back
+    loss.backward()
+    assert len(calls) == 3 and w.grad is not None
+    with torch.no_grad():                                  # an ignore_index that is a real token id: not fused
+        ce.linear_cross_entropy(h, w, labels.clamp(min=0), ignore_index=3)
+    assert len(calls) == 3
+    monkeypatch.setenv("DLION_LMHEAD_FUSED", "0")          # switched off
+    with torch.no_grad():
+        torch.testing.assert_close(ce.linear_cross_entropy(h, w, labels), ref, atol=1e-5, rtol=1e-5)
+    assert len(calls) == 3
