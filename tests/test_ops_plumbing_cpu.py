@@ -231,3 +231,25 @@ def test_lm_head_dispatch_on_cpu(monkeypatch):
     with torch.no_grad():
         torch.testing.assert_close(ce.linear_cross_entropy(h, w, labels), ref, atol=1e-5, rtol=1e-5)
     assert len(calls) == 3
+
+
+def test_tensor_core_kernel_planning_is_host_only_and_sane():
+    """`dlion_lmhead_plan` / `dlion_dgrad_dgelu_parts` are plain host functions of the library (callable without a GPU):
+    the vocabulary split count keeps every SM busy without shredding the vocabulary, and the workspace sizes are what the
+    Python wrappers allocate (csrc/lmhead_lse_sm100.cu, csrc/gemm_dgelu_sm100.cu)."""
+    from distributed_lion_pytorch_b200.ops import _cabi, lm_head
+    if not _cabi.available():
+        pytest.skip("libdlion.so not built")
+    for rows, vocab in ((128, 256), (4096, 50257), (20480, 50257), (8192, 32000), (515, 32000), (1, 8)):
+        splits, ws = lm_head.plan(rows, vocab)
+        m_tiles, n_tiles = (rows + 127) // 128, (vocab + 255) // 256
+        assert 1 <= splits <= min(n_tiles, 64)
+        assert ws == (2 * splits + 1) * rows
+        units = m_tiles * splits
+        waves = -(-units // 148)
+        # no worse than 25 % over the ideal tile count per SM once there is more than a wave of work
+        if m_tiles * n_tiles >= 4 * 148:
+            assert waves * -(-n_tiles // splits) <= 1.25 * (m_tiles * n_tiles / 148) + 1
+    L = _cabi.lib()
+    assert L.dlion_dgrad_dgelu_parts(20480) == 160 * 4 and L.dlion_dgrad_dgelu_parts(1) == 4
+    assert L.dlion_dgrad_dgelu_parts(129) == 2 * 4
